@@ -1,0 +1,44 @@
+"""Access to the committed golden files (outputs of the reference, see tests/golden/make_golden.py).
+The .xz files are unpacked once into tests/golden/_cache/ (git-ignored)."""
+import hashlib
+import json
+import lzma
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+CACHE = os.path.join(GOLD, "_cache")
+MANIFEST = json.load(open(os.path.join(GOLD, "manifest.json")))
+
+
+def _unpack(name, want_sha):
+    os.makedirs(CACHE, exist_ok=True)
+    dst = os.path.join(CACHE, name)
+    if not os.path.exists(dst):
+        data = lzma.open(os.path.join(GOLD, name + ".xz"), "rb").read()
+        assert hashlib.sha256(data).hexdigest() == want_sha, "golden file corrupt: " + name
+        tmp = dst + ".tmp%d" % os.getpid()
+        with open(tmp, "wb") as f:
+            f.write(data)
+        os.replace(tmp, dst)
+    return dst
+
+
+def bundle_path(cfg):
+    return _unpack(cfg + ".bundle", MANIFEST[cfg]["bundle_sha256"])
+
+
+def fixture_path(cfg, tag):
+    return _unpack("%s.%s.fix" % (cfg, tag), MANIFEST[cfg]["fixtures"][tag]["sha256"])
+
+
+def fixture_args(cfg, tag):
+    """psc/pisc/init-mode the fixture was made with."""
+    a = MANIFEST[cfg]["fixtures"][tag]["args"].split()
+    kv = {a[i][2:]: a[i + 1] for i in range(0, len(a) - 1) if a[i].startswith("--")}
+    return dict(psc=int(kv.get("psc", 1)), pisc=int(kv.get("pisc", 1)),
+                init_mode=MANIFEST[cfg]["init_mode"])
+
+
+def all_fixtures(skip=()):
+    return [(c, t) for c in sorted(MANIFEST) for t in sorted(MANIFEST[c]["fixtures"]) if c not in skip]
