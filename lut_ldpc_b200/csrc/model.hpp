@@ -1,0 +1,111 @@
+// Host-side model of a designed LUT decoder and the compiler that turns the reference's LUT trees
+// into straight-line "node programs" the kernels execute.
+//
+// What this mirrors in the reference (paths relative to the reference tree):
+//   graph flattening      LDPC_Code_LUT::decoder_parameterization   src/LDPC_Code_LUT.cpp:488-541
+//   tree slot selection   LDPC_Code_LUT::set_trees                  src/LDPC_Code_LUT.cpp:120-169
+//   tree text format      operator>>(Array<Array<LUT_Tree>>)        src/LUT_Tree.cpp:847-927, :448-535
+//   node evaluation       LUT_Tree_Node::var_msg_update / chk_msg_update   src/LUT_Tree.cpp:402-445
+//   leave-one-out         LUT_Tree::var_msg_update / chk_msg_update / dec_update   src/LUT_Tree.cpp:774-820
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace lutldpc {
+
+enum NodeType { NODE_IM = 0, NODE_ROOT = 1, NODE_MSG = 2, NODE_CHA = 3 };  // src/LUT_Tree.hpp:188-194
+
+struct TreeNode {
+  int type = 0, K = 0;
+  std::vector<int> Q;      // half table (var/dec trees) or magnitude table (check trees)
+  std::vector<int> child;  // indices into Tree::nodes
+};
+struct Tree {
+  int tree_type = 0, num_leaves = 0;
+  std::vector<TreeNode> nodes;  // pre-order, nodes[0] is the root
+};
+struct TreeArray {  // Array<Array<LUT_Tree>>: [iteration slot][degree slot]
+  int n_iter = 0, n_deg = 0;
+  std::vector<Tree> t;
+  const Tree& at(int it, int dg) const { return t[(size_t)it * n_deg + dg]; }
+};
+
+// Everything LDPC_Code_LUT::save_code stores that the decode path reads (src/LDPC_Code_LUT.cpp:643-697).
+struct DecoderModel {
+  int nvar = 0, nchk = 0, nchk_lin_indep = 0, num_edges = 0, max_iters = 0, Nq_Cha = 0;
+  bool minLUT = true;
+  std::vector<int32_t> dv, dc, cn_msg_idx, Nq_Msg, reuse, cha2msg;
+  std::vector<double> qb_Cha, qb_Msg;
+  TreeArray var_trees, chk_trees;
+  int gen_rows = 0, gen_cols = 0;
+  std::vector<uint8_t> gen;  // dense parity part P, codeword = [u, P*u]
+  // derived (set_trees / decoder_parameterization)
+  std::vector<int32_t> var_tree_idx_iter, var_tree_idx_degree, chk_tree_idx_degree;
+  std::vector<int32_t> vn_edge0;   // [nvar+1] first edge of each VN (edges are VN-major)
+  std::vector<int32_t> cn_start;   // [nchk+1] offsets into cn_msg_idx
+  std::vector<int32_t> chk_equ_idx;  // VN index of every entry of cn_msg_idx
+  int ninfo() const { return nvar - nchk_lin_indep; }
+  double rate() const { return double(ninfo()) / nvar; }
+};
+
+bool parse_tree_array(const char* txt, size_t len, TreeArray& out, std::string& err);
+bool load_bundle_file(const char* path, DecoderModel& m, std::string& err);
+// fills the derived members and validates; false + err on unsupported/inconsistent input
+bool finalize_model(DecoderModel& m, std::string& err);
+
+// ---- storage code ---------------------------------------------------------------------------
+// A label m in [0,Nq) (reference convention: m < Nq/2 <=> negative LLR <=> bit 1) is stored as a
+// q-bit sign/magnitude code  c = sign << (q-1) | mag,  q = ceil(log2 Nq):
+//   m <  Nq/2 : sign = 1, mag = Nq/2 - 1 - m        m >= Nq/2 : sign = 0, mag = m - Nq/2
+// (src/LDPC_Code_LUT.cpp:368-374 computes exactly this pair inside chk_update_minsum).
+int code_bits(int Nq);
+int label_to_code(int m, int Nq);
+int code_to_label(int c, int Nq);  // -1 for a code no label maps to
+
+// ---- node programs ----------------------------------------------------------------------------
+constexpr int kMaxOpInputs = 16;
+enum OpKind : uint8_t { OP_NARROW = 0, OP_WIDE = 1 };  // index fits a byte lane / a 16-bit lane
+
+struct DevOp {  // 64 bytes, read by the kernels from shared memory
+  uint32_t table_off;   // byte offset of this op's table inside the program's table blob
+  uint8_t n_in, kind, out_slot, q_out;
+  uint8_t sym;          // var/dec: 1 = half table, sign of the last input folded out
+  uint8_t chk;          // 1 = check-node op (magnitude index + parity)
+  uint8_t idx_bits, pad0;
+  uint8_t in_slot[kMaxOpInputs];
+  uint8_t sh[kMaxOpInputs];
+  uint8_t q[kMaxOpInputs];
+  uint8_t pad1[4];
+};
+static_assert(sizeof(DevOp) == 64, "DevOp layout");
+
+struct DevProgHeader {  // 64 bytes
+  uint32_t n_ops, n_slots, n_in, n_out;  // n_in = number of message inputs (dv or dc); +1 channel slot for var/dec
+  uint32_t ops_off, outs_off, tables_off, total_bytes;  // byte offsets from the header start
+  uint32_t table_bytes, has_cha, q_in, q_out;
+  uint32_t pad[4];
+};
+static_assert(sizeof(DevProgHeader) == 64, "DevProgHeader layout");
+
+struct NodeProgram {
+  int n_in = 0, n_out = 0, n_slots = 0, n_lookups_naive = 0;
+  bool has_cha = false;
+  std::vector<DevOp> ops;
+  std::vector<uint8_t> out_slot;  // slot holding output ii
+  std::vector<uint8_t> tables;
+  int q_in = 0, q_out = 0;
+  // serialised image: header | ops | outs | tables, 16-byte aligned pieces
+  std::vector<uint8_t> image() const;
+};
+
+enum ProgMode { PROG_VAR = 0, PROG_DEC = 1, PROG_CHK = 2 };
+// Compiles tree `t` for a node of degree `deg`:
+//   PROG_VAR: deg outputs, output ii = tree over (inputs without ii) ++ channel   (LUT_Tree.cpp:774-790)
+//   PROG_DEC: 1 output, tree over all inputs ++ channel                           (LUT_Tree.cpp:809-820)
+//   PROG_CHK: deg outputs, output ii = tree over (inputs without ii)              (LUT_Tree.cpp:792-807)
+// Nq_in = alphabet of the message inputs, Nq_cha = alphabet of the channel label.
+bool compile_program(const Tree& t, int deg, ProgMode mode, int Nq_in, int Nq_cha, NodeProgram& out,
+                     std::string& err);
+
+}  // namespace lutldpc
