@@ -1,0 +1,160 @@
+/* lutldpc.h -- C ABI of the B200-native batched LUT-LDPC decoder (liblutldpc_b200.so).
+ *
+ * The reference (mmeidlinger/lut_ldpc) has no FFI layer: its boundary for this path is the C++ class
+ * lut_ldpc::LDPC_Code_LUT behind itpp::Channel_Code (src/LDPC_Code_LUT.hpp:86-285) called from
+ * LDPC_BER_Sim::sim_snr_point (src/LDPC_BER_Sim.cpp:246-311).  Each entry point below names the
+ * reference interface it replaces (paths relative to the reference tree).  INTEGRATION.md shows the
+ * C++ stub a maintainer adds on the reference side.
+ *
+ * Conventions: plain pointers and sizes only; every call returns LUTLDPC_OK (0) or a negative
+ * status and never throws/aborts across the ABI; lutldpc_last_error() gives the message of the last
+ * failing call on that handle (or of the last failing create when handle == NULL).  A handle is bound
+ * to the CUDA device that was current when it was created and is not thread-safe (the reference
+ * object is not re-entrant either: lut_decode mutates the member `msgs`, src/LDPC_Code_LUT.hpp:311).
+ * There is no CPU fallback: without a CUDA device create fails with LUTLDPC_ERR_CUDA.
+ *
+ * Labels: a quantised value m is the reference's integer in [0,Nq), m < Nq/2 <=> negative LLR <=>
+ * bit 1 (src/LDPC_Code_LUT.cpp:260-261,275).  Frame-major buffers: element (f, v) at f*nvar + v.
+ */
+#ifndef LUTLDPC_H
+#define LUTLDPC_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LUTLDPC_ABI_VERSION 1
+
+enum {
+  LUTLDPC_OK = 0,
+  LUTLDPC_ERR_ARG = -1,     /* bad argument (NULL, size, range) */
+  LUTLDPC_ERR_MODEL = -2,   /* decoder description inconsistent or unsupported */
+  LUTLDPC_ERR_CUDA = -3,    /* CUDA runtime error / no device */
+  LUTLDPC_ERR_STATE = -4    /* call not valid in the handle's current state */
+};
+enum { LUTLDPC_INIT_CONT = 0, LUTLDPC_INIT_QCHA = 1 };   /* LDPC_Code_LUT::initial_message_mode_t */
+enum { LUTLDPC_TRACE_INIT = 0, LUTLDPC_TRACE_CN = 1, LUTLDPC_TRACE_VN = 2 };
+
+typedef struct lutldpc_decoder lutldpc_decoder;
+
+/* Flattened LDPC_Code_LUT: exactly the variables LDPC_Code_LUT::save_code writes
+ * (src/LDPC_Code_LUT.cpp:643-697); trees as the reference's own text serialisation
+ * (operator<< on Array<Array<LUT_Tree>>, src/LUT_Tree.cpp:847-864). */
+typedef struct lutldpc_desc {
+  int32_t nvar, nchk, nchk_lin_indep, num_edges, max_iters;
+  int32_t Nq_Cha, min_lut;
+  const int32_t* dv_vec;       /* [nvar]  */
+  const int32_t* dc_vec;       /* [nchk]  */
+  const int32_t* cn_msg_idx;   /* [num_edges] */
+  const int32_t* Nq_Msg;       /* [max_iters] */
+  const int32_t* reuse_vec;    /* [max_iters], 0/1 */
+  const int32_t* Nq_Cha_2_Nq_Msg_map; /* [Nq_Cha] or NULL */
+  const double* qb_Cha;        /* [Nq_Cha-1] */
+  const double* qb_Msg;        /* [n_qb_Msg] */
+  int32_t n_qb_Msg;
+  const char* var_tree_string; size_t var_tree_len;
+  const char* chk_tree_string; size_t chk_tree_len;   /* may be NULL/0 when min_lut != 0 */
+  const uint8_t* gen_parity;   /* optional dense P [gen_rows][gen_cols], codeword = [u, P*u] */
+  int32_t gen_rows, gen_cols;
+} lutldpc_desc;
+
+typedef struct lutldpc_info {
+  int32_t nvar, nchk, nchk_lin_indep, ninfo, num_edges, max_iters, Nq_Cha, min_lut, has_gen;
+  int32_t n_degree_classes;
+  int64_t lookups_per_frame_iter;        /* LUT evaluations the compiled programs do per VN pass */
+  int64_t lookups_per_frame_iter_naive;  /* what the reference's recursion does: sum dv*(nodes) */
+  double rate;
+} lutldpc_info;
+
+int lutldpc_abi_version(void);
+/* message of the last failure; handle may be NULL for create errors */
+const char* lutldpc_last_error(const lutldpc_decoder* h);
+
+/* ---- construction: LDPC_Code_LUT ctor + set_code + set_trees (src/LDPC_Code_LUT.cpp:51-169,488-541),
+ *      from-file ctor / load_code (:568-641) for the bundle form of the codec */
+int lutldpc_create(const lutldpc_desc* desc, lutldpc_decoder** out);
+int lutldpc_create_from_bundle(const char* bundle_path, lutldpc_decoder** out);
+void lutldpc_destroy(lutldpc_decoder* h);
+int lutldpc_get_info(const lutldpc_decoder* h, lutldpc_info* info);
+
+/* LDPC_Code_LUT::set_exit_conditions(max_iters, psc, pisc), src/LDPC_Code_LUT.cpp:176-185.
+ * max_iters must equal the number of designed iterations: the decision trees belong to the last one. */
+int lutldpc_set_exit_conditions(lutldpc_decoder* h, int max_iters, int psc, int pisc);
+/* LDPC_Code_LUT::set_initial_message_mode, src/LDPC_Code_LUT.hpp:237-239 */
+int lutldpc_set_initial_message_mode(lutldpc_decoder* h, int mode);
+/* the stream all later work of this handle is enqueued on (a cudaStream_t; NULL = default stream) */
+int lutldpc_set_stream(lutldpc_decoder* h, void* cuda_stream);
+/* how often (in iterations) the host looks at the count of unfinished frames to stop a batch early;
+ * 0 = never look (fully asynchronous: all max_iters iterations are enqueued, finished frames idle) */
+int lutldpc_set_poll_interval(lutldpc_decoder* h, int every_n_iterations);
+
+/* ---- decode.  n_frames independent frames per call (the reference decodes one).
+ *
+ * lutldpc_decode_quantized == LDPC_Code_LUT::lut_decode(LLRin_cha, LLRin_msg, LLRout)
+ * (src/LDPC_Code_LUT.cpp:259-353), the bit-exact entry:
+ *   llr_cha, llr_msg  [n_frames][nvar] labels in [0,Nq_Cha) / [0,Nq_Msg(0))
+ *   out_bits          [n_frames][nvar] 0/1 (LLRout; the first ninfo of a frame are decode()'s result)
+ *   out_iters         [n_frames] lut_decode's return: 0, +n, +max_iters or -max_iters
+ * Host pointers; the copies run on the handle's stream and the call returns after they completed. */
+int lutldpc_decode_quantized(lutldpc_decoder* h, int n_frames, const uint8_t* llr_cha, const uint8_t* llr_msg,
+                             uint8_t* out_bits, int32_t* out_iters);
+/* Same with DEVICE pointers; asynchronous on the handle's stream (no host synchronisation when
+ * poll_every == 0: all max_iters iterations are enqueued, finished frames idle). */
+int lutldpc_decode_quantized_device(lutldpc_decoder* h, int n_frames, const uint8_t* d_llr_cha,
+                                    const uint8_t* d_llr_msg, uint8_t* d_out_bits, int32_t* d_out_iters);
+/* lutldpc_decode_llr == LDPC_Code_LUT::decode(const vec& llr_in, bvec& syst_bits)
+ * (src/LDPC_Code_LUT.cpp:204-239): quant_nonlin front end (src/common.cpp:120-138) + lut_decode.
+ *   llr [n_frames][nvar] doubles;  out_bits [n_frames][nvar];  out_iters may be NULL. */
+int lutldpc_decode_llr(lutldpc_decoder* h, int n_frames, const double* llr, uint8_t* out_bits, int32_t* out_iters);
+int lutldpc_decode_llr_device(lutldpc_decoder* h, int n_frames, const double* d_llr, uint8_t* d_out_bits,
+                              int32_t* d_out_iters);
+/* front end only: quant_nonlin(llr, qb_Cha) and quant_nonlin(llr, qb_Msg) | Nq_Cha_2_Nq_Msg_map */
+int lutldpc_quantize(lutldpc_decoder* h, int n_frames, const double* llr, uint8_t* llr_cha, uint8_t* llr_msg);
+
+/* lut_decode with the reference's output_verbosity >= 2 message dumps for ONE frame of the batch
+ * (src/LDPC_Code_LUT.cpp:291-298,311-317,331-337): record r holds all num_edges messages as labels,
+ * kind/iter as in LUTLDPC_TRACE_*.  At most max_rec records are written. */
+int lutldpc_decode_quantized_traced(lutldpc_decoder* h, int n_frames, const uint8_t* llr_cha,
+                                    const uint8_t* llr_msg, uint8_t* out_bits, int32_t* out_iters,
+                                    int trace_frame, uint8_t* trace_msgs, int32_t* trace_kind,
+                                    int32_t* trace_iter, int max_rec, int32_t* n_rec);
+
+/* LDPC_Generator_Systematic::encode (itpp/itpp/comm/ldpc.cpp:1038): codeword = [u, P*u].
+ * info [n_frames][ninfo] -> codeword [n_frames][nvar]; LUTLDPC_ERR_STATE without a generator. */
+int lutldpc_encode(lutldpc_decoder* h, int n_frames, const uint8_t* info, uint8_t* codeword);
+/* syndrome_check(const bvec&), src/LDPC_Code_LUT.cpp:455-469: ok[f] = 1 iff H*bits_f == 0 */
+int lutldpc_syndrome_check(lutldpc_decoder* h, int n_frames, const uint8_t* bits, uint8_t* ok);
+
+/* ---- fused Monte-Carlo step == the frame loop of LDPC_BER_Sim::sim_snr_point
+ * (src/LDPC_BER_Sim.cpp:246-311): source -> encode -> BPSK -> AWGN -> LLR = 4x/N0 -> quantise ->
+ * lut_decode -> BERC/BLERC counting, all on the device; only the counters cross to the host. */
+typedef struct lutldpc_sim_params {
+  double snr_db;          /* Eb/N0 in dB; N0 = 10^(-snr/10)/rate, sigma^2 = N0/2 (:248-249) */
+  int64_t n_frames;       /* frames to simulate in this call */
+  uint64_t seed;          /* Philox4x32-10 key */
+  uint64_t first_frame;   /* global index of the first frame (Philox counter); disjoint ranges per GPU/call */
+  int32_t zero_codeword;  /* LDPC.zero_codeword; 0 needs a generator in the decoder */
+  int32_t batch_frames;   /* frames in flight per launch (0 = default) */
+} lutldpc_sim_params;
+
+#define LUTLDPC_ITER_HIST_MAX 256
+typedef struct lutldpc_sim_counters {
+  uint64_t frames, frame_errors;             /* BLERC ferc: blocks / block errors over the ninfo data bits */
+  uint64_t data_bits, data_bit_errors;       /* BERC berc_data */
+  uint64_t uncoded_bits, uncoded_bit_errors; /* BERC berc_uncoded (slicer on all nvar symbols) */
+  uint64_t sum_iters, decode_failures;       /* sum |lut_decode return|, # of negative returns */
+  uint64_t iter_hist[LUTLDPC_ITER_HIST_MAX]; /* histogram of |return| (clamped) */
+} lutldpc_sim_counters;
+/* counters are ADDED to *acc (so successive calls / ranks accumulate) */
+int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc);
+
+/* ---- timing aid for bench.py: device-time (ms) of the last decode/simulate call's kernels, measured
+ * with CUDA events on the handle's stream, and number of kernels it launched */
+int lutldpc_last_call_stats(const lutldpc_decoder* h, double* device_ms, int64_t* kernel_launches,
+                            int64_t* frame_iterations);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

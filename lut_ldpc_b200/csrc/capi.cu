@@ -1,0 +1,322 @@
+// C ABI (include/lutldpc.h) over the decoder object.  No torch types, no exceptions across the ABI.
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "decoder.hpp"
+
+using namespace lutldpc;
+
+static thread_local std::string g_create_error;
+
+#define CKH(call, where)                                   \
+  do {                                                     \
+    cudaError_t e_ = (call);                               \
+    if (e_ != cudaSuccess) return h->cuda_fail(e_, where); \
+  } while (0)
+
+extern "C" {
+
+int lutldpc_abi_version(void) { return LUTLDPC_ABI_VERSION; }
+
+const char* lutldpc_last_error(const lutldpc_decoder* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+static int finish_create(lutldpc_decoder* h, lutldpc_decoder** out) {
+  int rc = h->init_device();
+  if (rc != LUTLDPC_OK) {
+    g_create_error = h->err;
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return LUTLDPC_OK;
+}
+
+int lutldpc_create_from_bundle(const char* bundle_path, lutldpc_decoder** out) {
+  if (!bundle_path || !out) { g_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
+  *out = nullptr;
+  lutldpc_decoder* h = new (std::nothrow) lutldpc_decoder();
+  if (!h) { g_create_error = "out of memory"; return LUTLDPC_ERR_ARG; }
+  std::string err;
+  if (!load_bundle_file(bundle_path, h->m, err)) {
+    g_create_error = err;
+    delete h;
+    return LUTLDPC_ERR_MODEL;
+  }
+  return finish_create(h, out);
+}
+
+int lutldpc_create(const lutldpc_desc* d, lutldpc_decoder** out) {
+  if (!d || !out) { g_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
+  *out = nullptr;
+  if (!d->dv_vec || !d->dc_vec || !d->cn_msg_idx || !d->Nq_Msg || !d->reuse_vec || !d->qb_Cha || !d->var_tree_string ||
+      d->nvar <= 0 || d->nchk <= 0 || d->num_edges <= 0 || d->max_iters <= 0 || d->n_qb_Msg < 0 ||
+      (d->n_qb_Msg > 0 && !d->qb_Msg)) {
+    g_create_error = "lutldpc_desc: missing array or non-positive size";
+    return LUTLDPC_ERR_ARG;
+  }
+  lutldpc_decoder* h = new (std::nothrow) lutldpc_decoder();
+  if (!h) { g_create_error = "out of memory"; return LUTLDPC_ERR_ARG; }
+  DecoderModel& m = h->m;
+  m.nvar = d->nvar; m.nchk = d->nchk; m.nchk_lin_indep = d->nchk_lin_indep; m.num_edges = d->num_edges;
+  m.max_iters = d->max_iters; m.Nq_Cha = d->Nq_Cha; m.minLUT = d->min_lut != 0;
+  m.dv.assign(d->dv_vec, d->dv_vec + d->nvar);
+  m.dc.assign(d->dc_vec, d->dc_vec + d->nchk);
+  m.cn_msg_idx.assign(d->cn_msg_idx, d->cn_msg_idx + d->num_edges);
+  m.Nq_Msg.assign(d->Nq_Msg, d->Nq_Msg + d->max_iters);
+  m.reuse.assign(d->reuse_vec, d->reuse_vec + d->max_iters);
+  std::string err;
+  if (d->Nq_Cha < 2 || d->Nq_Cha > 16) err = "Nq_Cha out of range";
+  if (err.empty()) {
+    if (d->Nq_Cha_2_Nq_Msg_map) m.cha2msg.assign(d->Nq_Cha_2_Nq_Msg_map, d->Nq_Cha_2_Nq_Msg_map + d->Nq_Cha);
+    m.qb_Cha.assign(d->qb_Cha, d->qb_Cha + d->Nq_Cha - 1);
+    if (d->n_qb_Msg) m.qb_Msg.assign(d->qb_Msg, d->qb_Msg + d->n_qb_Msg);
+    if (!parse_tree_array(d->var_tree_string, d->var_tree_len, m.var_trees, err)) err = "var trees: " + err;
+  }
+  if (err.empty() && d->chk_tree_string && d->chk_tree_len) {
+    std::string e2;
+    if (!parse_tree_array(d->chk_tree_string, d->chk_tree_len, m.chk_trees, e2) && !m.minLUT) err = "chk trees: " + e2;
+  }
+  if (err.empty() && d->gen_parity && d->gen_rows > 0 && d->gen_cols > 0) {
+    m.gen_rows = d->gen_rows; m.gen_cols = d->gen_cols;
+    m.gen.assign(d->gen_parity, d->gen_parity + (size_t)d->gen_rows * d->gen_cols);
+  }
+  if (err.empty()) finalize_model(m, err);
+  if (!err.empty()) {
+    g_create_error = err;
+    delete h;
+    return LUTLDPC_ERR_MODEL;
+  }
+  return finish_create(h, out);
+}
+
+void lutldpc_destroy(lutldpc_decoder* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  delete h;
+}
+
+int lutldpc_get_info(const lutldpc_decoder* h, lutldpc_info* info) {
+  if (!h || !info) return LUTLDPC_ERR_ARG;
+  const DecoderModel& m = h->m;
+  memset(info, 0, sizeof *info);
+  info->nvar = m.nvar; info->nchk = m.nchk; info->nchk_lin_indep = m.nchk_lin_indep; info->ninfo = m.ninfo();
+  info->num_edges = m.num_edges; info->max_iters = h->max_iters; info->Nq_Cha = m.Nq_Cha; info->min_lut = m.minLUT;
+  info->has_gen = !m.gen.empty(); info->n_degree_classes = (int)h->vn_classes.size(); info->rate = m.rate();
+  int nvc = (int)h->vn_classes.size();
+  for (int c = 0; c < nvc; ++c) {  // first iteration slot is representative (shapes rarely change per slot)
+    info->lookups_per_frame_iter += h->var_progs[c].n_ops * h->vn_classes[c].n;
+    info->lookups_per_frame_iter_naive += h->var_progs[c].n_naive * h->vn_classes[c].n;
+  }
+  return LUTLDPC_OK;
+}
+
+int lutldpc_set_exit_conditions(lutldpc_decoder* h, int max_iters, int psc, int pisc) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  // the decision trees belong to the last designed iteration (dec_update_lut(.., max_iters-1, ..),
+  // src/LDPC_Code_LUT.cpp:342), so the iteration count is fixed by the design
+  if (max_iters != h->m.max_iters)
+    return h->fail(LUTLDPC_ERR_ARG, "max_iters must equal the number of designed iterations (" +
+                                        std::to_string(h->m.max_iters) + ")");
+  h->max_iters = max_iters; h->psc = psc != 0; h->pisc = pisc != 0;
+  return LUTLDPC_OK;
+}
+
+int lutldpc_set_initial_message_mode(lutldpc_decoder* h, int mode) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (mode != LUTLDPC_INIT_CONT && mode != LUTLDPC_INIT_QCHA) return h->fail(LUTLDPC_ERR_ARG, "unknown initial message mode");
+  if (mode == LUTLDPC_INIT_QCHA && h->m.cha2msg.empty()) return h->fail(LUTLDPC_ERR_STATE, "decoder has no Nq_Cha_2_Nq_Msg_map");
+  if (mode == LUTLDPC_INIT_CONT && (int)h->m.qb_Msg.size() != h->m.Nq_Msg[0] - 1)
+    return h->fail(LUTLDPC_ERR_STATE, "decoder has no message quantiser qb_Msg for continuous inputs");
+  h->init_mode = mode;
+  return LUTLDPC_OK;
+}
+
+int lutldpc_set_stream(lutldpc_decoder* h, void* cuda_stream) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  h->stream = (cudaStream_t)cuda_stream;
+  return LUTLDPC_OK;
+}
+
+int lutldpc_set_poll_interval(lutldpc_decoder* h, int every) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  h->poll_every = every < 0 ? 0 : every;
+  return LUTLDPC_OK;
+}
+
+// ------------------------------------------------------------------------------------ decode
+static int check_decode_args(lutldpc_decoder* h, int n_frames, const void* a, const void* b2, const void* c) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (n_frames < 0) return h->fail(LUTLDPC_ERR_ARG, "n_frames < 0");
+  if (n_frames > 0 && (!a || !b2 || !c)) return h->fail(LUTLDPC_ERR_ARG, "NULL buffer");
+  return LUTLDPC_OK;
+}
+
+int lutldpc_decode_quantized_device(lutldpc_decoder* h, int n_frames, const uint8_t* d_cha, const uint8_t* d_msg,
+                                    uint8_t* d_out_bits, int32_t* d_out_iters) {
+  int rc = check_decode_args(h, n_frames, d_cha, d_msg, d_out_bits);
+  if (rc) return rc;
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  const int N = h->m.nvar, maxb = h->max_batch_frames();
+  for (int f0 = 0; f0 < n_frames; f0 += maxb) {
+    int nf = std::min(maxb, n_frames - f0);
+    rc = h->run_batch(nf, d_cha + (size_t)f0 * N, d_msg + (size_t)f0 * N, nullptr);
+    if (rc) return rc;
+    CKH(launch_unpack(h->g, h->b, d_out_bits + (size_t)f0 * N, h->stream), "unpack");
+    if (d_out_iters)
+      CKH(cudaMemcpyAsync(d_out_iters + f0, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToDevice, h->stream), "iters copy");
+  }
+  return LUTLDPC_OK;
+}
+
+static int decode_host(lutldpc_decoder* h, int n_frames, const uint8_t* cha, const uint8_t* msg, const double* llr,
+                       uint8_t* out_bits, int32_t* out_iters, TraceSink* tr) {
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  const int N = h->m.nvar, maxb = tr ? n_frames : h->max_batch_frames();
+  cudaStream_t st = h->stream;
+  for (int f0 = 0; f0 < n_frames; f0 += maxb) {
+    int nf = std::min(maxb, n_frames - f0);
+    size_t cnt = (size_t)nf * N;
+    CKH(h->buf_lab_cha.ensure(cnt), "alloc labels");
+    CKH(h->buf_lab_msg.ensure(cnt), "alloc labels");
+    CKH(h->buf_out.ensure(cnt), "alloc out");
+    if (llr) {
+      CKH(h->buf_llr.ensure(cnt), "alloc llr");
+      CKH(cudaMemcpyAsync(h->buf_llr.p, llr + (size_t)f0 * N, cnt * 8, cudaMemcpyHostToDevice, st), "H2D llr");
+      CKH(launch_quantize(h->buf_llr.p, cnt, h->d_qb_cha.p, (int)h->m.qb_Cha.size(), h->d_qb_msg.p,
+                          (int)h->m.qb_Msg.size(), h->d_cha2msg.p, h->init_mode == LUTLDPC_INIT_QCHA,
+                          h->buf_lab_cha.p, h->buf_lab_msg.p, st), "quantize");
+    } else {
+      CKH(cudaMemcpyAsync(h->buf_lab_cha.p, cha + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, st), "H2D cha");
+      CKH(cudaMemcpyAsync(h->buf_lab_msg.p, msg + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, st), "H2D msg");
+    }
+    int rc = h->run_batch(nf, h->buf_lab_cha.p, h->buf_lab_msg.p, tr);
+    if (rc) return rc;
+    CKH(launch_unpack(h->g, h->b, h->buf_out.p, st), "unpack");
+    CKH(cudaMemcpyAsync(out_bits + (size_t)f0 * N, h->buf_out.p, cnt, cudaMemcpyDeviceToHost, st), "D2H bits");
+    if (out_iters)
+      CKH(cudaMemcpyAsync(out_iters + f0, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToHost, st), "D2H iters");
+    CKH(cudaStreamSynchronize(st), "sync");
+  }
+  return LUTLDPC_OK;
+}
+
+int lutldpc_decode_quantized(lutldpc_decoder* h, int n_frames, const uint8_t* cha, const uint8_t* msg,
+                             uint8_t* out_bits, int32_t* out_iters) {
+  int rc = check_decode_args(h, n_frames, cha, msg, out_bits);
+  if (rc) return rc;
+  return decode_host(h, n_frames, cha, msg, nullptr, out_bits, out_iters, nullptr);
+}
+
+int lutldpc_decode_quantized_traced(lutldpc_decoder* h, int n_frames, const uint8_t* cha, const uint8_t* msg,
+                                    uint8_t* out_bits, int32_t* out_iters, int trace_frame, uint8_t* trace_msgs,
+                                    int32_t* trace_kind, int32_t* trace_iter, int max_rec, int32_t* n_rec) {
+  int rc = check_decode_args(h, n_frames, cha, msg, out_bits);
+  if (rc) return rc;
+  if (trace_frame < 0 || trace_frame >= n_frames || !trace_msgs || !trace_kind || !trace_iter || !n_rec || max_rec < 0)
+    return h->fail(LUTLDPC_ERR_ARG, "bad trace arguments");
+  if (n_frames > h->max_batch_frames()) return h->fail(LUTLDPC_ERR_ARG, "traced decode is limited to one batch");
+  TraceSink tr;
+  tr.frame = trace_frame; tr.max_rec = max_rec; tr.msgs = trace_msgs; tr.kind = trace_kind; tr.iter = trace_iter;
+  rc = decode_host(h, n_frames, cha, msg, nullptr, out_bits, out_iters, &tr);
+  *n_rec = tr.n_rec;
+  return rc;
+}
+
+int lutldpc_decode_llr(lutldpc_decoder* h, int n_frames, const double* llr, uint8_t* out_bits, int32_t* out_iters) {
+  int rc = check_decode_args(h, n_frames, llr, llr, out_bits);
+  if (rc) return rc;
+  if (h->init_mode == LUTLDPC_INIT_CONT && (int)h->m.qb_Msg.size() != h->m.Nq_Msg[0] - 1)
+    return h->fail(LUTLDPC_ERR_STATE, "decoder has no message quantiser qb_Msg for continuous inputs");
+  return decode_host(h, n_frames, nullptr, nullptr, llr, out_bits, out_iters, nullptr);
+}
+
+int lutldpc_decode_llr_device(lutldpc_decoder* h, int n_frames, const double* d_llr, uint8_t* d_out_bits,
+                              int32_t* d_out_iters) {
+  int rc = check_decode_args(h, n_frames, d_llr, d_llr, d_out_bits);
+  if (rc) return rc;
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  const int N = h->m.nvar, maxb = h->max_batch_frames();
+  for (int f0 = 0; f0 < n_frames; f0 += maxb) {
+    int nf = std::min(maxb, n_frames - f0);
+    size_t cnt = (size_t)nf * N;
+    CKH(h->buf_lab_cha.ensure(cnt), "alloc labels");
+    CKH(h->buf_lab_msg.ensure(cnt), "alloc labels");
+    CKH(launch_quantize(d_llr + (size_t)f0 * N, cnt, h->d_qb_cha.p, (int)h->m.qb_Cha.size(), h->d_qb_msg.p,
+                        (int)h->m.qb_Msg.size(), h->d_cha2msg.p, h->init_mode == LUTLDPC_INIT_QCHA, h->buf_lab_cha.p,
+                        h->buf_lab_msg.p, h->stream), "quantize");
+    rc = h->run_batch(nf, h->buf_lab_cha.p, h->buf_lab_msg.p, nullptr);
+    if (rc) return rc;
+    CKH(launch_unpack(h->g, h->b, d_out_bits + (size_t)f0 * N, h->stream), "unpack");
+    if (d_out_iters)
+      CKH(cudaMemcpyAsync(d_out_iters + f0, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToDevice, h->stream), "iters copy");
+  }
+  return LUTLDPC_OK;
+}
+
+int lutldpc_quantize(lutldpc_decoder* h, int n_frames, const double* llr, uint8_t* cha, uint8_t* msg) {
+  int rc = check_decode_args(h, n_frames, llr, cha, msg);
+  if (rc) return rc;
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  size_t cnt = (size_t)n_frames * h->m.nvar;
+  if (!cnt) return LUTLDPC_OK;
+  cudaStream_t st = h->stream;
+  CKH(h->buf_llr.ensure(cnt), "alloc llr");
+  CKH(h->buf_lab_cha.ensure(cnt), "alloc labels");
+  CKH(h->buf_lab_msg.ensure(cnt), "alloc labels");
+  CKH(cudaMemcpyAsync(h->buf_llr.p, llr, cnt * 8, cudaMemcpyHostToDevice, st), "H2D llr");
+  CKH(launch_quantize(h->buf_llr.p, cnt, h->d_qb_cha.p, (int)h->m.qb_Cha.size(), h->d_qb_msg.p, (int)h->m.qb_Msg.size(),
+                      h->d_cha2msg.p, h->init_mode == LUTLDPC_INIT_QCHA, h->buf_lab_cha.p, h->buf_lab_msg.p, st), "quantize");
+  CKH(cudaMemcpyAsync(cha, h->buf_lab_cha.p, cnt, cudaMemcpyDeviceToHost, st), "D2H");
+  CKH(cudaMemcpyAsync(msg, h->buf_lab_msg.p, cnt, cudaMemcpyDeviceToHost, st), "D2H");
+  CKH(cudaStreamSynchronize(st), "sync");
+  return LUTLDPC_OK;
+}
+
+int lutldpc_syndrome_check(lutldpc_decoder* h, int n_frames, const uint8_t* bits, uint8_t* ok) {
+  int rc = check_decode_args(h, n_frames, bits, bits, ok);
+  if (rc) return rc;
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  const int N = h->m.nvar, maxb = h->max_batch_frames();
+  cudaStream_t st = h->stream;
+  for (int f0 = 0; f0 < n_frames; f0 += maxb) {
+    int nf = std::min(maxb, n_frames - f0);
+    size_t cnt = (size_t)nf * N;
+    if ((rc = h->ensure_batch(nf))) return rc;
+    CKH(h->buf_lab_cha.ensure(cnt), "alloc");
+    CKH(cudaMemcpyAsync(h->buf_lab_cha.p, bits + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, st), "H2D bits");
+    CKH(launch_reset_flags(h->b, st), "reset_flags");
+    CKH(launch_pack_bits(h->buf_lab_cha.p, h->g, h->b, st), "pack_bits");
+    CKH(launch_syndrome(h->g, h->b, st), "syndrome");
+    std::vector<uint32_t> sf(h->b.W);
+    CKH(cudaMemcpyAsync(sf.data(), h->b.syn_fail, sf.size() * 4, cudaMemcpyDeviceToHost, st), "D2H flags");
+    CKH(cudaStreamSynchronize(st), "sync");
+    for (int f = 0; f < nf; ++f) ok[f0 + f] = !((sf[f >> 3] >> (4 * (f & 7))) & 1);
+  }
+  return LUTLDPC_OK;
+}
+
+int lutldpc_last_call_stats(const lutldpc_decoder* h, double* device_ms, int64_t* kernel_launches,
+                            int64_t* frame_iterations) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (!h->have_stats) return LUTLDPC_ERR_STATE;
+  if (cudaEventSynchronize(h->ev1) != cudaSuccess) return LUTLDPC_ERR_CUDA;
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) return LUTLDPC_ERR_CUDA;
+  if (device_ms) *device_ms = ms;
+  if (kernel_launches) *kernel_launches = h->launches;
+  if (frame_iterations && h->stat_frame_iters >= 0) {
+    *frame_iterations = h->stat_frame_iters;
+  } else if (frame_iterations) {
+    std::vector<int32_t> it((size_t)h->last_frames);
+    if (cudaMemcpy(it.data(), h->b.iters, it.size() * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return LUTLDPC_ERR_CUDA;
+    int64_t s = 0;
+    for (int32_t v : it) s += v < 0 ? -v : v;
+    *frame_iterations = s;
+  }
+  return LUTLDPC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,288 @@
+// Decoder object: device set-up and the pass schedule of one batch.  See decoder.hpp.
+#include "decoder.hpp"
+
+#include <algorithm>
+#include <cstring>
+#include <map>
+
+using namespace lutldpc;
+
+#define CK(call, where)                         \
+  do {                                          \
+    cudaError_t e_ = (call);                    \
+    if (e_ != cudaSuccess) return cuda_fail(e_, where); \
+  } while (0)
+
+lutldpc_decoder::~lutldpc_decoder() {
+  if (h_active) cudaFreeHost(h_active);
+  if (ev0) cudaEventDestroy(ev0);
+  if (ev1) cudaEventDestroy(ev1);
+}
+
+int lutldpc_decoder::cuda_fail(cudaError_t e, const char* where) {
+  err = std::string("CUDA error in ") + where + ": " + cudaGetErrorString(e);
+  return LUTLDPC_ERR_CUDA;
+}
+
+int lutldpc_decoder::init_device() {
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(LUTLDPC_ERR_CUDA, "no CUDA device available (this library has no CPU fallback)");
+  CK(cudaGetDevice(&device), "cudaGetDevice");
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+  if (prop.major < 10)
+    return fail(LUTLDPC_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100 (kernels are built for sm_100a only)");
+  CK(configure_kernels(), "configure_kernels");
+  max_iters = m.max_iters;
+
+  CK(d_vn_edge0.upload(m.vn_edge0), "upload vn_edge0");
+  CK(d_dv.upload(m.dv), "upload dv");
+  CK(d_cn_start.upload(m.cn_start), "upload cn_start");
+  CK(d_cn_msg_idx.upload(m.cn_msg_idx), "upload cn_msg_idx");
+  CK(d_chk_equ_idx.upload(m.chk_equ_idx), "upload chk_equ_idx");
+  CK(d_qb_cha.upload(m.qb_Cha), "upload qb_Cha");
+  CK(d_qb_msg.upload(m.qb_Msg), "upload qb_Msg");
+  CK(d_cha2msg.upload(m.cha2msg), "upload cha2msg");
+  if (!m.gen.empty()) CK(d_gen.upload(m.gen), "upload generator");
+  g.vn_edge0 = d_vn_edge0.p; g.dv = d_dv.p; g.cn_start = d_cn_start.p; g.cn_msg_idx = d_cn_msg_idx.p;
+  g.chk_equ_idx = d_chk_equ_idx.p; g.nvar = m.nvar; g.nchk = m.nchk; g.num_edges = m.num_edges;
+  g.max_dc = *std::max_element(m.dc.begin(), m.dc.end());
+
+  // degree classes (set_trees: one tree per degree slot, src/LDPC_Code_LUT.cpp:128-139)
+  int nvc = m.var_trees.n_deg;
+  vn_classes = std::vector<NodeClass>(nvc);
+  {
+    std::vector<std::vector<int32_t>> lists(nvc);
+    for (int v = 0; v < m.nvar; ++v) lists[m.var_tree_idx_degree[v]].push_back(v);
+    for (int c = 0; c < nvc; ++c) {
+      vn_classes[c].degree = m.var_trees.at(0, c).num_leaves;
+      vn_classes[c].n = (int)lists[c].size();
+      CK(vn_classes[c].list.upload(lists[c]), "upload vn class list");
+    }
+  }
+  int ncc = m.minLUT ? 0 : m.chk_trees.n_deg;
+  cn_classes = std::vector<NodeClass>(ncc);
+  if (ncc) {
+    std::vector<std::vector<int32_t>> lists(ncc);
+    for (int c = 0; c < m.nchk; ++c) lists[m.chk_tree_idx_degree[c]].push_back(c);
+    for (int c = 0; c < ncc; ++c) {
+      cn_classes[c].degree = m.chk_trees.at(0, c).num_leaves + 1;
+      cn_classes[c].n = (int)lists[c].size();
+      CK(cn_classes[c].list.upload(lists[c]), "upload cn class list");
+    }
+  }
+
+  // compile every (iteration slot, degree class) tree into a node program
+  n_iter_slots = m.var_trees.n_iter;
+  std::vector<int> slot_first_iter(n_iter_slots, -1);
+  for (int ii = 0; ii < m.max_iters; ++ii) {
+    int t = m.var_tree_idx_iter[ii];
+    if (slot_first_iter[t] < 0) slot_first_iter[t] = ii;
+    else if (m.Nq_Msg[ii] != m.Nq_Msg[slot_first_iter[t]])
+      return fail(LUTLDPC_ERR_MODEL, "iterations that reuse a LUT slot must share the message resolution");
+  }
+  std::vector<uint8_t> blob;
+  auto add_prog = [&](const NodeProgram& p, ProgRef& r) {
+    std::vector<uint8_t> img = p.image();
+    r.off = blob.size();
+    r.bytes = (uint32_t)img.size();
+    r.n_slots = (uint32_t)p.n_slots;
+    r.n_in = (uint32_t)p.n_in;
+    r.n_ops = (int64_t)p.ops.size();
+    r.n_naive = p.n_lookups_naive;
+    blob.insert(blob.end(), img.begin(), img.end());
+  };
+  var_progs.assign((size_t)n_iter_slots * nvc, ProgRef());
+  for (int t = 0; t < n_iter_slots; ++t) {
+    bool dec = t == n_iter_slots - 1;  // the last slot holds the decision trees
+    int ii = slot_first_iter[t];
+    for (int c = 0; c < nvc; ++c) {
+      if (vn_classes[c].n == 0) continue;
+      const Tree& tr = m.var_trees.at(t, c);
+      NodeProgram p;
+      std::string perr;
+      if (!compile_program(tr, vn_classes[c].degree, dec ? PROG_DEC : PROG_VAR, m.Nq_Msg[ii], m.Nq_Cha, p, perr))
+        return fail(LUTLDPC_ERR_MODEL, "var tree (slot " + std::to_string(t) + ", degree " +
+                                           std::to_string(vn_classes[c].degree) + "): " + perr);
+      int want_out = dec ? 2 : m.Nq_Msg[std::min(ii + 1, m.max_iters - 1)];
+      if (!dec && tr.nodes[0].K != want_out)
+        return fail(LUTLDPC_ERR_MODEL, "var tree output alphabet does not match Nq_Msg of the next iteration");
+      if (dec && tr.nodes[0].K != 2) return fail(LUTLDPC_ERR_MODEL, "decision tree root must be binary");
+      add_prog(p, var_progs[(size_t)t * nvc + c]);
+    }
+  }
+  chk_progs.assign((size_t)n_iter_slots * ncc, ProgRef());
+  for (int t = 0; t < n_iter_slots && ncc; ++t) {
+    int ii = slot_first_iter[t];
+    for (int c = 0; c < ncc; ++c) {
+      if (cn_classes[c].n == 0) continue;
+      NodeProgram p;
+      std::string perr;
+      if (!compile_program(m.chk_trees.at(t, c), cn_classes[c].degree, PROG_CHK, m.Nq_Msg[ii], m.Nq_Cha, p, perr))
+        return fail(LUTLDPC_ERR_MODEL, "chk tree (slot " + std::to_string(t) + ", degree " +
+                                           std::to_string(cn_classes[c].degree) + "): " + perr);
+      if (m.chk_trees.at(t, c).nodes[0].K != m.Nq_Msg[ii])
+        return fail(LUTLDPC_ERR_MODEL, "chk tree output alphabet does not match Nq_Msg");
+      add_prog(p, chk_progs[(size_t)t * ncc + c]);
+    }
+  }
+  for (auto& r : var_progs)
+    if (r.bytes + (size_t)r.n_slots * kNodeThreads * 4 > 200 * 1024)
+      return fail(LUTLDPC_ERR_MODEL, "a node program (LUTs + value slots) exceeds the 200 KiB shared-memory budget");
+  for (auto& r : chk_progs)
+    if (r.bytes + (size_t)r.n_slots * kNodeThreads * 4 > 200 * 1024)
+      return fail(LUTLDPC_ERR_MODEL, "a node program (LUTs + value slots) exceeds the 200 KiB shared-memory budget");
+  CK(d_prog_blob.upload(blob), "upload node programs");
+  CK(cudaMallocHost((void**)&h_active, sizeof(uint32_t)), "cudaMallocHost");
+  CK(cudaEventCreate(&ev0), "cudaEventCreate");
+  CK(cudaEventCreate(&ev1), "cudaEventCreate");
+  return LUTLDPC_OK;
+}
+
+int lutldpc_decoder::max_batch_frames() const {
+  // bound the resident batch to ~16 GiB of message state
+  double per_frame = m.num_edges / 2.0 + m.nvar / 2.0 + m.nvar / 8.0 + 8;
+  long f = (long)(16.0 * 1024 * 1024 * 1024 / per_frame);
+  f = std::min(f, 65536L);
+  f = std::max(256L, f / 256 * 256);
+  return (int)f;
+}
+
+int lutldpc_decoder::ensure_batch(int n_frames) {
+  int W = ((n_frames + 255) / 256) * 32;
+  CK(buf_msgs.ensure((size_t)m.num_edges * W), "alloc msgs");
+  CK(buf_cha.ensure((size_t)m.nvar * W), "alloc cha");
+  CK(buf_hard.ensure((size_t)m.nvar * W), "alloc hard");
+  CK(buf_flags.ensure((size_t)4 * W + 32), "alloc flags");
+  CK(buf_iters.ensure((size_t)8 * W), "alloc iters");
+  b.msgs = buf_msgs.p; b.cha = buf_cha.p; b.hard = buf_hard.p;
+  b.done = buf_flags.p; b.vn_fail = buf_flags.p + W; b.cn_fail = buf_flags.p + 2 * W; b.syn_fail = buf_flags.p + 3 * W;
+  b.n_active = buf_flags.p + 4 * W;
+  b.iters = buf_iters.p;
+  b.W = W; b.F = n_frames;
+  return LUTLDPC_OK;
+}
+
+// LDPC_Code_LUT::lut_decode for a whole batch (src/LDPC_Code_LUT.cpp:259-353; control flow: SURVEY A.6).
+int lutldpc_decoder::begin_batch(int n_frames) {
+  int rc = ensure_batch(n_frames);
+  if (rc) return rc;
+  launches = 0;
+  CK(cudaEventRecord(ev0, stream), "event");
+  CK(launch_reset_flags(b, stream), "reset_flags"); ++launches;
+  return LUTLDPC_OK;
+}
+
+int lutldpc_decoder::run_batch(int n_frames, const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, TraceSink* tr) {
+  int rc = begin_batch(n_frames);
+  if (rc) return rc;
+  CK(launch_pack(d_cha_lab, d_msg_lab, g, b, m.Nq_Cha, m.Nq_Msg[0], stream), "pack"); ++launches;
+  return run_passes(tr);
+}
+
+// Expects cha / msgs / hard of the current batch to be initialised (pack or the channel kernel).
+int lutldpc_decoder::run_passes(TraceSink* tr) {
+  int rc = 0;
+  const int n_frames = b.F;
+  const int nvc = (int)vn_classes.size(), ncc = (int)cn_classes.size();
+  const uint8_t* blob = d_prog_blob.p;
+  cudaStream_t st = stream;
+  auto record = [&](int kind, int it, int Nq) -> int {
+    if (!tr || !tr->live || tr->n_rec >= tr->max_rec) return 0;
+    CK(buf_trace.ensure((size_t)m.num_edges), "alloc trace");
+    CK(launch_extract_frame(b, m.num_edges, tr->frame, Nq, buf_trace.p, st), "extract_frame");
+    CK(cudaMemcpyAsync(tr->msgs + (size_t)tr->n_rec * m.num_edges, buf_trace.p, m.num_edges, cudaMemcpyDeviceToHost, st),
+       "trace copy");
+    CK(cudaStreamSynchronize(st), "trace sync");
+    tr->kind[tr->n_rec] = kind;
+    tr->iter[tr->n_rec] = it;
+    ++tr->n_rec;
+    return 0;
+  };
+  auto traced_frame_done = [&](bool& done) -> int {  // after a finalize
+    int32_t it = 0;
+    uint32_t dw = 0;
+    CK(cudaMemcpyAsync(&dw, b.done + (tr->frame >> 3), 4, cudaMemcpyDeviceToHost, st), "trace done copy");
+    CK(cudaMemcpyAsync(&it, b.iters + tr->frame, 4, cudaMemcpyDeviceToHost, st), "trace iters copy");
+    CK(cudaStreamSynchronize(st), "trace sync");
+    done = (dw >> (4 * (tr->frame & 7))) & 1;
+    return 0;
+  };
+  auto poll = [&](bool& all_done) -> int {
+    all_done = false;
+    if (poll_every <= 0) return 0;
+    CK(cudaMemcpyAsync(h_active, b.n_active, 4, cudaMemcpyDeviceToHost, st), "poll copy");
+    CK(cudaStreamSynchronize(st), "poll sync");
+    all_done = *h_active == 0;
+    return 0;
+  };
+  bool all_done = false;
+  if (tr) tr->live = true;
+  if (pisc) {  // :277
+    CK(launch_syndrome(g, b, st), "syndrome"); ++launches;
+    CK(launch_finalize(FIN_INIT, 0, b, st), "finalize"); ++launches;
+    if (tr) { bool d; if ((rc = traced_frame_done(d))) return rc; if (d) tr->live = false; }
+    if ((rc = poll(all_done))) return rc;
+  }
+  if ((rc = record(LUTLDPC_TRACE_INIT, -1, m.Nq_Msg[0]))) return rc;
+  int polled = 0;
+  for (int ii = 0; ii < max_iters && !all_done; ++ii) {
+    const int t = m.var_tree_idx_iter[ii];
+    const int want = psc && ii > 0;
+    // check-node pass (:304-310); its sign parities complete the early-exit test of VN pass ii-1
+    if (m.minLUT) {
+      CK(launch_cn_minsum(g, b, code_bits(m.Nq_Msg[ii]), want, st), "cn_minsum"); ++launches;
+    } else {
+      for (int c = 0; c < ncc; ++c) {
+        const ProgRef& r = chk_progs[(size_t)t * ncc + c];
+        NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, cn_classes[c].list.p, cn_classes[c].n};
+        CK(launch_node(NODE_CHK, nl, g, b, want, st), "chk_lut"); ++launches;
+      }
+    }
+    if ((rc = record(LUTLDPC_TRACE_CN, ii, m.Nq_Msg[ii]))) return rc;
+    if (want) {  // psc: VN pass ii-1 unanimous and syndrome zero -> return ii (:327)
+      CK(launch_finalize(FIN_ITER, ii, b, st), "finalize"); ++launches;
+      if (tr && tr->live) {
+        bool d;
+        if ((rc = traced_frame_done(d))) return rc;
+        if (d) {  // the reference returned before dumping VN(ii-1) and never ran CN(ii)
+          tr->n_rec = std::max(0, tr->n_rec - 2);
+          tr->live = false;
+        }
+      }
+      if (poll_every > 0 && ++polled % poll_every == 0) {
+        if ((rc = poll(all_done))) return rc;
+        if (all_done) break;
+      }
+    }
+    if (ii != max_iters - 1) {  // variable-node pass (:320-325)
+      for (int c = 0; c < nvc; ++c) {
+        if (!vn_classes[c].n) continue;
+        const ProgRef& r = var_progs[(size_t)t * nvc + c];
+        NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
+        CK(launch_node(NODE_VAR, nl, g, b, psc, st), "var_lut"); ++launches;
+      }
+      if ((rc = record(LUTLDPC_TRACE_VN, ii, m.Nq_Msg[ii + 1]))) return rc;
+    } else if ((rc = record(LUTLDPC_TRACE_VN, ii, m.Nq_Msg[ii]))) {  // the reference dumps here too (:331)
+      return rc;
+    }
+  }
+  if (!all_done) {  // decision + final syndrome (:340-349)
+    const int t = m.var_tree_idx_iter[max_iters - 1];
+    for (int c = 0; c < nvc; ++c) {
+      if (!vn_classes[c].n) continue;
+      const ProgRef& r = var_progs[(size_t)t * nvc + c];
+      NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
+      CK(launch_node(NODE_DEC, nl, g, b, 0, st), "dec_lut"); ++launches;
+    }
+    CK(launch_syndrome(g, b, st), "syndrome"); ++launches;
+    CK(launch_finalize(FIN_LAST, max_iters, b, st), "finalize"); ++launches;
+  }
+  CK(cudaEventRecord(ev1, st), "event");
+  have_stats = true;
+  last_frames = n_frames;
+  stat_frame_iters = -1;
+  return LUTLDPC_OK;
+}

@@ -1,0 +1,104 @@
+// The object behind a lutldpc_decoder handle: host model, device copies, compiled node programs,
+// batch buffers and the pass schedule of LDPC_Code_LUT::lut_decode (src/LDPC_Code_LUT.cpp:259-353).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/lutldpc.h"
+#include "kernels.hpp"
+#include "model.hpp"
+
+namespace lutldpc {
+
+template <class T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  ~DevBuf() { release(); }
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  cudaError_t ensure(size_t count) {  // grow-only
+    if (count <= n) return cudaSuccess;
+    release();
+    cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+    if (e == cudaSuccess) n = count;
+    else p = nullptr;
+    return e;
+  }
+  cudaError_t upload(const std::vector<T>& v) {
+    cudaError_t e = ensure(v.size() ? v.size() : 1);
+    if (e != cudaSuccess || v.empty()) return e;
+    return cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+  }
+};
+
+struct ProgRef {
+  size_t off = 0;  // into the program blob
+  uint32_t bytes = 0, n_slots = 0, n_in = 0;
+  int64_t n_ops = 0, n_naive = 0;
+};
+
+struct NodeClass {  // all variable (or check) nodes of one degree slot
+  int degree = 0, n = 0;
+  DevBuf<int32_t> list;
+};
+
+struct TraceSink {
+  int frame = -1, max_rec = 0, n_rec = 0;
+  uint8_t* msgs = nullptr;
+  int32_t* kind = nullptr;
+  int32_t* iter = nullptr;
+  bool live = false;
+};
+
+}  // namespace lutldpc
+
+struct lutldpc_decoder {
+  lutldpc::DecoderModel m;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int max_iters = 0, psc = 1, pisc = 1, init_mode = LUTLDPC_INIT_CONT, poll_every = 1;
+  std::string err;
+
+  lutldpc::DevBuf<int32_t> d_vn_edge0, d_dv, d_cn_start, d_cn_msg_idx, d_chk_equ_idx, d_cha2msg;
+  lutldpc::DevBuf<double> d_qb_cha, d_qb_msg;
+  lutldpc::DevBuf<uint8_t> d_prog_blob, d_gen;
+  lutldpc::GraphArrays g;
+  std::vector<lutldpc::NodeClass> vn_classes, cn_classes;
+  std::vector<lutldpc::ProgRef> var_progs;  // [iter slot][vn class]; last slot = decision trees
+  std::vector<lutldpc::ProgRef> chk_progs;  // [iter slot][cn class]
+  int n_iter_slots = 0;
+
+  // batch state
+  lutldpc::BatchBuffers b;
+  lutldpc::DevBuf<uint32_t> buf_msgs, buf_cha, buf_flags;
+  lutldpc::DevBuf<uint8_t> buf_hard, buf_lab_cha, buf_lab_msg, buf_out, buf_trace;
+  lutldpc::DevBuf<int32_t> buf_iters;
+  lutldpc::DevBuf<double> buf_llr;
+  lutldpc::DevBuf<uint8_t> buf_cw;                 // transmitted codeword bits, [nvar][W] like hard
+  lutldpc::DevBuf<uint32_t> buf_ferr;              // per-word frame-error flags (byte form)
+  lutldpc::DevBuf<unsigned long long> buf_cnt;     // device image of lutldpc_sim_counters
+  uint32_t* h_active = nullptr;  // pinned
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool have_stats = false;
+  int64_t launches = 0, last_frames = 0, stat_frame_iters = -1;
+
+  ~lutldpc_decoder();
+  int fail(int code, const std::string& msg) { err = msg; return code; }
+  int cuda_fail(cudaError_t e, const char* where);
+  int init_device();          // uploads + program compilation
+  int ensure_batch(int n_frames);
+  // one batch, labels already on the device (frame-major); results left in b.hard / b.iters
+  int run_batch(int n_frames, const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, lutldpc::TraceSink* tr);
+  int begin_batch(int n_frames);            // buffers + flag reset + start event
+  int run_passes(lutldpc::TraceSink* tr);   // all iterations + decision on the initialised batch
+  int max_batch_frames() const;
+};

@@ -1,0 +1,515 @@
+// sm_100a kernels of the batched LUT-LDPC decoder.  One thread owns one 32-bit word = one edge (or
+// node) of 8 consecutive frames; a warp covers 32 consecutive words of a row, i.e. one 128-byte line
+// per edge, so every global access of the decode loop is a fully coalesced line.  Integer work only:
+// no tensor cores (this is table look-up and compare, not a contraction).
+#include "kernels.hpp"
+
+#include <cstdio>
+
+#include "core.cuh"
+
+namespace lutldpc {
+
+// ---------------------------------------------------------------------------------------------
+// bulk (TMA engine) global->shared copy of a contiguous, 16-byte aligned block, completion on an
+// mbarrier.  Used to stage a node program (op list + LUTs) and index slices into shared memory.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// Whole-CTA helper: thread 0 issues the copy (in <= 16 KiB pieces), everyone waits for the bytes.
+// `bytes` must be a multiple of 16.  The barrier is single-use (parity 0).
+__device__ __forceinline__ void stage_to_smem(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(bar, bytes);
+    const uint32_t kPiece = 16384;
+    for (uint32_t off = 0; off < bytes; off += kPiece) {
+      uint32_t n = bytes - off < kPiece ? bytes - off : kPiece;
+      bulk_g2s((char*)dst + off, (const char*)src + off, n, bar);
+    }
+  }
+  mbar_wait(bar, 0);
+}
+
+// label -> storage code for one byte label (model.hpp)
+__device__ __forceinline__ uint32_t lab2code(uint32_t m, int Nq, int q) {
+  uint32_t nz = Nq >> 1;
+  m = m < (uint32_t)Nq ? m : (uint32_t)Nq - 1;  // out-of-range labels are clamped, never indexed with
+  return m < nz ? ((1u << (q - 1)) | (nz - 1 - m)) : (m - nz);
+}
+
+// ---------------------------------------------------------------------------------------------
+// pack: frame-major byte labels -> frame-interleaved nibble words.
+//   LLRout = (LLRin_cha < Nq_Cha/2)                      src/LDPC_Code_LUT.cpp:275
+//   msgs[e] = LLRin_msg[v] for every edge e of v         src/LDPC_Code_LUT.cpp:284-289
+// Tile = 32 variable nodes x 256 frames through shared memory so that reads are 32-byte sectors of a
+// frame row and writes are 128-byte lines of an edge row.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_pack(const uint8_t* __restrict__ cha_lab, const uint8_t* __restrict__ msg_lab,
+                                              const int32_t* __restrict__ vn_edge0, int nvar, int F, int W,
+                                              int Nq_cha, int q_cha, int Nq_msg, int q_msg,
+                                              uint32_t* __restrict__ cha, uint32_t* __restrict__ msgs,
+                                              uint8_t* __restrict__ hard) {
+  __shared__ uint8_t tc[256][33];
+  __shared__ uint8_t tm[256][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int v0 = blockIdx.x * 32, w0 = blockIdx.y * 32, f0 = w0 * 8;
+  for (int i = 0; i < 32; ++i) {
+    int fl = ty + 8 * i, f = f0 + fl, v = v0 + tx;
+    uint8_t c = 0, m = 0;
+    bool in = f < F && v < nvar;
+    if (in) {
+      c = cha_lab[(size_t)f * nvar + v];
+      m = msg_lab[(size_t)f * nvar + v];
+    }
+    // padded frames carry the weakest positive label (code 0)
+    tc[fl][tx] = in ? (uint8_t)lab2code(c, Nq_cha, q_cha) : 0;
+    tm[fl][tx] = in ? (uint8_t)lab2code(m, Nq_msg, q_msg) : 0;
+  }
+  __syncthreads();
+  const int w = w0 + tx;
+  for (int vi = ty; vi < 32; vi += 8) {
+    int v = v0 + vi;
+    if (v >= nvar || w >= W) continue;
+    uint32_t cw = 0, mw = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      cw |= (uint32_t)tc[8 * tx + j][vi] << (4 * j);
+      mw |= (uint32_t)tm[8 * tx + j][vi] << (4 * j);
+    }
+    cha[(size_t)v * W + w] = cw;
+    hard[(size_t)v * W + w] = (uint8_t)nib_bits_to_byte(cw, q_cha - 1);
+    int e0 = vn_edge0[v], e1 = vn_edge0[v + 1];
+    for (int e = e0; e < e1; ++e) msgs[(size_t)e * W + w] = mw;
+  }
+}
+
+// bits [F][nvar] (0/1) -> hard[nvar][W]; used by the stand-alone syndrome check
+__global__ void __launch_bounds__(256) k_pack_bits(const uint8_t* __restrict__ bits, int nvar, int F, int W,
+                                                   uint8_t* __restrict__ hard) {
+  __shared__ uint8_t tb[256][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int v0 = blockIdx.x * 32, w0 = blockIdx.y * 32, f0 = w0 * 8;
+  for (int i = 0; i < 32; ++i) {
+    int fl = ty + 8 * i, f = f0 + fl, v = v0 + tx;
+    tb[fl][tx] = (f < F && v < nvar) ? (bits[(size_t)f * nvar + v] & 1) : 0;
+  }
+  __syncthreads();
+  const int w = w0 + tx;
+  for (int vi = ty; vi < 32; vi += 8) {
+    int v = v0 + vi;
+    if (v >= nvar || w >= W) continue;
+    uint32_t b = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) b |= (uint32_t)tb[8 * tx + j][vi] << j;
+    hard[(size_t)v * W + w] = (uint8_t)b;
+  }
+}
+
+// done = padding frames; fail flags cleared
+__global__ void k_reset_flags(uint32_t* done, uint32_t* vn_fail, uint32_t* cn_fail, uint32_t* syn_fail,
+                              int32_t* iters, uint32_t* n_active, int W, int F) {
+  int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w == 0) *n_active = (uint32_t)F;
+  if (w >= W) return;
+  uint32_t d = 0;
+  for (int j = 0; j < 8; ++j) {
+    int f = 8 * w + j;
+    if (f >= F) d |= 1u << (4 * j);
+    iters[f] = 0;
+  }
+  done[w] = d;
+  vn_fail[w] = 0;
+  cn_fail[w] = 0;
+  syn_fail[w] = 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// check-node pass, min-sum (LDPC_Code_LUT::chk_update_minsum, src/LDPC_Code_LUT.cpp:355-402).
+// Thread = (check, word).  The sign parity of the incoming messages doubles as the syndrome bit of
+// the previous variable-node pass (src/LDPC_Code_LUT.cpp:437-452: when every VN is unanimous, the
+// sign on each edge IS the tentative bit), so the early-termination syndrome costs no extra pass.
+// ---------------------------------------------------------------------------------------------
+template <int MAXDC>
+__global__ void __launch_bounds__(128) k_cn_minsum(const int32_t* __restrict__ cn_start,
+                                                   const int32_t* __restrict__ cn_msg_idx, int nchk, int W, int q,
+                                                   uint32_t* __restrict__ msgs, const uint32_t* __restrict__ done,
+                                                   uint32_t* __restrict__ cn_fail, int want_fail) {
+  const int c = blockIdx.x;
+  const int w = blockIdx.y * blockDim.x + threadIdx.x;
+  if (w >= W) return;
+  if (done[w] == kNibOnes) return;  // all 8 frames of this word have finished
+  const QMask qm = make_qmask(q);
+  const int s = cn_start[c], dc = cn_start[c + 1] - s;
+  const int32_t* idx = cn_msg_idx + s;
+  uint32_t x[MAXDC];
+#pragma unroll
+  for (int k = 0; k < MAXDC; ++k)
+    if (k < dc) x[k] = msgs[(size_t)idx[k] * W + w];
+  CnAcc a;
+  cn_init(a, x[0], x[1], qm);
+#pragma unroll
+  for (int k = 2; k < MAXDC; ++k)
+    if (k < dc) cn_accum(a, x[k], qm);
+#pragma unroll
+  for (int k = 0; k < MAXDC; ++k)
+    if (k < dc) msgs[(size_t)idx[k] * W + w] = cn_emit(a, x[k], qm);
+  if (want_fail) {
+    uint32_t f = (a.par >> qm.s) & kNibOnes;
+    if (f) atomicOr(&cn_fail[w], f);
+  }
+}
+
+// any degree (up to the reference's max_cnd = 200, src/LDPC_Code_LUT.hpp:363): second pass re-reads
+__global__ void __launch_bounds__(128) k_cn_minsum_any(const int32_t* __restrict__ cn_start,
+                                                       const int32_t* __restrict__ cn_msg_idx, int nchk, int W,
+                                                       int q, uint32_t* __restrict__ msgs,
+                                                       const uint32_t* __restrict__ done,
+                                                       uint32_t* __restrict__ cn_fail, int want_fail) {
+  const int c = blockIdx.x;
+  const int w = blockIdx.y * blockDim.x + threadIdx.x;
+  if (w >= W) return;
+  if (done[w] == kNibOnes) return;
+  const QMask qm = make_qmask(q);
+  const int s = cn_start[c], dc = cn_start[c + 1] - s;
+  const int32_t* idx = cn_msg_idx + s;
+  CnAcc a;
+  cn_init(a, msgs[(size_t)idx[0] * W + w], msgs[(size_t)idx[1] * W + w], qm);
+  for (int k = 2; k < dc; ++k) cn_accum(a, msgs[(size_t)idx[k] * W + w], qm);
+  for (int k = 0; k < dc; ++k) {
+    size_t o = (size_t)idx[k] * W + w;
+    msgs[o] = cn_emit(a, msgs[o], qm);
+  }
+  if (want_fail) {
+    uint32_t f = (a.par >> qm.s) & kNibOnes;
+    if (f) atomicOr(&cn_fail[w], f);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// LUT node pass: variable-node update (LUT_Tree::var_msg_update, src/LUT_Tree.cpp:774-790), final
+// decision (LUT_Tree::dec_update, :809-820) or LUT check-node update (LUT_Tree::chk_msg_update,
+// :792-807).  All nodes of one launch share a degree and therefore one straight-line node program
+// (model.hpp): the op list and its LUTs are staged into shared memory with one bulk copy, every
+// thread then runs the program for its 8 frames with the intermediate values in a private column of
+// shared memory (slot-major, so accesses are conflict-free).
+// ---------------------------------------------------------------------------------------------
+struct SmemVals {
+  uint32_t* base;  // this thread's column
+  __device__ __forceinline__ uint32_t get(int s) const { return base[s * kNodeThreads]; }
+  __device__ __forceinline__ void set(int s, uint32_t v) { base[s * kNodeThreads] = v; }
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(kNodeThreads) k_node(const uint8_t* __restrict__ prog, uint32_t prog_bytes,
+                                                        const int32_t* __restrict__ node_list, int n_nodes,
+                                                        int nodes_per_cta, const int32_t* __restrict__ start,
+                                                        const int32_t* __restrict__ cn_msg_idx, int W,
+                                                        uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
+                                                        uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
+                                                        uint32_t* __restrict__ fail, int want_flags) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ uint64_t bar;
+  stage_to_smem(smem, prog, prog_bytes, &bar);
+  const DevProgHeader* hdr = reinterpret_cast<const DevProgHeader*>(smem);
+  const DevOp* ops = reinterpret_cast<const DevOp*>(smem + hdr->ops_off);
+  const uint8_t* outs = smem + hdr->outs_off;
+  const uint8_t* tables = smem + hdr->tables_off;
+  const uint32_t n_ops = hdr->n_ops;
+  const int n_in = (int)hdr->n_in, n_out = (int)hdr->n_out;
+  SmemVals vals{reinterpret_cast<uint32_t*>(smem + prog_bytes) + threadIdx.x};
+
+  const int w = blockIdx.y * kNodeThreads + threadIdx.x;
+  if (w >= W) return;
+  const uint32_t dn = done[w];
+  if (dn == kNibOnes) return;
+  const uint32_t done_byte = nib_bits_to_byte(dn, 0);
+  const int so = (int)hdr->q_out - 1, si = (int)hdr->q_in - 1;
+  uint32_t failacc = 0;
+  const int i0 = blockIdx.x * nodes_per_cta;
+  const int i1 = min(i0 + nodes_per_cta, n_nodes);
+  for (int i = i0; i < i1; ++i) {
+    const int node = node_list[i];
+    const int s = start[node];
+    uint32_t par = 0;
+    for (int k = 0; k < n_in; ++k) {
+      const size_t row = MODE == NODE_CHK ? (size_t)cn_msg_idx[s + k] : (size_t)(s + k);
+      uint32_t x = msgs[row * W + w];
+      vals.set(k, x);
+      if (MODE == NODE_CHK) par ^= x;
+    }
+    if (MODE != NODE_CHK) vals.set(n_in, cha[(size_t)node * W + w]);
+    run_program(n_ops, ops, tables, vals);
+    if (MODE == NODE_VAR) {
+      uint32_t A = 0xFFFFFFFFu, O = 0, first = 0;
+      for (int ii = 0; ii < n_out; ++ii) {
+        uint32_t r = vals.get(outs[ii]);
+        msgs[(size_t)(s + ii) * W + w] = r;
+        A &= r;
+        O |= r;
+        if (ii == 0) first = r;
+      }
+      if (want_flags) {
+        failacc |= (A ^ O) >> so;  // some outgoing signs differ (src/LDPC_Code_LUT.cpp:441-447)
+        uint8_t* hp = hard + (size_t)node * W + w;
+        uint32_t nb = nib_bits_to_byte(first, so);
+        *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
+      }
+    } else if (MODE == NODE_CHK) {
+      for (int ii = 0; ii < n_out; ++ii)
+        msgs[(size_t)cn_msg_idx[s + ii] * W + w] = vals.get(outs[ii]);
+      failacc |= par >> si;
+    } else {  // NODE_DEC: bit = (root output < 1), root alphabet 2 -> the sign bit (src/LDPC_Code_LUT.cpp:342)
+      uint8_t* hp = hard + (size_t)node * W + w;
+      uint32_t nb = nib_bits_to_byte(vals.get(outs[0]), so);
+      *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
+    }
+  }
+  if (want_flags && MODE != NODE_DEC) {
+    failacc &= kNibOnes;
+    if (failacc) atomicOr(&fail[w], failacc);
+  }
+}
+
+// syndrome of the hard decisions (syndrome_check(const bvec&), src/LDPC_Code_LUT.cpp:455-469)
+__global__ void __launch_bounds__(128) k_syndrome(const int32_t* __restrict__ cn_start,
+                                                  const int32_t* __restrict__ chk_equ_idx, int W,
+                                                  const uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
+                                                  uint32_t* __restrict__ syn_fail) {
+  const int c = blockIdx.x;
+  const int w = blockIdx.y * blockDim.x + threadIdx.x;
+  if (w >= W) return;
+  if (done[w] == kNibOnes) return;
+  const int s = cn_start[c], e = cn_start[c + 1];
+  uint32_t x = 0;
+  for (int k = s; k < e; ++k) x ^= hard[(size_t)chk_equ_idx[k] * W + w];
+  if (x) atomicOr(&syn_fail[w], byte_to_nib_bits(x));
+}
+
+// Per-frame bookkeeping between passes (single CTA; W is at most a few thousand words).
+//   FIN_INIT  pisc: frames whose channel hard decision is a codeword return 0     (:277)
+//   FIN_ITER  psc : unanimous VNs + zero syndrome -> return `value` = ii+1        (:327)
+//   FIN_LAST  after the decision pass: +-max_iters                                (:346-349)
+__global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int W, uint32_t* done, uint32_t* vn_fail,
+                                                   uint32_t* cn_fail, uint32_t* syn_fail, int32_t* iters,
+                                                   uint32_t* n_active) {
+  __shared__ uint32_t red[32];
+  uint32_t cnt = 0;
+  for (int w = threadIdx.x; w < W; w += blockDim.x) {
+    uint32_t d = done[w], conv;
+    if (mode == FIN_INIT) {
+      conv = ~d & ~syn_fail[w] & kNibOnes;
+      syn_fail[w] = 0;
+    } else if (mode == FIN_ITER) {
+      conv = ~d & ~(vn_fail[w] | cn_fail[w]) & kNibOnes;
+      vn_fail[w] = 0;
+      cn_fail[w] = 0;
+    } else {
+      conv = ~d & kNibOnes;
+    }
+    if (conv) {
+      uint32_t sf = mode == FIN_LAST ? syn_fail[w] : 0;
+      for (int j = 0; j < 8; ++j)
+        if ((conv >> (4 * j)) & 1) iters[8 * w + j] = ((sf >> (4 * j)) & 1) ? -value : value;
+    }
+    if (mode == FIN_LAST) syn_fail[w] = 0;
+    d |= conv;
+    done[w] = d;
+    cnt += __popc(~d & kNibOnes);
+  }
+  for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = cnt;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    cnt = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0;
+    for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
+    if (threadIdx.x == 0) *n_active = cnt;
+  }
+}
+
+// hard[nvar][W] -> out_bits[F][nvar]
+__global__ void __launch_bounds__(256) k_unpack(const uint8_t* __restrict__ hard, int nvar, int F, int W,
+                                                uint8_t* __restrict__ out) {
+  __shared__ uint8_t t[32][36];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int v0 = blockIdx.x * 32, w0 = blockIdx.y * 32, f0 = w0 * 8;
+  for (int vi = ty; vi < 32; vi += 8) {
+    int v = v0 + vi, w = w0 + tx;
+    t[vi][tx] = (v < nvar && w < W) ? hard[(size_t)v * W + w] : 0;
+  }
+  __syncthreads();
+  for (int i = 0; i < 32; ++i) {
+    int fl = ty + 8 * i, f = f0 + fl, v = v0 + tx;
+    if (f < F && v < nvar) out[(size_t)f * nvar + v] = (t[tx][fl >> 3] >> (fl & 7)) & 1;
+  }
+}
+
+// all edge messages of one frame as reference labels (the verbosity>=2 dumps, :291-337)
+__global__ void k_extract_frame(const uint32_t* __restrict__ msgs, int num_edges, int W, int frame, int Nq, int q,
+                                uint8_t* __restrict__ out) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= num_edges) return;
+  uint32_t c = (msgs[(size_t)e * W + (frame >> 3)] >> (4 * (frame & 7))) & 0xF;
+  uint32_t sign = (c >> (q - 1)) & 1, mag = c & ((1u << (q - 1)) - 1), nz = Nq >> 1;
+  out[e] = (uint8_t)(sign ? nz - 1 - mag : nz + mag);
+}
+
+// quant_nonlin (src/common.cpp:120-138): number of leading thresholds with x > b[i]
+__device__ __forceinline__ int quant_nonlin_dev(double x, const double* __restrict__ b, int nb) {
+  int idx = 0;
+  for (int i = 0; i < nb; ++i) {
+    if (x > b[i]) ++idx;
+    else break;
+  }
+  return idx;
+}
+// front end of LDPC_Code_LUT::decode (src/LDPC_Code_LUT.cpp:207-221)
+__global__ void k_quantize(const double* __restrict__ llr, size_t n, const double* __restrict__ qb_cha, int n_qb_cha,
+                           const double* __restrict__ qb_msg, int n_qb_msg, const int32_t* __restrict__ cha2msg,
+                           int use_map, uint8_t* __restrict__ cha_lab, uint8_t* __restrict__ msg_lab) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double x = llr[i];
+  int c = quant_nonlin_dev(x, qb_cha, n_qb_cha);
+  cha_lab[i] = (uint8_t)c;
+  msg_lab[i] = (uint8_t)(use_map ? cha2msg[c] : quant_nonlin_dev(x, qb_msg, n_qb_msg));
+}
+
+// ---------------------------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------------------------
+static constexpr int kMaxNodeSmem = 200 * 1024;
+
+cudaError_t configure_kernels() {
+  cudaError_t e;
+  e = cudaFuncSetAttribute(k_node<NODE_VAR>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxNodeSmem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k_node<NODE_DEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxNodeSmem);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(k_node<NODE_CHK>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxNodeSmem);
+}
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+cudaError_t launch_pack(const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, const GraphArrays& g,
+                        const BatchBuffers& b, int Nq_cha, int Nq_msg, cudaStream_t st) {
+  dim3 grid(cdiv(g.nvar, 32), cdiv(b.W, 32));
+  k_pack<<<grid, 256, 0, st>>>(d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha),
+                               Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pack_bits(const uint8_t* d_bits, const GraphArrays& g, const BatchBuffers& b, cudaStream_t st) {
+  dim3 grid(cdiv(g.nvar, 32), cdiv(b.W, 32));
+  k_pack_bits<<<grid, 256, 0, st>>>(d_bits, g.nvar, b.F, b.W, b.hard);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_reset_flags(const BatchBuffers& b, cudaStream_t st) {
+  k_reset_flags<<<cdiv(b.W, 128), 128, 0, st>>>(b.done, b.vn_fail, b.cn_fail, b.syn_fail, b.iters, b.n_active, b.W,
+                                                 b.F);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_cn_minsum(const GraphArrays& g, const BatchBuffers& b, int q, int want_fail, cudaStream_t st) {
+  dim3 grid(g.nchk, cdiv(b.W, 128));
+#define CN_ARGS g.cn_start, g.cn_msg_idx, g.nchk, b.W, q, b.msgs, b.done, b.cn_fail, want_fail
+  if (g.max_dc <= 8) k_cn_minsum<8><<<grid, 128, 0, st>>>(CN_ARGS);
+  else if (g.max_dc <= 12) k_cn_minsum<12><<<grid, 128, 0, st>>>(CN_ARGS);
+  else if (g.max_dc <= 16) k_cn_minsum<16><<<grid, 128, 0, st>>>(CN_ARGS);
+  else if (g.max_dc <= 32) k_cn_minsum<32><<<grid, 128, 0, st>>>(CN_ARGS);
+  else k_cn_minsum_any<<<grid, 128, 0, st>>>(CN_ARGS);
+#undef CN_ARGS
+  return cudaGetLastError();
+}
+
+cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& g, const BatchBuffers& b,
+                        int want_flags, cudaStream_t st) {
+  if (nl.n_nodes == 0) return cudaSuccess;
+  size_t smem = (size_t)nl.prog_bytes + (size_t)nl.n_slots * kNodeThreads * sizeof(uint32_t);
+  if (smem > (size_t)kMaxNodeSmem) return cudaErrorInvalidValue;
+  int ycols = cdiv(b.W, kNodeThreads);
+  // enough CTAs to fill 148 SMs several times over, few enough that the program staging amortises
+  int per = (int)(((long long)nl.n_nodes * ycols) / (148 * 24));
+  per = per < 1 ? 1 : (per > 32 ? 32 : per);
+  dim3 grid(cdiv(nl.n_nodes, per), ycols);
+  uint32_t* fail = mode == NODE_CHK ? b.cn_fail : b.vn_fail;
+  const int32_t* start = mode == NODE_CHK ? g.cn_start : g.vn_edge0;
+#define NODE_ARGS nl.prog, nl.prog_bytes, nl.node_list, nl.n_nodes, per, start, g.cn_msg_idx, b.W, b.msgs, b.cha, \
+                  b.hard, b.done, fail, want_flags
+  if (mode == NODE_VAR) k_node<NODE_VAR><<<grid, kNodeThreads, smem, st>>>(NODE_ARGS);
+  else if (mode == NODE_DEC) k_node<NODE_DEC><<<grid, kNodeThreads, smem, st>>>(NODE_ARGS);
+  else k_node<NODE_CHK><<<grid, kNodeThreads, smem, st>>>(NODE_ARGS);
+#undef NODE_ARGS
+  return cudaGetLastError();
+}
+
+cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st) {
+  dim3 grid(g.nchk, cdiv(b.W, 128));
+  k_syndrome<<<grid, 128, 0, st>>>(g.cn_start, g.chk_equ_idx, b.W, b.hard, b.done, b.syn_fail);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b, cudaStream_t st) {
+  k_finalize<<<1, 1024, 0, st>>>((int)mode, value, b.W, b.done, b.vn_fail, b.cn_fail, b.syn_fail, b.iters,
+                                 b.n_active);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_bits, cudaStream_t st) {
+  dim3 grid(cdiv(g.nvar, 32), cdiv(b.W, 32));
+  k_unpack<<<grid, 256, 0, st>>>(b.hard, g.nvar, b.F, b.W, d_out_bits);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_extract_frame(const BatchBuffers& b, int num_edges, int frame, int Nq, uint8_t* d_out,
+                                 cudaStream_t st) {
+  k_extract_frame<<<cdiv(num_edges, 256), 256, 0, st>>>(b.msgs, num_edges, b.W, frame, Nq, code_bits(Nq), d_out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_quantize(const double* d_llr, size_t n, const double* d_qb_cha, int n_qb_cha,
+                            const double* d_qb_msg, int n_qb_msg, const int32_t* d_cha2msg, int use_map,
+                            uint8_t* d_cha_lab, uint8_t* d_msg_lab, cudaStream_t st) {
+  unsigned blocks = (unsigned)((n + 255) / 256);
+  k_quantize<<<blocks, 256, 0, st>>>(d_llr, n, d_qb_cha, n_qb_cha, d_qb_msg, n_qb_msg, d_cha2msg, use_map, d_cha_lab,
+                                     d_msg_lab);
+  return cudaGetLastError();
+}
+
+}  // namespace lutldpc

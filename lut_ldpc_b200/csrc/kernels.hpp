@@ -1,0 +1,70 @@
+// Launch interface between the C-ABI object (capi.cu) and the sm_100a kernels (kernels.cu).
+// HBM layout of one batch of F frames (W = words per row, 8 frames per 32-bit word, W % 32 == 0):
+//   msgs  [num_edges][W] u32   edge messages, edge-major (reference edge order), frames interleaved
+//   cha   [nvar][W]      u32   channel labels (storage code)
+//   hard  [nvar][W]      u8    hard decisions, bit j of byte (v,w) = frame 8w+j
+//   done / vn_fail / cn_fail / syn_fail [W] u32   per-frame flags at bit 0 of each nibble
+//   iters [8W] i32             lut_decode return value per frame
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+namespace lutldpc {
+
+constexpr int kNodeThreads = 128;  // word columns per CTA of the node kernels
+
+struct BatchBuffers {
+  uint32_t* msgs = nullptr;
+  uint32_t* cha = nullptr;
+  uint8_t* hard = nullptr;
+  uint32_t* done = nullptr;
+  uint32_t* vn_fail = nullptr;
+  uint32_t* cn_fail = nullptr;
+  uint32_t* syn_fail = nullptr;
+  int32_t* iters = nullptr;
+  uint32_t* n_active = nullptr;  // device counter written by finalize
+  int W = 0;                     // words per row
+  int F = 0;                     // real frames (<= 8W)
+};
+
+struct GraphArrays {  // device copies of the flattened graph
+  const int32_t* vn_edge0 = nullptr;   // [nvar+1]
+  const int32_t* dv = nullptr;         // [nvar]
+  const int32_t* cn_start = nullptr;   // [nchk+1]
+  const int32_t* cn_msg_idx = nullptr; // [E]
+  const int32_t* chk_equ_idx = nullptr;// [E]
+  int nvar = 0, nchk = 0, num_edges = 0, max_dc = 0;
+};
+
+struct NodeLaunch {       // one degree class of one pass
+  const uint8_t* prog = nullptr;   // device image: DevProgHeader | ops | outs | tables
+  uint32_t prog_bytes = 0, n_slots = 0, n_in = 0;
+  const int32_t* node_list = nullptr;  // [n_nodes] VN (or check) indices of this class
+  int n_nodes = 0;
+};
+
+enum NodeMode { NODE_VAR = 0, NODE_DEC = 1, NODE_CHK = 2 };
+enum FinalizeMode { FIN_INIT = 0, FIN_ITER = 1, FIN_LAST = 2 };
+
+// pack: frame-major labels -> cha/msgs/hard; q_cha/q_msg = code widths; Nq_* = alphabets
+cudaError_t launch_pack(const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, const GraphArrays& g,
+                        const BatchBuffers& b, int Nq_cha, int Nq_msg, cudaStream_t st);
+cudaError_t launch_reset_flags(const BatchBuffers& b, cudaStream_t st);
+cudaError_t launch_cn_minsum(const GraphArrays& g, const BatchBuffers& b, int q, int want_fail, cudaStream_t st);
+cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& g, const BatchBuffers& b,
+                        int want_flags, cudaStream_t st);
+cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st);
+cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b, cudaStream_t st);
+cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_bits, cudaStream_t st);
+cudaError_t launch_extract_frame(const BatchBuffers& b, int num_edges, int frame, int Nq, uint8_t* d_out,
+                                 cudaStream_t st);
+// quant_nonlin front end: llr [F][nvar] f64 -> labels
+cudaError_t launch_quantize(const double* d_llr, size_t n, const double* d_qb_cha, int n_qb_cha,
+                            const double* d_qb_msg, int n_qb_msg, const int32_t* d_cha2msg, int use_map,
+                            uint8_t* d_cha_lab, uint8_t* d_msg_lab, cudaStream_t st);
+// hard-bit pack for syndrome_check on caller-supplied words: bits [F][nvar] -> hard
+cudaError_t launch_pack_bits(const uint8_t* d_bits, const GraphArrays& g, const BatchBuffers& b, cudaStream_t st);
+cudaError_t configure_kernels();  // opt-in shared memory sizes; call once per device
+
+}  // namespace lutldpc

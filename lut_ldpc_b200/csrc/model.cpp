@@ -217,3 +217,267 @@ int code_to_label(int c, int Nq) {
   if (mag >= nz || c >= (1 << q)) return -1;
   return sign ? nz - 1 - mag : nz + mag;
 }
+
+// ------------------------------------------------------------------ node-program compiler
+namespace {
+
+struct RawOp {
+  int node;
+  std::vector<int> in;  // value ids
+  int out;              // value id
+};
+
+struct Compiler {
+  const Tree& t;
+  ProgMode mode;
+  std::vector<int> val_A;  // label alphabet of every value id
+  std::map<std::vector<int>, int> memo;
+  std::vector<RawOp> ops;
+  int naive = 0;
+  std::string err;
+
+  bool is_leaf(const TreeNode& nd) const {
+    // var/dec trees: a leaf of either type consumes the next input (src/LUT_Tree.cpp:403-407);
+    // check trees: only MSG leaves exist (src/LUT_Tree.cpp:421-425)
+    return mode == PROG_CHK ? nd.type == NODE_MSG : (nd.type == NODE_MSG || nd.type == NODE_CHA);
+  }
+  int eval(int n, const std::vector<int>& seq, size_t& pos) {
+    const TreeNode& nd = t.nodes[n];
+    if (is_leaf(nd)) {
+      if (pos >= seq.size()) { err = "tree consumes more inputs than the node degree provides"; return -1; }
+      return seq[pos++];
+    }
+    if (nd.child.empty()) { err = "inner tree node without children"; return -1; }
+    if ((int)nd.child.size() > kMaxOpInputs) { err = "tree node with more than 16 inputs"; return -1; }
+    std::vector<int> key;
+    key.push_back(n);
+    for (int ch : nd.child) {
+      int v = eval(ch, seq, pos);
+      if (v < 0) return -1;
+      key.push_back(v);
+    }
+    ++naive;
+    auto it = memo.find(key);
+    if (it != memo.end()) return it->second;
+    int id = (int)val_A.size();
+    val_A.push_back(nd.K);
+    RawOp op;
+    op.node = n;
+    op.in.assign(key.begin() + 1, key.end());
+    op.out = id;
+    ops.push_back(op);
+    memo[key] = id;
+    return id;
+  }
+};
+
+struct BuiltTable {
+  std::vector<uint8_t> bytes;
+  std::vector<int> q, sh;
+  int idx_bits = 0, q_out = 0;
+  bool sym = false;
+};
+
+// Re-indexes one node's Q table from the reference's mixed-radix label domain
+// (label = sum base_k*child_k, base_{k+1} = base_k*K_k, src/LUT_Tree.cpp:409-417) into the
+// storage-code domain (index = concatenated sign/magnitude codes).
+bool build_var_table(const Tree& t, int n, const std::vector<int>& A, BuiltTable& bt, std::string& err) {
+  const TreeNode& nd = t.nodes[n];
+  int nin = (int)A.size(), B = 0;
+  bt.q.resize(nin); bt.sh.resize(nin);
+  for (int k = 0; k < nin; ++k) { bt.q[k] = code_bits(A[k]); bt.sh[k] = B; B += bt.q[k]; }
+  if (B > 17) { err = "LUT node index wider than 17 bits is not supported"; return false; }
+  if (nd.K < 2 || nd.K > 16) { err = "LUT node output alphabet out of range"; return false; }
+  bt.q_out = code_bits(nd.K);
+  int qlen = (int)nd.Q.size();
+  size_t full = (size_t)1 << B;
+  std::vector<int> T(full, -1);
+  for (size_t idx = 0; idx < full; ++idx) {
+    long label = 0, base = 1;
+    bool valid = true;
+    for (int k = 0; k < nin; ++k) {
+      int code = (int)((idx >> bt.sh[k]) & ((1u << bt.q[k]) - 1));
+      int m = code_to_label(code, A[k]);
+      if (m < 0) { valid = false; break; }
+      label += base * m;
+      base *= t.nodes[nd.child[k]].K;
+    }
+    if (!valid) continue;
+    if (label >= 2L * qlen) {
+      err = "a tree leaf is fed a wider alphabet than its LUT was designed for (label outside the table)";
+      return false;
+    }
+    int r = label < qlen ? nd.Q[label] : nd.K - 1 - nd.Q[2 * qlen - 1 - label];  // src/LUT_Tree.cpp:414-417
+    if (r < 0 || r >= nd.K) { err = "LUT entry outside the node's output alphabet"; return false; }
+    T[idx] = label_to_code(r, nd.K);
+  }
+  // symmetry: flipping every input's sign flips the output's sign
+  size_t F = 0;
+  for (int k = 0; k < nin; ++k) F |= (size_t)1 << (bt.sh[k] + bt.q[k] - 1);
+  int Hout = 1 << (bt.q_out - 1);
+  bool sym = true;
+  for (size_t idx = 0; idx < full && sym; ++idx) {
+    int a = T[idx], b = T[idx ^ F];
+    if ((a < 0) != (b < 0) || (a >= 0 && b != (a ^ Hout))) sym = false;
+  }
+  bt.sym = sym;
+  bt.idx_bits = sym ? B - 1 : B;
+  if (bt.idx_bits > 16) { err = "LUT node index wider than 16 bits is not supported"; return false; }
+  size_t n_ent = (size_t)1 << bt.idx_bits;
+  bt.bytes.resize(n_ent);
+  for (size_t idx = 0; idx < n_ent; ++idx) bt.bytes[idx] = (uint8_t)(T[idx] < 0 ? 0 : T[idx]);
+  return true;
+}
+
+// Check-tree node (src/LUT_Tree.cpp:427-444): index from the magnitudes, entry = value for parity 1.
+bool build_chk_table(const Tree& t, int n, const std::vector<int>& A, BuiltTable& bt, std::string& err) {
+  const TreeNode& nd = t.nodes[n];
+  int nin = (int)A.size(), B = 0;
+  bt.q.resize(nin); bt.sh.resize(nin);
+  for (int k = 0; k < nin; ++k) { bt.q[k] = code_bits(A[k]); bt.sh[k] = B; B += bt.q[k] - 1; }
+  if (B > 16) { err = "check LUT node index wider than 16 bits is not supported"; return false; }
+  if (nd.K < 2 || nd.K > 16) { err = "LUT node output alphabet out of range"; return false; }
+  bt.q_out = code_bits(nd.K);
+  bt.idx_bits = B;
+  bt.sym = false;
+  int qlen = (int)nd.Q.size();
+  size_t n_ent = (size_t)1 << B;
+  bt.bytes.assign(n_ent, 0);
+  for (size_t idx = 0; idx < n_ent; ++idx) {
+    long label = 0, base = 1;
+    bool valid = true;
+    for (int k = 0; k < nin; ++k) {
+      int mag = (int)((idx >> bt.sh[k]) & ((1u << (bt.q[k] - 1)) - 1));
+      if (mag >= A[k] / 2) { valid = false; break; }
+      label += base * mag;
+      base *= t.nodes[nd.child[k]].K / 2;
+    }
+    if (!valid) continue;
+    if (label >= qlen) { err = "check LUT label outside the table"; return false; }
+    int r = nd.Q[label];
+    if (r < 0 || r >= nd.K) { err = "LUT entry outside the node's output alphabet"; return false; }
+    bt.bytes[idx] = (uint8_t)label_to_code(r, nd.K);
+  }
+  return true;
+}
+
+}  // namespace
+
+bool compile_program(const Tree& t, int deg, ProgMode mode, int Nq_in, int Nq_cha, NodeProgram& out,
+                     std::string& err) {
+  out = NodeProgram();
+  Compiler c{t, mode};
+  bool has_cha = mode != PROG_CHK;
+  int n_in = deg;
+  for (int k = 0; k < n_in; ++k) c.val_A.push_back(Nq_in);
+  if (has_cha) c.val_A.push_back(Nq_cha);
+  int n_inputs = n_in + (has_cha ? 1 : 0);
+  int n_out = mode == PROG_DEC ? 1 : deg;
+  std::vector<int> outs(n_out);
+  for (int ii = 0; ii < n_out; ++ii) {
+    std::vector<int> seq;
+    for (int k = 0; k < n_in; ++k)
+      if (mode == PROG_DEC || k != ii) seq.push_back(k);
+    if (has_cha) seq.push_back(n_in);
+    size_t pos = 0;
+    int v = c.eval(0, seq, pos);
+    if (v < 0) { err = c.err; return false; }
+    if (pos != seq.size()) { err = "tree leaf count does not match the node degree"; return false; }
+    outs[ii] = v;
+  }
+  // tables (shared between ops of the same node fed the same alphabets)
+  std::map<std::vector<int>, std::pair<uint32_t, BuiltTable>> tables;
+  out.ops.resize(c.ops.size());
+  for (size_t i = 0; i < c.ops.size(); ++i) {
+    const RawOp& ro = c.ops[i];
+    std::vector<int> key{ro.node}, A;
+    for (int v : ro.in) { A.push_back(c.val_A[v]); key.push_back(c.val_A[v]); }
+    auto it = tables.find(key);
+    if (it == tables.end()) {
+      BuiltTable bt;
+      bool ok = mode == PROG_CHK ? build_chk_table(t, ro.node, A, bt, err) : build_var_table(t, ro.node, A, bt, err);
+      if (!ok) return false;
+      size_t off = (out.tables.size() + 127) & ~(size_t)127;  // a 128-entry table spans each bank exactly once
+      out.tables.resize(off + bt.bytes.size(), 0);
+      memcpy(out.tables.data() + off, bt.bytes.data(), bt.bytes.size());
+      it = tables.emplace(key, std::make_pair((uint32_t)off, std::move(bt))).first;
+    }
+    const BuiltTable& bt = it->second.second;
+    DevOp& d = out.ops[i];
+    memset(&d, 0, sizeof d);
+    d.table_off = it->second.first;
+    d.n_in = (uint8_t)ro.in.size();
+    d.kind = bt.idx_bits <= 8 ? OP_NARROW : OP_WIDE;
+    d.q_out = (uint8_t)bt.q_out;
+    d.sym = bt.sym;
+    d.chk = mode == PROG_CHK;
+    d.idx_bits = (uint8_t)bt.idx_bits;
+    for (size_t k = 0; k < ro.in.size(); ++k) { d.q[k] = (uint8_t)bt.q[k]; d.sh[k] = (uint8_t)bt.sh[k]; }
+  }
+  // slot allocation: inputs own slots [0, n_inputs); outputs stay live to the end
+  int n_vals = (int)c.val_A.size();
+  std::vector<int> last_use(n_vals, -1), slot(n_vals, -1);
+  for (size_t i = 0; i < c.ops.size(); ++i)
+    for (int v : c.ops[i].in) last_use[v] = (int)i;
+  for (int v : outs) last_use[v] = 1 << 30;
+  for (int v = 0; v < n_inputs; ++v) slot[v] = v;
+  std::vector<int> free_slots;
+  int n_slots = n_inputs;
+  for (size_t i = 0; i < c.ops.size(); ++i) {
+    const RawOp& ro = c.ops[i];
+    // the destination may not alias an input of the same op (the kernel reads all inputs first, but
+    // keeping them distinct costs nothing)
+    int s;
+    if (!free_slots.empty()) { s = free_slots.back(); free_slots.pop_back(); }
+    else s = n_slots++;
+    slot[ro.out] = s;
+    for (size_t k = 0; k < ro.in.size(); ++k) {
+      int v = ro.in[k];
+      bool dup = false;
+      for (size_t j = 0; j < k; ++j) dup |= ro.in[j] == v;
+      if (!dup && v >= n_inputs && last_use[v] == (int)i) free_slots.push_back(slot[v]);
+    }
+    if (last_use[ro.out] < 0) free_slots.push_back(s);  // dead value (cannot happen with memoised eval)
+  }
+  if (n_slots > 255) { err = "node program needs more than 255 value slots"; return false; }
+  for (size_t i = 0; i < c.ops.size(); ++i) {
+    out.ops[i].out_slot = (uint8_t)slot[c.ops[i].out];
+    for (size_t k = 0; k < c.ops[i].in.size(); ++k) out.ops[i].in_slot[k] = (uint8_t)slot[c.ops[i].in[k]];
+  }
+  out.out_slot.resize(n_out);
+  for (int ii = 0; ii < n_out; ++ii) out.out_slot[ii] = (uint8_t)slot[outs[ii]];
+  out.n_in = n_in;
+  out.n_out = n_out;
+  out.n_slots = n_slots;
+  out.has_cha = has_cha;
+  out.n_lookups_naive = c.naive;
+  out.q_in = code_bits(Nq_in);
+  out.q_out = code_bits(t.nodes[0].K);
+  return true;
+}
+
+std::vector<uint8_t> NodeProgram::image() const {
+  auto al = [](size_t x) { return (x + 127) & ~(size_t)127; };
+  DevProgHeader h;
+  memset(&h, 0, sizeof h);
+  h.n_ops = (uint32_t)ops.size();
+  h.n_slots = (uint32_t)n_slots;
+  h.n_in = (uint32_t)n_in;
+  h.n_out = (uint32_t)n_out;
+  h.ops_off = (uint32_t)sizeof(DevProgHeader);
+  h.outs_off = (uint32_t)(h.ops_off + ops.size() * sizeof(DevOp));
+  h.tables_off = (uint32_t)al(h.outs_off + out_slot.size());
+  h.table_bytes = (uint32_t)tables.size();
+  h.total_bytes = (uint32_t)al(h.tables_off + tables.size());
+  h.has_cha = has_cha;
+  h.q_in = (uint32_t)q_in;
+  h.q_out = (uint32_t)q_out;
+  std::vector<uint8_t> img(h.total_bytes, 0);
+  memcpy(img.data(), &h, sizeof h);
+  if (!ops.empty()) memcpy(img.data() + h.ops_off, ops.data(), ops.size() * sizeof(DevOp));
+  if (!out_slot.empty()) memcpy(img.data() + h.outs_off, out_slot.data(), out_slot.size());
+  if (!tables.empty()) memcpy(img.data() + h.tables_off, tables.data(), tables.size());
+  return img;
+}
+
+}  // namespace lutldpc

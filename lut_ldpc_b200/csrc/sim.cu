@@ -1,0 +1,340 @@
+// Fused Monte-Carlo front/back end around the decoder: the frame loop of
+// LDPC_BER_Sim::sim_snr_point (src/LDPC_BER_Sim.cpp:246-311) on the device.
+//   source      bitsin = zeros | randb(K)                                   :263-268
+//   encode      [u, P*u]  (LDPC_Generator_Systematic::encode)               itpp/itpp/comm/ldpc.cpp:1038
+//   BPSK        0 -> +1, 1 -> -1                                            itpp/itpp/comm/modulator.cpp:351-357
+//   AWGN        x = s + sqrt(N0/2) * n                                      itpp/itpp/comm/channel.cpp:1560-1568
+//   LLR         4x/N0, slicer bit = (x > 0 ? 0 : 1)                         modulator.cpp:367-392
+//   quantise    quant_nonlin(qb_Cha) and quant_nonlin(qb_Msg) | map         src/LDPC_Code_LUT.cpp:207-221
+//   count       BERC (data, uncoded), BLERC                                 itpp/itpp/comm/error_counters.cpp
+// The reference draws its normals from dSFMT + ziggurat; here Philox4x32-10 + Box-Muller, so parity
+// with the reference is statistical (BER/FER inside the Monte-Carlo confidence interval), while the
+// decode itself stays bit-exact.
+#include <cstring>
+#include <vector>
+
+#include "core.cuh"
+#include "decoder.hpp"
+
+using namespace lutldpc;
+
+namespace {
+
+// ---- Philox4x32-10 (Salmon et al., SC'11), counter = (c0..c3), key = (k0, k1)
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+  uint32_t hi0 = __umulhi(M0, c[0]), lo0 = M0 * c[0];
+  uint32_t hi1 = __umulhi(M1, c[2]), lo1 = M1 * c[2];
+  uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+  c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+}
+__device__ __forceinline__ void philox4x32_10(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    philox_round(c, k0, k1);
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+}
+enum { STREAM_NOISE = 0, STREAM_INFO = 1 };
+
+// one standard normal for (frame, symbol): Box-Muller on two 52/32-bit uniforms of one Philox block
+__device__ __forceinline__ double normal_for(uint64_t frame, uint32_t sym, uint32_t k0, uint32_t k1) {
+  uint32_t c[4] = {(uint32_t)frame, (uint32_t)(frame >> 32), sym, STREAM_NOISE};
+  philox4x32_10(c, k0, k1);
+  uint64_t a = ((uint64_t)c[0] << 32) | c[1];
+  double u1 = ((double)(a >> 11) + 0.5) * (1.0 / 9007199254740992.0);  // (0,1)
+  double u2 = ((double)c[2] + 0.5) * (1.0 / 4294967296.0);
+  double s, co;
+  sincospi(2.0 * u2, &s, &co);
+  return sqrt(-2.0 * log(u1)) * co;
+}
+
+__device__ __forceinline__ int quant_nonlin_s(double x, const double* b, int nb) {  // src/common.cpp:120-138
+  int idx = 0;
+  for (int i = 0; i < nb; ++i) {
+    if (x > b[i]) ++idx;
+    else break;
+  }
+  return idx;
+}
+__device__ __forceinline__ uint32_t lab2code_s(uint32_t m, int Nq, int q) {
+  uint32_t nz = Nq >> 1;
+  return m < nz ? ((1u << (q - 1)) | (nz - 1 - m)) : (m - nz);
+}
+
+// information bits: cw[k][w] bit j = randb for frame 8w+j, symbol k (k < K)
+__global__ void k_info_bits(uint8_t* __restrict__ cw, int K, int W, int F, uint64_t first_frame, uint32_t k0,
+                            uint32_t k1) {
+  int w = blockIdx.y * blockDim.x + threadIdx.x;
+  int k = blockIdx.x;
+  if (w >= W || k >= K) return;
+  uint32_t byte = 0;
+  for (int j = 0; j < 8; ++j) {
+    int f = 8 * w + j;
+    if (f >= F) break;
+    uint64_t frame = first_frame + f;
+    uint32_t c[4] = {(uint32_t)frame, (uint32_t)(frame >> 32), (uint32_t)(k >> 7), STREAM_INFO};
+    philox4x32_10(c, k0, k1);
+    byte |= ((c[(k >> 5) & 3] >> (k & 31)) & 1u) << j;
+  }
+  cw[(size_t)k * W + w] = (uint8_t)byte;
+}
+
+// parity part: cw[K + r][w] = XOR_k P[r][k] & cw[k][w]   (dense GF(2) mat-vec, all frames of a word at once)
+__global__ void __launch_bounds__(128) k_encode(const uint8_t* __restrict__ P, int rows, int K, int W,
+                                                uint8_t* __restrict__ cw) {
+  int w = blockIdx.y * blockDim.x + threadIdx.x;
+  int r = blockIdx.x;
+  if (w >= W || r >= rows) return;
+  const uint8_t* row = P + (size_t)r * K;
+  uint32_t acc = 0;
+  for (int k = 0; k < K; ++k)
+    if (row[k]) acc ^= cw[(size_t)k * W + w];  // row[k] is uniform over the CTA
+  cw[(size_t)(K + r) * W + w] = (uint8_t)acc;
+}
+
+struct ChanParams {
+  double sigma, four_over_N0;
+  int n_qb_cha, n_qb_msg, use_map, Nq_cha, q_cha, Nq_msg, q_msg;
+};
+
+// BPSK + AWGN + LLR + both quantisers -> channel labels, initial messages, channel hard decision,
+// and the uncoded (slicer) error count.  Thread = (variable node, word).
+__global__ void __launch_bounds__(128) k_channel(const uint8_t* __restrict__ cw, int zero_cw,
+                                                 const int32_t* __restrict__ vn_edge0, int nvar, int W, int F,
+                                                 uint64_t first_frame, uint32_t k0, uint32_t k1, ChanParams cp,
+                                                 const double* __restrict__ qb_cha, const double* __restrict__ qb_msg,
+                                                 const int32_t* __restrict__ cha2msg, uint32_t* __restrict__ cha,
+                                                 uint32_t* __restrict__ msgs, uint8_t* __restrict__ hard,
+                                                 unsigned long long* __restrict__ cnt_uncoded_err) {
+  __shared__ double s_qc[16], s_qm[16];
+  __shared__ int s_map[16];
+  if (threadIdx.x < 16) {
+    s_qc[threadIdx.x] = threadIdx.x < cp.n_qb_cha ? qb_cha[threadIdx.x] : 0.0;
+    s_qm[threadIdx.x] = threadIdx.x < cp.n_qb_msg ? qb_msg[threadIdx.x] : 0.0;
+    s_map[threadIdx.x] = (cp.use_map && threadIdx.x < cp.Nq_cha) ? cha2msg[threadIdx.x] : 0;
+  }
+  __syncthreads();
+  const int w = blockIdx.y * blockDim.x + threadIdx.x;
+  const int v = blockIdx.x;
+  uint32_t nerr = 0;
+  if (w < W) {
+    uint32_t bits = zero_cw ? 0u : cw[(size_t)v * W + w];
+    uint32_t cword = 0, mword = 0, slicer = 0;
+    for (int j = 0; j < 8; ++j) {
+      int f = 8 * w + j;
+      if (f >= F) break;
+      double s = ((bits >> j) & 1u) ? -1.0 : 1.0;
+      double x = s + cp.sigma * normal_for(first_frame + f, (uint32_t)v, k0, k1);
+      double llr = cp.four_over_N0 * x;
+      int c = quant_nonlin_s(llr, s_qc, cp.n_qb_cha);
+      int mm = cp.use_map ? s_map[c] : quant_nonlin_s(llr, s_qm, cp.n_qb_msg);
+      cword |= lab2code_s((uint32_t)c, cp.Nq_cha, cp.q_cha) << (4 * j);
+      mword |= lab2code_s((uint32_t)mm, cp.Nq_msg, cp.q_msg) << (4 * j);
+      slicer |= (x > 0.0 ? 0u : 1u) << j;
+    }
+    cha[(size_t)v * W + w] = cword;
+    hard[(size_t)v * W + w] = (uint8_t)nib_bits_to_byte(cword, cp.q_cha - 1);
+    for (int e = vn_edge0[v]; e < vn_edge0[v + 1]; ++e) msgs[(size_t)e * W + w] = mword;
+    nerr = __popc(slicer ^ bits);
+  }
+  for (int o = 16; o; o >>= 1) nerr += __shfl_xor_sync(0xFFFFFFFFu, nerr, o);
+  if ((threadIdx.x & 31) == 0 && nerr) atomicAdd(cnt_uncoded_err, (unsigned long long)nerr);
+}
+
+// data-bit errors over the first K symbols and per-frame error flags (BERC::count / BLERC::count)
+__global__ void __launch_bounds__(128) k_count_data(const uint8_t* __restrict__ hard, const uint8_t* __restrict__ cw,
+                                                    int zero_cw, int K, int W, int rows_per_cta,
+                                                    uint32_t* __restrict__ ferr,
+                                                    unsigned long long* __restrict__ cnt_data_err) {
+  const int w = blockIdx.y * blockDim.x + threadIdx.x;
+  uint32_t nerr = 0, any = 0;
+  if (w < W) {
+    int k0 = blockIdx.x * rows_per_cta, k1 = min(K, k0 + rows_per_cta);
+    for (int k = k0; k < k1; ++k) {
+      uint32_t d = hard[(size_t)k * W + w] ^ (zero_cw ? 0u : (uint32_t)cw[(size_t)k * W + w]);
+      nerr += __popc(d);
+      any |= d;
+    }
+    if (any) atomicOr(&ferr[w], any);
+  }
+  for (int o = 16; o; o >>= 1) nerr += __shfl_xor_sync(0xFFFFFFFFu, nerr, o);
+  if ((threadIdx.x & 31) == 0 && nerr) atomicAdd(cnt_data_err, (unsigned long long)nerr);
+}
+
+// counters layout = lutldpc_sim_counters as u64[8 + LUTLDPC_ITER_HIST_MAX]
+__global__ void k_count_frames(const uint32_t* __restrict__ ferr, const int32_t* __restrict__ iters, int F, int K,
+                               int nvar, unsigned long long* __restrict__ cnt) {
+  unsigned long long fe = 0, si = 0, nf = 0;
+  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < F; f += gridDim.x * blockDim.x) {
+    fe += (ferr[f >> 3] >> (f & 7)) & 1u;
+    int it = iters[f];
+    nf += it < 0;
+    it = it < 0 ? -it : it;
+    si += it;
+    atomicAdd(&cnt[8 + min(it, LUTLDPC_ITER_HIST_MAX - 1)], 1ull);
+  }
+  for (int o = 16; o; o >>= 1) {
+    fe += __shfl_xor_sync(0xFFFFFFFFu, fe, o);
+    si += __shfl_xor_sync(0xFFFFFFFFu, si, o);
+    nf += __shfl_xor_sync(0xFFFFFFFFu, nf, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (fe) atomicAdd(&cnt[1], fe);
+    if (si) atomicAdd(&cnt[6], si);
+    if (nf) atomicAdd(&cnt[7], nf);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    atomicAdd(&cnt[0], (unsigned long long)F);
+    atomicAdd(&cnt[2], (unsigned long long)F * K);
+    atomicAdd(&cnt[4], (unsigned long long)F * nvar);
+  }
+}
+
+// frame-major 0/1 bytes <-> bit-per-frame rows, for lutldpc_encode
+__global__ void k_bits_to_rows(const uint8_t* __restrict__ in, int ncols_in, int K, int W, int F, uint8_t* rows) {
+  int w = blockIdx.y * blockDim.x + threadIdx.x, k = blockIdx.x;
+  if (w >= W || k >= K) return;
+  uint32_t b = 0;
+  for (int j = 0; j < 8; ++j) {
+    int f = 8 * w + j;
+    if (f < F) b |= (uint32_t)(in[(size_t)f * ncols_in + k] & 1) << j;
+  }
+  rows[(size_t)k * W + w] = (uint8_t)b;
+}
+__global__ void k_rows_to_bits(const uint8_t* __restrict__ rows, int N, int W, int F, uint8_t* out) {
+  int w = blockIdx.y * blockDim.x + threadIdx.x, v = blockIdx.x;
+  if (w >= W || v >= N) return;
+  uint32_t b = rows[(size_t)v * W + w];
+  for (int j = 0; j < 8; ++j) {
+    int f = 8 * w + j;
+    if (f < F) out[(size_t)f * N + v] = (b >> j) & 1;
+  }
+}
+
+}  // namespace
+
+#define CKH(call, where)                                   \
+  do {                                                     \
+    cudaError_t e_ = (call);                               \
+    if (e_ != cudaSuccess) return h->cuda_fail(e_, where); \
+  } while (0)
+#define CKL(where) CKH(cudaGetLastError(), where)
+
+extern "C" {
+
+int lutldpc_encode(lutldpc_decoder* h, int n_frames, const uint8_t* info, uint8_t* codeword) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (n_frames < 0 || (n_frames && (!info || !codeword))) return h->fail(LUTLDPC_ERR_ARG, "bad argument");
+  if (h->m.gen.empty()) return h->fail(LUTLDPC_ERR_STATE, "decoder has no generator matrix");
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  const int N = h->m.nvar, K = h->m.gen_cols, rows = h->m.gen_rows;
+  if (K + rows != N) return h->fail(LUTLDPC_ERR_MODEL, "generator shape does not match nvar");
+  cudaStream_t st = h->stream;
+  const int maxb = h->max_batch_frames();
+  for (int f0 = 0; f0 < n_frames; f0 += maxb) {
+    int nf = std::min(maxb, n_frames - f0);
+    int W = ((nf + 255) / 256) * 32;
+    CKH(h->buf_cw.ensure((size_t)N * W), "alloc cw");
+    CKH(h->buf_lab_cha.ensure((size_t)nf * N), "alloc");
+    CKH(cudaMemcpyAsync(h->buf_lab_cha.p, info + (size_t)f0 * K, (size_t)nf * K, cudaMemcpyHostToDevice, st), "H2D info");
+    dim3 gk(K, (W + 127) / 128), gr(rows, (W + 127) / 128), gn(N, (W + 127) / 128);
+    k_bits_to_rows<<<gk, 128, 0, st>>>(h->buf_lab_cha.p, K, K, W, nf, h->buf_cw.p);
+    CKL("bits_to_rows");
+    k_encode<<<gr, 128, 0, st>>>(h->d_gen.p, rows, K, W, h->buf_cw.p);
+    CKL("encode");
+    CKH(h->buf_out.ensure((size_t)nf * N), "alloc out");
+    k_rows_to_bits<<<gn, 128, 0, st>>>(h->buf_cw.p, N, W, nf, h->buf_out.p);
+    CKL("rows_to_bits");
+    CKH(cudaMemcpyAsync(codeword + (size_t)f0 * N, h->buf_out.p, (size_t)nf * N, cudaMemcpyDeviceToHost, st), "D2H cw");
+    CKH(cudaStreamSynchronize(st), "sync");
+  }
+  return LUTLDPC_OK;
+}
+
+int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (!p || !acc || p->n_frames < 0) return h->fail(LUTLDPC_ERR_ARG, "bad argument");
+  const DecoderModel& m = h->m;
+  if (!p->zero_codeword && m.gen.empty())
+    return h->fail(LUTLDPC_ERR_STATE, "zero_codeword=0 needs a generator matrix in the decoder");
+  if (h->init_mode == LUTLDPC_INIT_CONT && (int)m.qb_Msg.size() != m.Nq_Msg[0] - 1)
+    return h->fail(LUTLDPC_ERR_STATE, "decoder has no message quantiser qb_Msg for continuous inputs");
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  cudaStream_t st = h->stream;
+  const int N = m.nvar, K = m.ninfo();
+  if (!p->zero_codeword && (m.gen_cols != K || m.gen_rows != N - K))
+    return h->fail(LUTLDPC_ERR_MODEL, "generator shape does not match the code");
+  int batch = p->batch_frames > 0 ? p->batch_frames : 8192;
+  batch = std::min(batch, h->max_batch_frames());
+  batch = std::max(256, batch / 256 * 256);
+  const size_t n_cnt = 8 + LUTLDPC_ITER_HIST_MAX;
+  CKH(h->buf_cnt.ensure(n_cnt), "alloc counters");
+  CKH(cudaMemsetAsync(h->buf_cnt.p, 0, n_cnt * 8, st), "memset counters");
+  // N0 = 10^(-snr/10) / rate, sigma^2 = N0/2   (src/LDPC_BER_Sim.cpp:248-249)
+  const double N0 = pow(10.0, -p->snr_db / 10.0) / m.rate();
+  ChanParams cp;
+  cp.sigma = sqrt(N0 / 2.0);
+  cp.four_over_N0 = 4.0 / N0;
+  cp.n_qb_cha = (int)m.qb_Cha.size(); cp.n_qb_msg = (int)m.qb_Msg.size();
+  cp.use_map = h->init_mode == LUTLDPC_INIT_QCHA;
+  cp.Nq_cha = m.Nq_Cha; cp.q_cha = code_bits(m.Nq_Cha); cp.Nq_msg = m.Nq_Msg[0]; cp.q_msg = code_bits(m.Nq_Msg[0]);
+  const uint32_t k0 = (uint32_t)p->seed, k1 = (uint32_t)(p->seed >> 32);
+  int64_t total_launches = 0;
+  cudaEvent_t e_first = nullptr, e_last = nullptr;
+  CKH(cudaEventCreate(&e_first), "event");
+  CKH(cudaEventCreate(&e_last), "event");
+  CKH(cudaEventRecord(e_first, st), "event");
+  for (int64_t done = 0; done < p->n_frames; done += batch) {
+    int nf = (int)std::min<int64_t>(batch, p->n_frames - done);
+    int rc = h->begin_batch(nf);
+    if (rc) return rc;
+    const int W = h->b.W;
+    const uint64_t first = p->first_frame + (uint64_t)done;
+    CKH(h->buf_ferr.ensure((size_t)W), "alloc ferr");
+    CKH(cudaMemsetAsync(h->buf_ferr.p, 0, (size_t)W * 4, st), "memset ferr");
+    dim3 gw((W + 127) / 128);
+    if (!p->zero_codeword) {
+      CKH(h->buf_cw.ensure((size_t)N * W), "alloc cw");
+      k_info_bits<<<dim3(K, gw.x), 128, 0, st>>>(h->buf_cw.p, K, W, nf, first, k0, k1);
+      CKL("info_bits");
+      k_encode<<<dim3(N - K, gw.x), 128, 0, st>>>(h->d_gen.p, N - K, K, W, h->buf_cw.p);
+      CKL("encode");
+      h->launches += 2;
+    }
+    k_channel<<<dim3(N, gw.x), 128, 0, st>>>(h->buf_cw.p, p->zero_codeword != 0, h->g.vn_edge0, N, W, nf, first, k0, k1,
+                                             cp, h->d_qb_cha.p, h->d_qb_msg.p, h->d_cha2msg.p, h->b.cha, h->b.msgs,
+                                             h->b.hard, h->buf_cnt.p + 5);
+    CKL("channel");
+    ++h->launches;
+    rc = h->run_passes(nullptr);
+    if (rc) return rc;
+    int rows_per = 64;
+    k_count_data<<<dim3((K + rows_per - 1) / rows_per, gw.x), 128, 0, st>>>(h->b.hard, h->buf_cw.p, p->zero_codeword != 0,
+                                                                          K, W, rows_per, h->buf_ferr.p, h->buf_cnt.p + 3);
+    CKL("count_data");
+    k_count_frames<<<std::min(64, (nf + 255) / 256), 256, 0, st>>>(h->buf_ferr.p, h->b.iters, nf, K, N, h->buf_cnt.p);
+    CKL("count_frames");
+    total_launches += h->launches + 2;
+  }
+  CKH(cudaEventRecord(e_last, st), "event");
+  std::vector<unsigned long long> host(n_cnt);
+  CKH(cudaMemcpyAsync(host.data(), h->buf_cnt.p, n_cnt * 8, cudaMemcpyDeviceToHost, st), "D2H counters");
+  CKH(cudaStreamSynchronize(st), "sync");
+  // report the whole call (all batches) through last_call_stats
+  std::swap(h->ev0, e_first);
+  std::swap(h->ev1, e_last);
+  cudaEventDestroy(e_first);
+  cudaEventDestroy(e_last);
+  h->launches = total_launches;
+  h->have_stats = p->n_frames > 0;
+  h->stat_frame_iters = (int64_t)host[6];
+  acc->frames += host[0]; acc->frame_errors += host[1]; acc->data_bits += host[2]; acc->data_bit_errors += host[3];
+  acc->uncoded_bits += host[4]; acc->uncoded_bit_errors += host[5]; acc->sum_iters += host[6];
+  acc->decode_failures += host[7];
+  for (int i = 0; i < LUTLDPC_ITER_HIST_MAX; ++i) acc->iter_hist[i] += host[8 + i];
+  return LUTLDPC_OK;
+}
+
+}  // extern "C"
