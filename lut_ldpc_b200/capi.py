@@ -1,0 +1,226 @@
+"""ctypes binding of include/lutldpc.h (liblutldpc_b200.so).  Fails loudly when the library is absent."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+INIT_CONT, INIT_QCHA = 0, 1
+TRACE_INIT, TRACE_CN, TRACE_VN = 0, 1, 2
+ITER_HIST_MAX = 256
+
+
+class LutLdpcError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("lutldpc error %d: %s" % (code, msg))
+        self.code = code
+
+
+def library_path():
+    return os.path.join(HERE, "liblutldpc_b200.so")
+
+
+def build_library(verbose=False):
+    """nvcc -gencode arch=compute_100a,code=sm_100a build of csrc/ (see csrc/Makefile)."""
+    subprocess.check_call(["make", "-C", os.path.join(HERE, "csrc"), "-j8"] + ([] if verbose else ["-s"]))
+    return library_path()
+
+
+class _Info(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("nvar", "nchk", "nchk_lin_indep", "ninfo", "num_edges", "max_iters", "Nq_Cha",
+                                         "min_lut", "has_gen", "n_degree_classes")] + \
+               [("lookups_per_frame_iter", C.c_int64), ("lookups_per_frame_iter_naive", C.c_int64), ("rate", C.c_double)]
+
+
+class _SimParams(C.Structure):
+    _fields_ = [("snr_db", C.c_double), ("n_frames", C.c_int64), ("seed", C.c_uint64), ("first_frame", C.c_uint64),
+                ("zero_codeword", C.c_int32), ("batch_frames", C.c_int32)]
+
+
+class SimCounters(C.Structure):
+    """lutldpc_sim_counters: the BERC/BLERC counters of LDPC_BER_Sim::sim_snr_point."""
+    _fields_ = [(n, C.c_uint64) for n in ("frames", "frame_errors", "data_bits", "data_bit_errors", "uncoded_bits",
+                                          "uncoded_bit_errors", "sum_iters", "decode_failures")] + \
+               [("iter_hist", C.c_uint64 * ITER_HIST_MAX)]
+
+    NAMES = ("frames", "frame_errors", "data_bits", "data_bit_errors", "uncoded_bits", "uncoded_bit_errors",
+             "sum_iters", "decode_failures")
+
+    def as_array(self):
+        return np.array([getattr(self, n) for n in self.NAMES] + list(self.iter_hist), dtype=np.int64)
+
+    @classmethod
+    def from_array(cls, a):
+        c = cls()
+        for i, n in enumerate(cls.NAMES):
+            setattr(c, n, int(a[i]))
+        for i in range(ITER_HIST_MAX):
+            c.iter_hist[i] = int(a[len(cls.NAMES) + i])
+        return c
+
+    def as_dict(self):
+        return {n: int(getattr(self, n)) for n in self.NAMES}
+
+
+_lib = None
+EXPORTS = ["lutldpc_abi_version", "lutldpc_last_error", "lutldpc_create", "lutldpc_create_from_bundle",
+           "lutldpc_destroy", "lutldpc_get_info", "lutldpc_set_exit_conditions", "lutldpc_set_initial_message_mode",
+           "lutldpc_set_stream", "lutldpc_set_poll_interval", "lutldpc_decode_quantized",
+           "lutldpc_decode_quantized_device", "lutldpc_decode_llr", "lutldpc_decode_llr_device", "lutldpc_quantize",
+           "lutldpc_decode_quantized_traced", "lutldpc_encode", "lutldpc_syndrome_check", "lutldpc_simulate_snr",
+           "lutldpc_last_call_stats"]
+
+
+def load_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    p = library_path()
+    if not os.path.exists(p):
+        raise LutLdpcError(-3, "%s is missing: build it with lut_ldpc_b200.build_library() "
+                               "(nvcc, sm_100a); there is no CPU fallback" % p)
+    L = C.CDLL(p)
+    vp, i32, i64 = C.c_void_p, C.c_int, C.c_int64
+    L.lutldpc_last_error.restype = C.c_char_p
+    L.lutldpc_last_error.argtypes = [vp]
+    L.lutldpc_create_from_bundle.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.lutldpc_create.argtypes = [vp, C.POINTER(vp)]
+    L.lutldpc_destroy.argtypes = [vp]
+    L.lutldpc_destroy.restype = None
+    L.lutldpc_get_info.argtypes = [vp, C.POINTER(_Info)]
+    L.lutldpc_set_exit_conditions.argtypes = [vp, i32, i32, i32]
+    L.lutldpc_set_initial_message_mode.argtypes = [vp, i32]
+    L.lutldpc_set_stream.argtypes = [vp, vp]
+    L.lutldpc_set_poll_interval.argtypes = [vp, i32]
+    L.lutldpc_decode_quantized.argtypes = [vp, i32, vp, vp, vp, vp]
+    L.lutldpc_decode_quantized_device.argtypes = [vp, i32, vp, vp, vp, vp]
+    L.lutldpc_decode_llr.argtypes = [vp, i32, vp, vp, vp]
+    L.lutldpc_decode_llr_device.argtypes = [vp, i32, vp, vp, vp]
+    L.lutldpc_quantize.argtypes = [vp, i32, vp, vp, vp]
+    L.lutldpc_decode_quantized_traced.argtypes = [vp, i32, vp, vp, vp, vp, i32, vp, vp, vp, i32, vp]
+    L.lutldpc_encode.argtypes = [vp, i32, vp, vp]
+    L.lutldpc_syndrome_check.argtypes = [vp, i32, vp, vp]
+    L.lutldpc_simulate_snr.argtypes = [vp, C.POINTER(_SimParams), C.POINTER(SimCounters)]
+    L.lutldpc_last_call_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64)]
+    _lib = L
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Decoder:
+    """One lutldpc_decoder handle (an LDPC_Code_LUT bound to the current CUDA device)."""
+
+    def __init__(self, bundle_path):
+        self._L = load_library()
+        h = C.c_void_p()
+        rc = self._L.lutldpc_create_from_bundle(os.fsencode(bundle_path), C.byref(h))
+        if rc != 0:
+            raise LutLdpcError(rc, (self._L.lutldpc_last_error(None) or b"").decode())
+        self._h = h
+        info = _Info()
+        self._ck(self._L.lutldpc_get_info(self._h, C.byref(info)))
+        self.info = info
+        for n, _ in _Info._fields_:
+            setattr(self, n, getattr(info, n))
+
+    from_bundle = classmethod(lambda cls, path: cls(path))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.lutldpc_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise LutLdpcError(rc, (self._L.lutldpc_last_error(self._h) or b"").decode())
+
+    # ---- configuration (LDPC_Code_LUT::set_exit_conditions / set_initial_message_mode)
+    def set_exit_conditions(self, max_iters, psc=True, pisc=False):
+        self._ck(self._L.lutldpc_set_exit_conditions(self._h, int(max_iters), int(psc), int(pisc)))
+
+    def set_initial_message_mode(self, mode):
+        self._ck(self._L.lutldpc_set_initial_message_mode(self._h, int(mode)))
+
+    def set_stream(self, cuda_stream_ptr):
+        self._ck(self._L.lutldpc_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
+
+    def set_poll_interval(self, every):
+        self._ck(self._L.lutldpc_set_poll_interval(self._h, int(every)))
+
+    # ---- decode (host buffers)
+    def decode_quantized(self, cha, msg):
+        cha = np.ascontiguousarray(cha, np.uint8).reshape(-1, self.nvar)
+        msg = np.ascontiguousarray(msg, np.uint8).reshape(-1, self.nvar)
+        assert cha.shape == msg.shape
+        out = np.empty(cha.shape, np.uint8)
+        it = np.empty(cha.shape[0], np.int32)
+        self._ck(self._L.lutldpc_decode_quantized(self._h, cha.shape[0], _p(cha), _p(msg), _p(out), _p(it)))
+        return out, it
+
+    def decode_quantized_traced(self, cha, msg, trace_frame, max_rec):
+        cha = np.ascontiguousarray(cha, np.uint8).reshape(-1, self.nvar)
+        msg = np.ascontiguousarray(msg, np.uint8).reshape(-1, self.nvar)
+        out = np.empty(cha.shape, np.uint8)
+        it = np.empty(cha.shape[0], np.int32)
+        tm = np.zeros((max_rec, self.num_edges), np.uint8)
+        tk = np.zeros(max_rec, np.int32)
+        ti = np.zeros(max_rec, np.int32)
+        n = C.c_int32(0)
+        self._ck(self._L.lutldpc_decode_quantized_traced(self._h, cha.shape[0], _p(cha), _p(msg), _p(out), _p(it),
+                                                         int(trace_frame), _p(tm), _p(tk), _p(ti), int(max_rec),
+                                                         C.byref(n)))
+        return out, it, [(int(tk[i]), int(ti[i]), tm[i].copy()) for i in range(n.value)]
+
+    def decode_llr(self, llr):
+        llr = np.ascontiguousarray(llr, np.float64).reshape(-1, self.nvar)
+        out = np.empty(llr.shape, np.uint8)
+        it = np.empty(llr.shape[0], np.int32)
+        self._ck(self._L.lutldpc_decode_llr(self._h, llr.shape[0], _p(llr), _p(out), _p(it)))
+        return out, it
+
+    def quantize(self, llr):
+        llr = np.ascontiguousarray(llr, np.float64).reshape(-1, self.nvar)
+        cha = np.empty(llr.shape, np.uint8)
+        msg = np.empty(llr.shape, np.uint8)
+        self._ck(self._L.lutldpc_quantize(self._h, llr.shape[0], _p(llr), _p(cha), _p(msg)))
+        return cha, msg
+
+    def encode(self, info):
+        info = np.ascontiguousarray(info, np.uint8).reshape(-1, self.ninfo)
+        cw = np.empty((info.shape[0], self.nvar), np.uint8)
+        self._ck(self._L.lutldpc_encode(self._h, info.shape[0], _p(info), _p(cw)))
+        return cw
+
+    def syndrome_check(self, bits):
+        bits = np.ascontiguousarray(bits, np.uint8).reshape(-1, self.nvar)
+        ok = np.empty(bits.shape[0], np.uint8)
+        self._ck(self._L.lutldpc_syndrome_check(self._h, bits.shape[0], _p(bits), _p(ok)))
+        return ok.astype(bool)
+
+    # ---- decode (device pointers, e.g. torch tensors' data_ptr())
+    def decode_quantized_device(self, n_frames, d_cha, d_msg, d_out, d_iters=0):
+        self._ck(self._L.lutldpc_decode_quantized_device(self._h, int(n_frames), C.c_void_p(d_cha), C.c_void_p(d_msg),
+                                                         C.c_void_p(d_out), C.c_void_p(d_iters or None)))
+
+    def decode_llr_device(self, n_frames, d_llr, d_out, d_iters=0):
+        self._ck(self._L.lutldpc_decode_llr_device(self._h, int(n_frames), C.c_void_p(d_llr), C.c_void_p(d_out),
+                                                   C.c_void_p(d_iters or None)))
+
+    # ---- fused Monte-Carlo step (LDPC_BER_Sim::sim_snr_point's frame loop)
+    def simulate_snr(self, snr_db, n_frames, seed=0, first_frame=0, zero_codeword=True, batch_frames=0, acc=None):
+        p = _SimParams(float(snr_db), int(n_frames), int(seed), int(first_frame), int(bool(zero_codeword)),
+                       int(batch_frames))
+        acc = acc if acc is not None else SimCounters()
+        self._ck(self._L.lutldpc_simulate_snr(self._h, C.byref(p), C.byref(acc)))
+        return acc
+
+    def last_call_stats(self):
+        ms, nl, fi = C.c_double(0), C.c_int64(0), C.c_int64(0)
+        self._ck(self._L.lutldpc_last_call_stats(self._h, C.byref(ms), C.byref(nl), C.byref(fi)))
+        return dict(device_ms=ms.value, kernel_launches=nl.value, frame_iterations=fi.value)

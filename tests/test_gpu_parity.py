@@ -1,0 +1,117 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the reference's own fixtures
+(bit-exact: hard decisions, lut_decode return values, every per-iteration message dump) and against
+the oracle restatement on seeded random inputs."""
+import numpy as np
+import pytest
+
+import _golden
+import pyoracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def L():
+    import lut_ldpc_b200
+    return lut_ldpc_b200
+
+
+_decoders = {}
+
+
+def _dec(L, cfg):
+    if cfg not in _decoders:
+        _decoders[cfg] = L.Decoder(_golden.bundle_path(cfg))
+    return _decoders[cfg]
+
+
+@pytest.mark.parametrize("cfg,tag", _golden.all_fixtures())
+def test_fixture_bit_exact(L, cfg, tag):
+    fx = pyoracle.read_fixture(_golden.fixture_path(cfg, tag))
+    a = _golden.fixture_args(cfg, tag)
+    dec = _dec(L, cfg)
+    dec.set_exit_conditions(dec.max_iters, a["psc"], a["pisc"])
+    out, it = dec.decode_quantized(fx["cha"], fx["msg"])
+    assert np.array_equal(it, fx["ret"])
+    assert np.array_equal(out, fx["out"])
+    for f, recs in enumerate(fx["traces"]):
+        o, i2, mine = dec.decode_quantized_traced(fx["cha"], fx["msg"], f, len(recs) + 4)
+        assert np.array_equal(i2, fx["ret"]) and np.array_equal(o, fx["out"])
+        assert len(mine) == len(recs), (len(mine), len(recs))
+        for (k0, i0, m0), (k1, i1, m1) in zip(recs, mine):
+            assert (k0, i0) == (k1, i1)
+            assert np.array_equal(m0, m1), (cfg, tag, f, k0, i0, np.flatnonzero(m0 != m1)[:8])
+
+
+@pytest.mark.parametrize("cfg,tag", [(c, t) for c, t in _golden.all_fixtures() if "with-llr 0" not in
+                                     _golden.MANIFEST[c]["fixtures"][t]["args"]])
+def test_llr_front_end(L, cfg, tag):
+    """decode(const vec&): quant_nonlin front end + lut_decode from the reference's double LLRs."""
+    fx = pyoracle.read_fixture(_golden.fixture_path(cfg, tag))
+    a = _golden.fixture_args(cfg, tag)
+    dec = _dec(L, cfg)
+    dec.set_exit_conditions(dec.max_iters, a["psc"], a["pisc"])
+    dec.set_initial_message_mode(L.INIT_QCHA if a["init_mode"] == "qcha" else L.INIT_CONT)
+    cha, msg = dec.quantize(fx["llr"])
+    assert np.array_equal(cha, fx["cha"]) and np.array_equal(msg, fx["msg"])
+    out, it = dec.decode_llr(fx["llr"])
+    assert np.array_equal(it, fx["ret"]) and np.array_equal(out, fx["out"])
+
+
+@pytest.mark.parametrize("cfg", ["c1b_reg36_n1000", "c2_irr_n500", "c1a_reg632_wide", "c4_reg632_high",
+                                 "x_varq_reuse", "x_lutcn_irr_n500", "x_qcha_irr_n1000"])
+@pytest.mark.parametrize("n_frames", [1, 8, 333])
+def test_random_inputs_vs_oracle(L, cfg, n_frames):
+    """Seeded noisy labels (ragged frame counts, several 256-frame column blocks) against the oracle."""
+    orc = pyoracle.Oracle(_golden.bundle_path(cfg))
+    dec = _dec(L, cfg)
+    rng = np.random.default_rng(1234 + n_frames)
+    nq_cha, nq_msg = orc.nq_cha, int(orc.nq_msg[0])
+    # all-zero codeword through a coarse "channel": mostly positive labels with noise
+    base = rng.normal(1.0, 0.9, size=(n_frames, orc.nvar))
+    cha = np.clip(np.floor((base + 2.0) / 4.0 * nq_cha), 0, nq_cha - 1).astype(np.uint8)
+    msg = np.clip(np.floor((base + 2.0) / 4.0 * nq_msg), 0, nq_msg - 1).astype(np.uint8)
+    for psc, pisc in ((1, 1), (0, 0), (1, 0)):
+        orc.set_exit_conditions(orc.max_iters, psc, pisc)
+        dec.set_exit_conditions(dec.max_iters, psc, pisc)
+        want_out, want_it = orc.lut_decode_batch(cha, msg)
+        out, it = dec.decode_quantized(cha, msg)
+        assert np.array_equal(it, want_it), (psc, pisc)
+        assert np.array_equal(out, want_out), (psc, pisc)
+
+
+def test_empty_batch(L):
+    dec = _dec(L, "c1b_reg36_n1000")
+    out, it = dec.decode_quantized(np.zeros((0, dec.nvar), np.uint8), np.zeros((0, dec.nvar), np.uint8))
+    assert out.shape == (0, dec.nvar) and it.shape == (0,)
+
+
+def test_encode_and_syndrome(L):
+    for cfg in ("c2_irr_n500", "c1a_reg632_wide"):
+        orc = pyoracle.Oracle(_golden.bundle_path(cfg))
+        dec = _dec(L, cfg)
+        rng = np.random.default_rng(7)
+        info = rng.integers(0, 2, size=(37, orc.ninfo), dtype=np.uint8)
+        cw = dec.encode(info)
+        want = np.stack([orc.encode(u) for u in info])
+        assert np.array_equal(cw, want)
+        ok = dec.syndrome_check(cw)
+        assert ok.all()
+        bad = cw.copy()
+        bad[5, 3] ^= 1
+        bad[20, orc.nvar - 1] ^= 1
+        ok = dec.syndrome_check(bad)
+        assert [i for i in range(37) if not ok[i]] == [5, 20]
+
+
+def test_decode_failure_and_large_code(L):
+    """N=64800: both fixture frames, replicated across two column blocks."""
+    cfg = "c5_n64800"
+    fx = pyoracle.read_fixture(_golden.fixture_path(cfg, "snr1.3"))
+    dec = _dec(L, cfg)
+    dec.set_exit_conditions(dec.max_iters, 1, 1)
+    cha = np.tile(fx["cha"], (130, 1))
+    msg = np.tile(fx["msg"], (130, 1))
+    out, it = dec.decode_quantized(cha, msg)
+    assert np.array_equal(it, np.tile(fx["ret"], 130))
+    assert np.array_equal(out, np.tile(fx["out"], (130, 1)))
