@@ -111,6 +111,8 @@ int lutldpc_decode_llr_device(lutldpc_decoder* h, int n_frames, const double* d_
                               int32_t* d_out_iters);
 /* front end only: quant_nonlin(llr, qb_Cha) and quant_nonlin(llr, qb_Msg) | Nq_Cha_2_Nq_Msg_map */
 int lutldpc_quantize(lutldpc_decoder* h, int n_frames, const double* llr, uint8_t* llr_cha, uint8_t* llr_msg);
+int lutldpc_quantize_device(lutldpc_decoder* h, int n_frames, const double* d_llr, uint8_t* d_llr_cha,
+                            uint8_t* d_llr_msg);
 
 /* lut_decode with the reference's output_verbosity >= 2 message dumps for ONE frame of the batch
  * (src/LDPC_Code_LUT.cpp:291-298,311-317,331-337): record r holds all num_edges messages as labels,
@@ -148,6 +150,16 @@ typedef struct lutldpc_sim_counters {
 } lutldpc_sim_counters;
 /* counters are ADDED to *acc (so successive calls / ranks accumulate) */
 int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc);
+
+/* ---- per-kernel device times.  With profiling on, an event is recorded after every kernel launch
+ * of the handle; lutldpc_get_profile returns, per kind, the summed device milliseconds and launch
+ * counts since profiling was switched on.  Kinds: 0 reset, 1 pack, 2 channel, 3 min-sum check pass,
+ * 4 syndrome, 5 finalize, 6 unpack, 7 count, 8 encode, 16+c variable-node pass of degree class c,
+ * 32+c decision pass, 48+c LUT check pass.  class_degree/class_nodes [16] describe the VN classes. */
+#define LUTLDPC_PROFILE_KINDS 64
+int lutldpc_set_profiling(lutldpc_decoder* h, int on);
+int lutldpc_get_profile(lutldpc_decoder* h, double* ms, int64_t* launches, int32_t* class_degree,
+                        int32_t* class_nodes);
 
 /* ---- timing aid for bench.py: device-time (ms) of the last decode/simulate call's kernels, measured
  * with CUDA events on the handle's stream, and number of kernels it launched */

@@ -69,7 +69,10 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_last_error", "lutldpc_create", "lutld
            "lutldpc_set_stream", "lutldpc_set_poll_interval", "lutldpc_decode_quantized",
            "lutldpc_decode_quantized_device", "lutldpc_decode_llr", "lutldpc_decode_llr_device", "lutldpc_quantize",
            "lutldpc_decode_quantized_traced", "lutldpc_encode", "lutldpc_syndrome_check", "lutldpc_simulate_snr",
-           "lutldpc_last_call_stats"]
+           "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device"]
+PROFILE_KINDS = 64
+PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
+                 7: "count", 8: "encode"}
 
 
 def load_library():
@@ -103,6 +106,9 @@ def load_library():
     L.lutldpc_syndrome_check.argtypes = [vp, i32, vp, vp]
     L.lutldpc_simulate_snr.argtypes = [vp, C.POINTER(_SimParams), C.POINTER(SimCounters)]
     L.lutldpc_last_call_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64)]
+    L.lutldpc_quantize_device.argtypes = [vp, i32, vp, vp, vp]
+    L.lutldpc_set_profiling.argtypes = [vp, i32]
+    L.lutldpc_get_profile.argtypes = [vp, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -208,6 +214,10 @@ class Decoder:
         self._ck(self._L.lutldpc_decode_quantized_device(self._h, int(n_frames), C.c_void_p(d_cha), C.c_void_p(d_msg),
                                                          C.c_void_p(d_out), C.c_void_p(d_iters or None)))
 
+    def quantize_device(self, n_frames, d_llr, d_cha, d_msg):
+        self._ck(self._L.lutldpc_quantize_device(self._h, int(n_frames), C.c_void_p(d_llr), C.c_void_p(d_cha),
+                                                 C.c_void_p(d_msg)))
+
     def decode_llr_device(self, n_frames, d_llr, d_out, d_iters=0):
         self._ck(self._L.lutldpc_decode_llr_device(self._h, int(n_frames), C.c_void_p(d_llr), C.c_void_p(d_out),
                                                    C.c_void_p(d_iters or None)))
@@ -219,6 +229,31 @@ class Decoder:
         acc = acc if acc is not None else SimCounters()
         self._ck(self._L.lutldpc_simulate_snr(self._h, C.byref(p), C.byref(acc)))
         return acc
+
+    def set_profiling(self, on):
+        self._ck(self._L.lutldpc_set_profiling(self._h, int(bool(on))))
+
+    def get_profile(self):
+        """{kernel name: (device ms, launches)} since profiling was switched on; VN classes by degree."""
+        ms = np.zeros(PROFILE_KINDS, np.float64)
+        n = np.zeros(PROFILE_KINDS, np.int64)
+        deg = np.zeros(16, np.int32)
+        cnt = np.zeros(16, np.int32)
+        self._ck(self._L.lutldpc_get_profile(self._h, _p(ms), _p(n), _p(deg), _p(cnt)))
+        out = {}
+        for k in range(PROFILE_KINDS):
+            if n[k] == 0:
+                continue
+            if k < 16:
+                name = PROFILE_NAMES.get(k, "kind%d" % k)
+            else:
+                name = "%s_c%d" % (("vn", "dec", "chk")[k // 16 - 1], k % 16)
+                if k < 48:
+                    name = "%s_dv%d" % (("vn", "dec")[k // 16 - 1], deg[k % 16])
+            out[name] = (float(ms[k]), int(n[k]))
+        self.vn_class_degree = [int(d) for d in deg if d]
+        self.vn_class_nodes = [int(c) for d, c in zip(deg, cnt) if d]
+        return out
 
     def last_call_stats(self):
         ms, nl, fi = C.c_double(0), C.c_int64(0), C.c_int64(0)

@@ -140,6 +140,30 @@ int lutldpc_set_stream(lutldpc_decoder* h, void* cuda_stream) {
   return LUTLDPC_OK;
 }
 
+int lutldpc_set_profiling(lutldpc_decoder* h, int on) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (h->profiling && !on) h->flush_profile();
+  h->profiling = on != 0;
+  if (on) {
+    h->evn = 0;
+    for (int i = 0; i < LUTLDPC_PROFILE_KINDS; ++i) { h->prof_ms[i] = 0; h->prof_n[i] = 0; }
+  }
+  return LUTLDPC_OK;
+}
+
+int lutldpc_get_profile(lutldpc_decoder* h, double* ms, int64_t* launches, int32_t* class_degree, int32_t* class_nodes) {
+  if (!h || !ms || !launches) return LUTLDPC_ERR_ARG;
+  int rc = h->flush_profile();
+  if (rc) return rc;
+  for (int i = 0; i < LUTLDPC_PROFILE_KINDS; ++i) { ms[i] = h->prof_ms[i]; launches[i] = h->prof_n[i]; }
+  for (int c = 0; c < 16; ++c) {
+    bool have = c < (int)h->vn_classes.size();
+    if (class_degree) class_degree[c] = have ? h->vn_classes[c].degree : 0;
+    if (class_nodes) class_nodes[c] = have ? h->vn_classes[c].n : 0;
+  }
+  return LUTLDPC_OK;
+}
+
 int lutldpc_set_poll_interval(lutldpc_decoder* h, int every) {
   if (!h) return LUTLDPC_ERR_ARG;
   h->poll_every = every < 0 ? 0 : every;
@@ -165,6 +189,7 @@ int lutldpc_decode_quantized_device(lutldpc_decoder* h, int n_frames, const uint
     rc = h->run_batch(nf, d_cha + (size_t)f0 * N, d_msg + (size_t)f0 * N, nullptr);
     if (rc) return rc;
     CKH(launch_unpack(h->g, h->b, d_out_bits + (size_t)f0 * N, h->stream), "unpack");
+    h->launched(KIND_UNPACK);
     if (d_out_iters)
       CKH(cudaMemcpyAsync(d_out_iters + f0, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToDevice, h->stream), "iters copy");
   }
@@ -195,6 +220,7 @@ static int decode_host(lutldpc_decoder* h, int n_frames, const uint8_t* cha, con
     int rc = h->run_batch(nf, h->buf_lab_cha.p, h->buf_lab_msg.p, tr);
     if (rc) return rc;
     CKH(launch_unpack(h->g, h->b, h->buf_out.p, st), "unpack");
+    h->launched(KIND_UNPACK);
     CKH(cudaMemcpyAsync(out_bits + (size_t)f0 * N, h->buf_out.p, cnt, cudaMemcpyDeviceToHost, st), "D2H bits");
     if (out_iters)
       CKH(cudaMemcpyAsync(out_iters + f0, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToHost, st), "D2H iters");
@@ -250,6 +276,7 @@ int lutldpc_decode_llr_device(lutldpc_decoder* h, int n_frames, const double* d_
     rc = h->run_batch(nf, h->buf_lab_cha.p, h->buf_lab_msg.p, nullptr);
     if (rc) return rc;
     CKH(launch_unpack(h->g, h->b, d_out_bits + (size_t)f0 * N, h->stream), "unpack");
+    h->launched(KIND_UNPACK);
     if (d_out_iters)
       CKH(cudaMemcpyAsync(d_out_iters + f0, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToDevice, h->stream), "iters copy");
   }
@@ -272,6 +299,17 @@ int lutldpc_quantize(lutldpc_decoder* h, int n_frames, const double* llr, uint8_
   CKH(cudaMemcpyAsync(cha, h->buf_lab_cha.p, cnt, cudaMemcpyDeviceToHost, st), "D2H");
   CKH(cudaMemcpyAsync(msg, h->buf_lab_msg.p, cnt, cudaMemcpyDeviceToHost, st), "D2H");
   CKH(cudaStreamSynchronize(st), "sync");
+  return LUTLDPC_OK;
+}
+
+int lutldpc_quantize_device(lutldpc_decoder* h, int n_frames, const double* d_llr, uint8_t* d_cha, uint8_t* d_msg) {
+  int rc = check_decode_args(h, n_frames, d_llr, d_cha, d_msg);
+  if (rc) return rc;
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  size_t cnt = (size_t)n_frames * h->m.nvar;
+  if (!cnt) return LUTLDPC_OK;
+  CKH(launch_quantize(d_llr, cnt, h->d_qb_cha.p, (int)h->m.qb_Cha.size(), h->d_qb_msg.p, (int)h->m.qb_Msg.size(),
+                      h->d_cha2msg.p, h->init_mode == LUTLDPC_INIT_QCHA, d_cha, d_msg, h->stream), "quantize");
   return LUTLDPC_OK;
 }
 

@@ -17,6 +17,7 @@ lutldpc_decoder::~lutldpc_decoder() {
   if (h_active) cudaFreeHost(h_active);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
+  for (cudaEvent_t e : evpool) cudaEventDestroy(e);
 }
 
 int lutldpc_decoder::cuda_fail(cudaError_t e, const char* where) {
@@ -141,6 +142,36 @@ int lutldpc_decoder::init_device() {
   return LUTLDPC_OK;
 }
 
+// profiling mode: one event after every launch; launch i took ev[i] - ev[i-1]
+void lutldpc_decoder::launched(int kind) {
+  ++launches;
+  if (!profiling) return;
+  if (evn == (int)evpool.size()) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    evpool.push_back(e);
+    evkind.push_back(0);
+  }
+  evkind[evn] = kind;
+  cudaEventRecord(evpool[evn], stream);
+  ++evn;
+}
+
+int lutldpc_decoder::flush_profile() {
+  if (evn > 0) {
+    CK(cudaEventSynchronize(evpool[evn - 1]), "profile sync");
+    for (int i = 1; i < evn; ++i) {
+      if (evkind[i] < 0) continue;
+      float ms = 0;
+      CK(cudaEventElapsedTime(&ms, evpool[i - 1], evpool[i]), "profile elapsed");
+      prof_ms[evkind[i]] += ms;
+      prof_n[evkind[i]] += 1;
+    }
+  }
+  evn = 0;
+  return LUTLDPC_OK;
+}
+
 int lutldpc_decoder::max_batch_frames() const {
   // bound the resident batch to ~16 GiB of message state
   double per_frame = m.num_edges / 2.0 + m.nvar / 2.0 + m.nvar / 8.0 + 8;
@@ -170,15 +201,18 @@ int lutldpc_decoder::begin_batch(int n_frames) {
   int rc = ensure_batch(n_frames);
   if (rc) return rc;
   launches = 0;
+  if (profiling && (rc = flush_profile())) return rc;
   CK(cudaEventRecord(ev0, stream), "event");
-  CK(launch_reset_flags(b, stream), "reset_flags"); ++launches;
+  launched(-1);
+  --launches;
+  CK(launch_reset_flags(b, stream), "reset_flags"); launched(KIND_RESET);
   return LUTLDPC_OK;
 }
 
 int lutldpc_decoder::run_batch(int n_frames, const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, TraceSink* tr) {
   int rc = begin_batch(n_frames);
   if (rc) return rc;
-  CK(launch_pack(d_cha_lab, d_msg_lab, g, b, m.Nq_Cha, m.Nq_Msg[0], stream), "pack"); ++launches;
+  CK(launch_pack(d_cha_lab, d_msg_lab, g, b, m.Nq_Cha, m.Nq_Msg[0], stream), "pack"); launched(KIND_PACK);
   return run_passes(tr);
 }
 
@@ -221,9 +255,9 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   bool all_done = false;
   if (tr) tr->live = true;
   if (pisc) {  // :277
-    CK(launch_syndrome(g, b, st), "syndrome"); ++launches;
-    CK(launch_finalize(FIN_INIT, 0, b, st), "finalize"); ++launches;
-    if (tr) { bool d; if ((rc = traced_frame_done(d))) return rc; if (d) tr->live = false; }
+    CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
+    CK(launch_finalize(FIN_INIT, 0, b, st), "finalize"); launched(KIND_FINALIZE);
+    if (tr) { bool d = false; if ((rc = traced_frame_done(d))) return rc; if (d) tr->live = false; }
     if ((rc = poll(all_done))) return rc;
   }
   if ((rc = record(LUTLDPC_TRACE_INIT, -1, m.Nq_Msg[0]))) return rc;
@@ -233,19 +267,19 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     const int want = psc && ii > 0;
     // check-node pass (:304-310); its sign parities complete the early-exit test of VN pass ii-1
     if (m.minLUT) {
-      CK(launch_cn_minsum(g, b, code_bits(m.Nq_Msg[ii]), want, st), "cn_minsum"); ++launches;
+      CK(launch_cn_minsum(g, b, code_bits(m.Nq_Msg[ii]), want, st), "cn_minsum"); launched(KIND_CN);
     } else {
       for (int c = 0; c < ncc; ++c) {
         const ProgRef& r = chk_progs[(size_t)t * ncc + c];
         NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, cn_classes[c].list.p, cn_classes[c].n};
-        CK(launch_node(NODE_CHK, nl, g, b, want, st), "chk_lut"); ++launches;
+        CK(launch_node(NODE_CHK, nl, g, b, want, st), "chk_lut"); launched(KIND_CHK0 + std::min(c, 15));
       }
     }
     if ((rc = record(LUTLDPC_TRACE_CN, ii, m.Nq_Msg[ii]))) return rc;
     if (want) {  // psc: VN pass ii-1 unanimous and syndrome zero -> return ii (:327)
-      CK(launch_finalize(FIN_ITER, ii, b, st), "finalize"); ++launches;
+      CK(launch_finalize(FIN_ITER, ii, b, st), "finalize"); launched(KIND_FINALIZE);
       if (tr && tr->live) {
-        bool d;
+        bool d = false;
         if ((rc = traced_frame_done(d))) return rc;
         if (d) {  // the reference returned before dumping VN(ii-1) and never ran CN(ii)
           tr->n_rec = std::max(0, tr->n_rec - 2);
@@ -262,7 +296,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
         if (!vn_classes[c].n) continue;
         const ProgRef& r = var_progs[(size_t)t * nvc + c];
         NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
-        CK(launch_node(NODE_VAR, nl, g, b, psc, st), "var_lut"); ++launches;
+        CK(launch_node(NODE_VAR, nl, g, b, psc, st), "var_lut"); launched(KIND_VN0 + std::min(c, 15));
       }
       if ((rc = record(LUTLDPC_TRACE_VN, ii, m.Nq_Msg[ii + 1]))) return rc;
     } else if ((rc = record(LUTLDPC_TRACE_VN, ii, m.Nq_Msg[ii]))) {  // the reference dumps here too (:331)
@@ -275,10 +309,10 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
       if (!vn_classes[c].n) continue;
       const ProgRef& r = var_progs[(size_t)t * nvc + c];
       NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
-      CK(launch_node(NODE_DEC, nl, g, b, 0, st), "dec_lut"); ++launches;
+      CK(launch_node(NODE_DEC, nl, g, b, 0, st), "dec_lut"); launched(KIND_DEC0 + std::min(c, 15));
     }
-    CK(launch_syndrome(g, b, st), "syndrome"); ++launches;
-    CK(launch_finalize(FIN_LAST, max_iters, b, st), "finalize"); ++launches;
+    CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
+    CK(launch_finalize(FIN_LAST, max_iters, b, st), "finalize"); launched(KIND_FINALIZE);
   }
   CK(cudaEventRecord(ev1, st), "event");
   have_stats = true;

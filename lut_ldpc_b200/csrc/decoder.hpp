@@ -12,6 +12,12 @@
 
 namespace lutldpc {
 
+enum ProfileKind {  // indices of lutldpc_get_profile
+  KIND_RESET = 0, KIND_PACK = 1, KIND_CHANNEL = 2, KIND_CN = 3, KIND_SYNDROME = 4, KIND_FINALIZE = 5,
+  KIND_UNPACK = 6, KIND_COUNT = 7, KIND_ENCODE = 8,
+  KIND_VN0 = 16, KIND_DEC0 = 32, KIND_CHK0 = 48  // + degree-class index
+};
+
 template <class T>
 struct DevBuf {
   T* p = nullptr;
@@ -90,6 +96,16 @@ struct lutldpc_decoder {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool have_stats = false;
   int64_t launches = 0, last_frames = 0, stat_frame_iters = -1;
+
+  // per-kernel device times (lutldpc_set_profiling)
+  bool profiling = false;
+  std::vector<cudaEvent_t> evpool;
+  std::vector<int> evkind;
+  int evn = 0;
+  double prof_ms[LUTLDPC_PROFILE_KINDS] = {0};
+  int64_t prof_n[LUTLDPC_PROFILE_KINDS] = {0};
+  void launched(int kind);
+  int flush_profile();
 
   ~lutldpc_decoder();
   int fail(int code, const std::string& msg) { err = msg; return code; }

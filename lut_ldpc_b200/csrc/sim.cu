@@ -301,13 +301,13 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
       CKL("info_bits");
       k_encode<<<dim3(N - K, gw.x), 128, 0, st>>>(h->d_gen.p, N - K, K, W, h->buf_cw.p);
       CKL("encode");
-      h->launches += 2;
+      h->launched(KIND_ENCODE);
     }
     k_channel<<<dim3(N, gw.x), 128, 0, st>>>(h->buf_cw.p, p->zero_codeword != 0, h->g.vn_edge0, N, W, nf, first, k0, k1,
                                              cp, h->d_qb_cha.p, h->d_qb_msg.p, h->d_cha2msg.p, h->b.cha, h->b.msgs,
                                              h->b.hard, h->buf_cnt.p + 5);
     CKL("channel");
-    ++h->launches;
+    h->launched(KIND_CHANNEL);
     rc = h->run_passes(nullptr);
     if (rc) return rc;
     int rows_per = 64;
@@ -316,6 +316,7 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
     CKL("count_data");
     k_count_frames<<<std::min(64, (nf + 255) / 256), 256, 0, st>>>(h->buf_ferr.p, h->b.iters, nf, K, N, h->buf_cnt.p);
     CKL("count_frames");
+    h->launched(KIND_COUNT);
     total_launches += h->launches + 2;
   }
   CKH(cudaEventRecord(e_last, st), "event");

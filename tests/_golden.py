@@ -28,6 +28,11 @@ def bundle_path(cfg):
     return _unpack(cfg + ".bundle", MANIFEST[cfg]["bundle_sha256"])
 
 
+def codec_path(cfg):
+    """The reference's own lut_codec.it for cfg (input of oracle/_ref/lutldpc_ref sim)."""
+    return _unpack(cfg + ".codec.it", MANIFEST[cfg]["codec_sha256"])
+
+
 def fixture_path(cfg, tag):
     return _unpack("%s.%s.fix" % (cfg, tag), MANIFEST[cfg]["fixtures"][tag]["sha256"])
 

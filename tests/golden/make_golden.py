@@ -3,6 +3,7 @@
 
 Runs only in the build container (needs /root/reference and oracle/_ref/lutldpc_ref, the unmodified
 reference decoder compiled by oracle/Makefile).  Everything it writes is an OUTPUT of the reference:
+  <cfg>.codec.it.xz    (bench configs only) the codec file written by the reference's save_code
   <cfg>.bundle.xz      flat decoder bundle (graph arrays, quantiser thresholds, the reference's own
                        text serialisation of its designed LUT trees)         -> oracle/ref_driver.cpp
   <cfg>.<tag>.fix.xz   frames pushed through the reference's lut_decode: quantised inputs, hard
@@ -79,6 +80,9 @@ CONFIGS = {
 }
 
 
+CODEC_FOR = ("c5_n64800", "c3_irr_n10000", "c1b_reg36_n1000")
+
+
 def sha(path):
     h = hashlib.sha256()
     with open(path, "rb") as f:
@@ -120,6 +124,9 @@ def main():
                      "bundle_sha256": sha(pre + ".bundle"), "bundle_bytes": os.path.getsize(pre + ".bundle"),
                      "init_mode": "qcha" if qcha else "cont", "fixtures": {}}
             xz(pre + ".bundle", os.path.join(HERE, name + ".bundle.xz"))
+            if name in CODEC_FOR:  # the reference's own codec file (save_code), for the timed CPU baseline
+                xz(pre + ".it", os.path.join(HERE, name + ".codec.it.xz"))
+                entry["codec_sha256"] = sha(pre + ".it")
             # with a generator the reference cannot re-load its own codec file (ref_driver.cpp note),
             # so those fixtures rebuild the decoder from the alist with the same design arguments
             src = [apath] + dargs.split() if "--gen" in dargs else [pre + ".it"]
