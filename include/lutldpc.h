@@ -65,6 +65,8 @@ typedef struct lutldpc_info {
   int64_t lookups_per_frame_iter;        /* LUT evaluations the compiled programs do per VN pass */
   int64_t lookups_per_frame_iter_naive;  /* what the reference's recursion does: sum dv*(nodes) */
   double rate;
+  int32_t n_var_programs;       /* (iteration slot, degree class) programs of the VN pass */
+  int32_t n_fast_var_programs;  /* ... of which run on the compile-time specialised kernel (vn_fast.cuh) */
 } lutldpc_info;
 
 int lutldpc_abi_version(void);

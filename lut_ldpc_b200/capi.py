@@ -30,7 +30,8 @@ def build_library(verbose=False):
 class _Info(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("nvar", "nchk", "nchk_lin_indep", "ninfo", "num_edges", "max_iters", "Nq_Cha",
                                          "min_lut", "has_gen", "n_degree_classes")] + \
-               [("lookups_per_frame_iter", C.c_int64), ("lookups_per_frame_iter_naive", C.c_int64), ("rate", C.c_double)]
+               [("lookups_per_frame_iter", C.c_int64), ("lookups_per_frame_iter_naive", C.c_int64), ("rate", C.c_double),
+                ("n_var_programs", C.c_int32), ("n_fast_var_programs", C.c_int32)]
 
 
 class _SimParams(C.Structure):

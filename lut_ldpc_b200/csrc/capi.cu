@@ -110,6 +110,12 @@ int lutldpc_get_info(const lutldpc_decoder* h, lutldpc_info* info) {
     info->lookups_per_frame_iter += h->var_progs[c].n_ops * h->vn_classes[c].n;
     info->lookups_per_frame_iter_naive += h->var_progs[c].n_naive * h->vn_classes[c].n;
   }
+  for (int t = 0; t + 1 < h->n_iter_slots; ++t)
+    for (int c = 0; c < nvc; ++c) {
+      if (!h->vn_classes[c].n) continue;
+      ++info->n_var_programs;
+      info->n_fast_var_programs += h->var_progs[(size_t)t * nvc + c].fast_dv != 0;
+    }
   return LUTLDPC_OK;
 }
 

@@ -2,6 +2,7 @@
 #include "decoder.hpp"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 
@@ -75,6 +76,7 @@ int lutldpc_decoder::init_device() {
     }
   }
 
+  if (const char* e = getenv("LUTLDPC_GENERIC_VN")) use_fast_vn = !(e[0] == '1');
   // compile every (iteration slot, degree class) tree into a node program
   n_iter_slots = m.var_trees.n_iter;
   std::vector<int> slot_first_iter(n_iter_slots, -1);
@@ -93,6 +95,8 @@ int lutldpc_decoder::init_device() {
     r.n_in = (uint32_t)p.n_in;
     r.n_ops = (int64_t)p.ops.size();
     r.n_naive = p.n_lookups_naive;
+    r.tables_off = reinterpret_cast<const DevProgHeader*>(img.data())->tables_off;
+    r.q_out = p.q_out;
     blob.insert(blob.end(), img.begin(), img.end());
   };
   var_progs.assign((size_t)n_iter_slots * nvc, ProgRef());
@@ -112,6 +116,7 @@ int lutldpc_decoder::init_device() {
         return fail(LUTLDPC_ERR_MODEL, "var tree output alphabet does not match Nq_Msg of the next iteration");
       if (dec && tr.nodes[0].K != 2) return fail(LUTLDPC_ERR_MODEL, "decision tree root must be binary");
       add_prog(p, var_progs[(size_t)t * nvc + c]);
+      if (!dec && use_fast_vn && fast_vn_matches(p)) var_progs[(size_t)t * nvc + c].fast_dv = vn_classes[c].degree;
     }
   }
   chk_progs.assign((size_t)n_iter_slots * ncc, ProgRef());
@@ -296,7 +301,9 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
         if (!vn_classes[c].n) continue;
         const ProgRef& r = var_progs[(size_t)t * nvc + c];
         NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
-        CK(launch_node(NODE_VAR, nl, g, b, psc, st), "var_lut"); launched(KIND_VN0 + std::min(c, 15));
+        if (r.fast_dv) CK(launch_vn_fast(r.fast_dv, blob + r.off + r.tables_off, r.q_out, nl, g, b, psc, st), "var_fast");
+        else CK(launch_node(NODE_VAR, nl, g, b, psc, st), "var_lut");
+        launched(KIND_VN0 + std::min(c, 15));
       }
       if ((rc = record(LUTLDPC_TRACE_VN, ii, m.Nq_Msg[ii + 1]))) return rc;
     } else if ((rc = record(LUTLDPC_TRACE_VN, ii, m.Nq_Msg[ii]))) {  // the reference dumps here too (:331)

@@ -50,6 +50,8 @@ struct ProgRef {
   size_t off = 0;  // into the program blob
   uint32_t bytes = 0, n_slots = 0, n_in = 0;
   int64_t n_ops = 0, n_naive = 0;
+  uint32_t tables_off = 0;  // of the table blob inside the image
+  int fast_dv = 0, q_out = 0;  // fast_dv != 0: the compile-time specialised kernel applies
 };
 
 struct NodeClass {  // all variable (or check) nodes of one degree slot
@@ -82,6 +84,7 @@ struct lutldpc_decoder {
   std::vector<lutldpc::ProgRef> var_progs;  // [iter slot][vn class]; last slot = decision trees
   std::vector<lutldpc::ProgRef> chk_progs;  // [iter slot][cn class]
   int n_iter_slots = 0;
+  bool use_fast_vn = true;  // LUTLDPC_GENERIC_VN=1 in the environment forces the interpreter (tests)
 
   // batch state
   lutldpc::BatchBuffers b;

@@ -7,6 +7,7 @@
 #include <cstdio>
 
 #include "core.cuh"
+#include "vn_fast.cuh"
 
 namespace lutldpc {
 
@@ -411,6 +412,101 @@ __global__ void k_quantize(const double* __restrict__ llr, size_t n, const doubl
 }
 
 // ---------------------------------------------------------------------------------------------
+// Specialised variable-node pass (vn_fast.cuh): balanced binary trees, 4-bit inputs.  Same contract
+// as k_node<NODE_VAR>; the program is compile-time, values stay in registers, the LUTs of the class
+// (128 B each, one per tree node) are staged into shared memory with one bulk copy.
+// ---------------------------------------------------------------------------------------------
+template <int DV, int II>
+struct FastStore {
+  static __device__ __forceinline__ void run(const uint32_t (&v)[DV + 1 + fastvn::Static<DV>::P.n_ops], uint32_t* row0,
+                                             size_t W, uint32_t& A, uint32_t& O) {
+    if constexpr (II < DV) {
+      const uint32_t r = v[fastvn::Static<DV>::P.out[II]];
+      row0[(size_t)II * W] = r;
+      A &= r;
+      O |= r;
+      FastStore<DV, II + 1>::run(v, row0, W, A, O);
+    }
+  }
+};
+
+template <int DV>
+__global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restrict__ tables_g,
+                                                           const int32_t* __restrict__ node_list, int n_nodes,
+                                                           int nodes_per_cta, const int32_t* __restrict__ vn_edge0,
+                                                           int W, uint32_t* __restrict__ msgs,
+                                                           const uint32_t* __restrict__ cha, uint8_t* __restrict__ hard,
+                                                           const uint32_t* __restrict__ done,
+                                                           uint32_t* __restrict__ vn_fail, int want_flags, int q_out) {
+  constexpr int NT = fastvn::Static<DV>::P.n_tables;
+  constexpr int NOPS = fastvn::Static<DV>::P.n_ops;
+  __shared__ __align__(128) uint8_t tabs[NT * 128];
+  __shared__ uint64_t bar;
+  stage_to_smem(tabs, tables_g, NT * 128, &bar);
+  const int w = blockIdx.y * kNodeThreads + threadIdx.x;
+  if (w >= W) return;
+  const uint32_t dn = done[w];
+  if (dn == kNibOnes) return;
+  const uint32_t done_byte = nib_bits_to_byte(dn, 0);
+  const int so = q_out - 1, root_shift = 4 - q_out;
+  uint32_t failacc = 0;
+  const int i0 = blockIdx.x * nodes_per_cta;
+  const int i1 = min(i0 + nodes_per_cta, n_nodes);
+  for (int i = i0; i < i1; ++i) {
+    const int node = node_list[i];
+    uint32_t* row0 = msgs + (size_t)vn_edge0[node] * W + w;
+    uint32_t v[DV + 1 + NOPS];
+#pragma unroll
+    for (int k = 0; k < DV; ++k) v[k] = row0[(size_t)k * W];
+    v[DV] = cha[(size_t)node * W + w];
+    fastvn::Exec<DV, 0>::run(v, tabs, root_shift);
+    uint32_t A = 0xFFFFFFFFu, O = 0;
+    FastStore<DV, 0>::run(v, row0, (size_t)W, A, O);
+    if (want_flags) {
+      failacc |= (A ^ O) >> so;
+      uint8_t* hp = hard + (size_t)node * W + w;
+      const uint32_t nb = nib_bits_to_byte(v[fastvn::Static<DV>::P.out[0]], so);
+      *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
+    }
+  }
+  if (want_flags) {
+    failacc &= kNibOnes;
+    if (failacc) atomicOr(&vn_fail[w], failacc);
+  }
+}
+
+#define LUTLDPC_FAST_DVS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16) X(17) X(18) X(19) X(20)
+
+static const fastvn::Prog* fast_prog(int dv) {
+  switch (dv) {
+#define X(D) case D: return &fastvn::Static<D>::P;
+    LUTLDPC_FAST_DVS(X)
+#undef X
+  }
+  return nullptr;
+}
+
+// True when the program compiled from the decoder's trees is exactly the compile-time one.
+bool fast_vn_matches(const NodeProgram& p) {
+  const fastvn::Prog* P = fast_prog(p.n_in);
+  if (!P || !p.has_cha || p.n_out != p.n_in || p.q_in != 4 || (int)p.ops.size() != P->n_ops) return false;
+  if (p.q_out < 1 || p.q_out > 4) return false;
+  for (int i = 0; i < P->n_ops; ++i) {
+    const DevOp& d = p.ops[i];
+    const fastvn::Op& f = P->ops[i];
+    if (d.n_in != 2 || d.kind != OP_NARROW || !d.sym || d.chk || d.idx_bits != 7 || d.q[0] != 4 || d.q[1] != 4) return false;
+    if (d.sh[0] != 0 || d.sh[1] != 4) return false;
+    if (d.table_off != (uint32_t)f.node * 128u) return false;
+    if (p.raw_in[i].size() != 2 || p.raw_in[i][0] != f.a || p.raw_in[i][1] != f.b) return false;
+    if ((p.raw_node[i] == 0) != f.root) return false;
+    if (d.q_out != (f.root ? p.q_out : 4)) return false;
+  }
+  for (int ii = 0; ii < p.n_in; ++ii)
+    if (p.raw_out[ii] != P->out[ii]) return false;
+  return (int)p.tables.size() >= P->n_tables * 128;
+}
+
+// ---------------------------------------------------------------------------------------------
 // launchers
 // ---------------------------------------------------------------------------------------------
 static constexpr int kMaxNodeSmem = 200 * 1024;
@@ -476,6 +572,27 @@ cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& 
   else if (mode == NODE_DEC) k_node<NODE_DEC><<<grid, kNodeThreads, smem, st>>>(NODE_ARGS);
   else k_node<NODE_CHK><<<grid, kNodeThreads, smem, st>>>(NODE_ARGS);
 #undef NODE_ARGS
+  return cudaGetLastError();
+}
+
+cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const NodeLaunch& nl, const GraphArrays& g,
+                           const BatchBuffers& b, int want_flags, cudaStream_t st) {
+  if (nl.n_nodes == 0) return cudaSuccess;
+  int ycols = cdiv(b.W, kNodeThreads);
+  int per = (int)(((long long)nl.n_nodes * ycols) / (148 * 24));
+  per = per < 1 ? 1 : (per > 32 ? 32 : per);
+  dim3 grid(cdiv(nl.n_nodes, per), ycols);
+  switch (dv) {
+#define X(D)                                                                                                       \
+  case D:                                                                                                          \
+    k_vn_fast<D><<<grid, kNodeThreads, 0, st>>>(d_tables, nl.node_list, nl.n_nodes, per, g.vn_edge0, b.W, b.msgs, \
+                                                b.cha, b.hard, b.done, b.vn_fail, want_flags, q_out);              \
+    break;
+    LUTLDPC_FAST_DVS(X)
+#undef X
+    default:
+      return cudaErrorInvalidValue;
+  }
   return cudaGetLastError();
 }
 

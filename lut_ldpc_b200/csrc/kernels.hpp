@@ -54,6 +54,11 @@ cudaError_t launch_reset_flags(const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_cn_minsum(const GraphArrays& g, const BatchBuffers& b, int q, int want_fail, cudaStream_t st);
 cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& g, const BatchBuffers& b,
                         int want_flags, cudaStream_t st);
+// compile-time specialised VN pass (vn_fast.cuh); d_tables = the program image's table blob
+struct NodeProgram;
+bool fast_vn_matches(const NodeProgram& p);
+cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const NodeLaunch& nl, const GraphArrays& g,
+                           const BatchBuffers& b, int want_flags, cudaStream_t st);
 cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_bits, cudaStream_t st);

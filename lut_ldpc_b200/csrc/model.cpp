@@ -446,6 +446,11 @@ bool compile_program(const Tree& t, int deg, ProgMode mode, int Nq_in, int Nq_ch
   }
   out.out_slot.resize(n_out);
   for (int ii = 0; ii < n_out; ++ii) out.out_slot[ii] = (uint8_t)slot[outs[ii]];
+  for (const RawOp& ro : c.ops) {
+    out.raw_node.push_back(ro.node);
+    out.raw_in.push_back(ro.in);
+  }
+  out.raw_out = outs;
   out.n_in = n_in;
   out.n_out = n_out;
   out.n_slots = n_slots;

@@ -95,6 +95,11 @@ struct NodeProgram {
   std::vector<uint8_t> out_slot;  // slot holding output ii
   std::vector<uint8_t> tables;
   int q_in = 0, q_out = 0;
+  // the program before slot allocation: value ids 0..n_in-1 = message inputs, n_in = channel label,
+  // n_in+1+i = result of op i (used to match compile-time specialised kernels, vn_fast.cuh)
+  std::vector<int> raw_node;              // tree node of op i
+  std::vector<std::vector<int>> raw_in;   // operand value ids of op i
+  std::vector<int> raw_out;               // value id of output ii
   // serialised image: header | ops | outs | tables, 16-byte aligned pieces
   std::vector<uint8_t> image() const;
 };

@@ -115,3 +115,27 @@ def test_decode_failure_and_large_code(L):
     out, it = dec.decode_quantized(cha, msg)
     assert np.array_equal(it, np.tile(fx["ret"], 130))
     assert np.array_equal(out, np.tile(fx["out"], (130, 1)))
+
+
+def test_fast_vn_path_is_used(L):
+    """The auto_bin_balanced 4-bit decoders must run on the specialised VN kernel, file trees on the interpreter."""
+    for cfg, fast in (("c5_n64800", True), ("c3_irr_n10000", True), ("c2_irr_n500", True), ("c1b_reg36_n1000", True),
+                      ("c4_reg632_high", False), ("c1a_reg632_wide", False)):
+        d = _dec(L, cfg)
+        assert d.n_var_programs > 0
+        assert (d.n_fast_var_programs == d.n_var_programs) == fast, (cfg, d.n_fast_var_programs, d.n_var_programs)
+
+
+def test_generic_interpreter_still_bit_exact(L):
+    """LUTLDPC_GENERIC_VN=1 forces the node-program interpreter for the balanced trees too."""
+    import os
+    fx = pyoracle.read_fixture(_golden.fixture_path("c2_irr_n500", "snr1.0"))
+    os.environ["LUTLDPC_GENERIC_VN"] = "1"
+    try:
+        d = L.Decoder(_golden.bundle_path("c2_irr_n500"))
+    finally:
+        del os.environ["LUTLDPC_GENERIC_VN"]
+    assert d.n_fast_var_programs == 0
+    d.set_exit_conditions(d.max_iters, 1, 1)
+    out, it = d.decode_quantized(fx["cha"], fx["msg"])
+    assert np.array_equal(it, fx["ret"]) and np.array_equal(out, fx["out"])
