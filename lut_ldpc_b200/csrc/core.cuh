@@ -74,6 +74,38 @@ LUT_HD uint32_t cn_emit(const CnAcc& a, uint32_t w, const QMask& qm) {
   return mag | ((w ^ a.par) & qm.H);
 }
 
+// Guarded variant used by the vectorised check-node kernel: min1/min2 carry the guard bit (sign-bit
+// position set) permanently, which saves the OR of every comparison; the selects below preserve it.
+struct CnAccG {
+  uint32_t min1g, min2g, par;
+};
+LUT_HD uint32_t ge_mask_g(uint32_t ag, uint32_t b, const QMask& qm) {  // ag has the guard bits set
+  uint32_t t = (ag - b) & qm.H;
+  return t - (t >> qm.s);
+}
+LUT_HD void cng_init(CnAccG& a, uint32_t w0, uint32_t w1, const QMask& qm) {
+  uint32_t x0 = w0 & qm.M, x1 = w1 & qm.M;
+  uint32_t m = ge_mask_g(x0 | qm.H, x1, qm);
+  a.min1g = ((x1 & m) | (x0 & ~m)) | qm.H;
+  a.min2g = ((x0 & m) | (x1 & ~m)) | qm.H;
+  a.par = w0 ^ w1;
+}
+LUT_HD void cng_accum(CnAccG& a, uint32_t w, const QMask& qm) {
+  uint32_t x = w & qm.M;
+  uint32_t m = ge_mask_g(a.min1g, x, qm);        // min1 >= x
+  uint32_t hi = (a.min1g & m) | (x & ~m);        // max(min1, x), guard bit clear (m covers magnitudes only)
+  a.min1g = (x & m) | (a.min1g & ~m);            // guard bit kept from min1g
+  uint32_t m2 = ge_mask_g(a.min2g, hi, qm);
+  a.min2g = (hi & m2) | (a.min2g & ~m2);
+  a.par ^= w;
+}
+LUT_HD uint32_t cng_emit(const CnAccG& a, uint32_t w, const QMask& qm) {
+  uint32_t x = w & qm.M;
+  uint32_t me = ge_mask_g(a.min1g, x, qm);       // x == min1
+  uint32_t mag = (a.min2g & me) | (a.min1g & ~me);   // bit H set (guards) -> replaced by the sign below
+  return (mag & qm.M) | ((w ^ a.par) & qm.H);
+}
+
 // Gathers bit `pos` of every nibble into the low byte (bit j = frame j).
 LUT_HD uint32_t nib_bits_to_byte(uint32_t x, int pos) {
   x = (x >> pos) & kNibOnes;

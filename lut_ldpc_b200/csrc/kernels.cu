@@ -5,6 +5,7 @@
 #include "kernels.hpp"
 
 #include <cstdio>
+#include <cstdlib>
 
 #include "core.cuh"
 #include "vn_fast.cuh"
@@ -65,6 +66,17 @@ __device__ __forceinline__ void stage_to_smem(void* dst, const void* src, uint32
     }
   }
   mbar_wait(bar, 0);
+}
+
+// OR `f` into a per-word flag that thousands of threads of the same pass target: look first (L2) and
+// only issue the atomic when it would set a new bit.  Flags only ever gain bits within a pass, so a
+// stale read can cost an extra atomic but never lose one.  Without this, the 32400 checks of the
+// N=64800 code all hit the same few hundred addresses and the pass is bound by L2 atomic serialisation.
+__device__ __forceinline__ void flag_or(uint32_t* p, uint32_t f) {
+  if (f) {
+    const uint32_t cur = __ldcg(p);
+    if (f & ~cur) atomicOr(p, f);
+  }
 }
 
 // label -> storage code for one byte label (model.hpp)
@@ -192,7 +204,67 @@ __global__ void __launch_bounds__(128) k_cn_minsum(const int32_t* __restrict__ c
     if (k < dc) msgs[(size_t)idx[k] * W + w] = cn_emit(a, x[k], qm);
   if (want_fail) {
     uint32_t f = (a.par >> qm.s) & kNibOnes;
-    if (f) atomicOr(&cn_fail[w], f);
+    flag_or(&cn_fail[w], f);
+  }
+}
+
+// Vectorised variant: each thread owns VEC consecutive words (8*VEC frames) of one check, so a warp
+// moves 128*VEC contiguous bytes per edge row and keeps dc*VEC independent 4-byte loads in flight.
+template <int VEC> struct WordVec;
+template <> struct WordVec<1> { typedef uint32_t T; };
+template <> struct WordVec<2> { typedef uint2 T; };
+template <> struct WordVec<4> { typedef uint4 T; };
+
+template <int MAXDC, int VEC>
+__global__ void __launch_bounds__(128) k_cn_minsum_v(const int32_t* __restrict__ cn_start,
+                                                     const int32_t* __restrict__ cn_msg_idx, int nchk, int W, int q,
+                                                     uint32_t* __restrict__ msgs, const uint32_t* __restrict__ done,
+                                                     uint32_t* __restrict__ cn_fail, int want_fail) {
+  typedef typename WordVec<VEC>::T V;
+  const int c = blockIdx.x;
+  const int w = (blockIdx.y * blockDim.x + threadIdx.x) * VEC;
+  if (w >= W) return;
+  union U { V v; uint32_t u[VEC]; };
+  U dn;
+  dn.v = *reinterpret_cast<const V*>(done + w);
+  bool all_done = true;
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) all_done &= dn.u[j] == kNibOnes;
+  if (all_done) return;
+  const QMask qm = make_qmask(q);
+  const int s = cn_start[c], dc = cn_start[c + 1] - s;
+  const int32_t* idx = cn_msg_idx + s;
+  int row[MAXDC];
+#pragma unroll
+  for (int k = 0; k < MAXDC; ++k)
+    if (k < dc) row[k] = idx[k];
+  U x[MAXDC];
+#pragma unroll
+  for (int k = 0; k < MAXDC; ++k)
+    if (k < dc) x[k].v = __ldcs(reinterpret_cast<const V*>(msgs + (size_t)row[k] * W + w));
+  CnAccG a[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) cng_init(a[j], x[0].u[j], x[1].u[j], qm);
+#pragma unroll
+  for (int k = 2; k < MAXDC; ++k)
+    if (k < dc) {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) cng_accum(a[j], x[k].u[j], qm);
+    }
+#pragma unroll
+  for (int k = 0; k < MAXDC; ++k)
+    if (k < dc) {
+      U o;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) o.u[j] = cng_emit(a[j], x[k].u[j], qm);
+      __stcs(reinterpret_cast<V*>(msgs + (size_t)row[k] * W + w), o.v);
+    }
+  if (want_fail) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      uint32_t f = (a[j].par >> qm.s) & kNibOnes;
+      flag_or(&cn_fail[w + j], f);
+    }
   }
 }
 
@@ -218,7 +290,7 @@ __global__ void __launch_bounds__(128) k_cn_minsum_any(const int32_t* __restrict
   }
   if (want_fail) {
     uint32_t f = (a.par >> qm.s) & kNibOnes;
-    if (f) atomicOr(&cn_fail[w], f);
+    flag_or(&cn_fail[w], f);
   }
 }
 
@@ -303,7 +375,7 @@ __global__ void __launch_bounds__(kNodeThreads) k_node(const uint8_t* __restrict
   }
   if (want_flags && MODE != NODE_DEC) {
     failacc &= kNibOnes;
-    if (failacc) atomicOr(&fail[w], failacc);
+    flag_or(&fail[w], failacc);
   }
 }
 
@@ -319,7 +391,7 @@ __global__ void __launch_bounds__(128) k_syndrome(const int32_t* __restrict__ cn
   const int s = cn_start[c], e = cn_start[c + 1];
   uint32_t x = 0;
   for (int k = s; k < e; ++k) x ^= hard[(size_t)chk_equ_idx[k] * W + w];
-  if (x) atomicOr(&syn_fail[w], byte_to_nib_bits(x));
+  if (x) flag_or(&syn_fail[w], byte_to_nib_bits(x));
 }
 
 // Per-frame bookkeeping between passes (single CTA; W is at most a few thousand words).
@@ -471,7 +543,7 @@ __global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restr
   }
   if (want_flags) {
     failacc &= kNibOnes;
-    if (failacc) atomicOr(&vn_fail[w], failacc);
+    flag_or(&vn_fail[w], failacc);
   }
 }
 
@@ -542,9 +614,25 @@ cudaError_t launch_reset_flags(const BatchBuffers& b, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
+}
+
 cudaError_t launch_cn_minsum(const GraphArrays& g, const BatchBuffers& b, int q, int want_fail, cudaStream_t st) {
-  dim3 grid(g.nchk, cdiv(b.W, 128));
+  static const int vec = env_int("LUTLDPC_CN_VEC", 2);  // words per thread (tuning knob, 0 = scalar kernel)
 #define CN_ARGS g.cn_start, g.cn_msg_idx, g.nchk, b.W, q, b.msgs, b.done, b.cn_fail, want_fail
+  if (vec == 2 || vec == 4) {
+    dim3 grid(g.nchk, cdiv(b.W, 128 * vec));
+#define CN_V(M)                                                        \
+  if (vec == 2) k_cn_minsum_v<M, 2><<<grid, 128, 0, st>>>(CN_ARGS);    \
+  else k_cn_minsum_v<M, 4><<<grid, 128, 0, st>>>(CN_ARGS);
+    if (g.max_dc <= 8) { CN_V(8) return cudaGetLastError(); }
+    if (g.max_dc <= 10) { CN_V(10) return cudaGetLastError(); }
+    if (g.max_dc <= 16) { CN_V(16) return cudaGetLastError(); }
+#undef CN_V
+  }
+  dim3 grid(g.nchk, cdiv(b.W, 128));
   if (g.max_dc <= 8) k_cn_minsum<8><<<grid, 128, 0, st>>>(CN_ARGS);
   else if (g.max_dc <= 12) k_cn_minsum<12><<<grid, 128, 0, st>>>(CN_ARGS);
   else if (g.max_dc <= 16) k_cn_minsum<16><<<grid, 128, 0, st>>>(CN_ARGS);

@@ -28,6 +28,7 @@ def lib():
         L.emul_stats.argtypes = [C.c_void_p, C.c_void_p]
         L.emul_decode.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
                                   C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.emul_cng_selftest.argtypes = [C.c_int, C.c_uint32]
         _lib = L
     return _lib
 

@@ -97,6 +97,30 @@ void emul_stats(void* h, int64_t* stats) {
   }
 }
 
+// The guarded min-sum variant (vectorised CN kernel) against the plain one on random code words.
+// Returns the number of mismatches.
+int emul_cng_selftest(int trials, uint32_t seed) {
+  auto rnd = [&]() { seed = seed * 1664525u + 1013904223u; return seed; };
+  int bad = 0;
+  for (int t = 0; t < trials; ++t) {
+    int q = 1 + (int)(rnd() >> 8) % 4, dc = 2 + (int)(rnd() >> 8) % 14;
+    QMask qm = make_qmask(q);
+    uint32_t keep = (kNibOnes << q) - kNibOnes;  // only q-bit codes occur
+    uint32_t w[16];
+    for (int k = 0; k < dc; ++k) {
+      uint32_t a = rnd(), b = rnd();
+      w[k] = ((a << 16) ^ (b >> 4) ^ (t % 5 == 0 ? 0 : a)) & keep;
+      if (t % 7 == 0) w[k] &= w[0];  // provoke ties
+    }
+    CnAcc a; CnAccG g;
+    cn_init(a, w[0], w[1], qm); cng_init(g, w[0], w[1], qm);
+    for (int k = 2; k < dc; ++k) { cn_accum(a, w[k], qm); cng_accum(g, w[k], qm); }
+    for (int k = 0; k < dc; ++k) bad += cn_emit(a, w[k], qm) != cng_emit(g, w[k], qm);
+    bad += ((a.par ^ g.par) & qm.H) != 0;
+  }
+  return bad;
+}
+
 // Same contract as lutldpc_decode_quantized_traced.
 int emul_decode(void* h, int F, const uint8_t* cha_lab, const uint8_t* msg_lab, int psc, int pisc, uint8_t* out_bits,
                 int32_t* iters, int trace_frame, uint8_t* tmsgs, int32_t* tkind, int32_t* titer, int max_rec,

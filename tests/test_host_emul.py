@@ -30,3 +30,8 @@ def test_program_sharing_reduces_lookups():
     ops, naive = em.stats()
     assert naive == 952522          # sum dv*(dv-1) for the N=64800 code
     assert ops < naive
+
+
+def test_guarded_minsum_equals_plain():
+    """core.cuh: the guard-bit min-sum used by the vectorised CN kernel == the plain SWAR min-sum."""
+    assert _emul.lib().emul_cng_selftest(200000, 12345) == 0
