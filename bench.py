@@ -108,6 +108,8 @@ def run_b200(args):
     F = args.frames or frames_def
     dec = L.Decoder(_golden.bundle_path(cfg))
     dec.set_exit_conditions(dec.max_iters, True, True)
+    if os.environ.get("LUTLDPC_POLL"):
+        dec.set_poll_interval(int(os.environ["LUTLDPC_POLL"]))
     stream = torch.cuda.Stream()
     dec.set_stream(stream.cuda_stream)
     K, N, E = dec.ninfo, dec.nvar, dec.num_edges
@@ -188,6 +190,7 @@ def run_b200(args):
                 "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms_per_launch": round(dom_ms / max(1, prof[dom][1]), 4),
                 "whole_step_algorithmic_gbs": round(step_gbs, 1), "whole_step_frac": round(step_gbs / peak, 4),
+                "profile_ms": {k: round(v[0], 3) for k, v in prof.items()},
                 "kernel_share_of_step": {k: round(v[0] / sum(x[0] for x in prof.values()), 4) for k, v in prof.items()}}
 
     # ---- end to end through the host-buffer C-ABI call (pinned host memory)

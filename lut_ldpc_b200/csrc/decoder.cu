@@ -64,6 +64,27 @@ int lutldpc_decoder::init_device() {
       CK(vn_classes[c].list.upload(lists[c]), "upload vn class list");
     }
   }
+  if (m.minLUT) {  // min-sum: checks grouped by exact degree, edge rows stored back to back
+    std::map<int, std::vector<int32_t>> rows;
+    bool ok = true;
+    for (int c = 0; c < m.nchk; ++c) {
+      ok &= cn_exact_supported(m.dc[c]);
+      std::vector<int32_t>& r = rows[m.dc[c]];
+      r.insert(r.end(), m.cn_msg_idx.begin() + m.cn_start[c], m.cn_msg_idx.begin() + m.cn_start[c + 1]);
+    }
+    const char* e = getenv("LUTLDPC_CN_GENERIC");
+    use_cn_exact = ok && !(e && e[0] == '1');
+    if (use_cn_exact) {
+      cn_exact = std::vector<NodeClass>(rows.size());
+      int i = 0;
+      for (auto& kv : rows) {
+        cn_exact[i].degree = kv.first;
+        cn_exact[i].n = (int)(kv.second.size() / kv.first);
+        CK(cn_exact[i].list.upload(kv.second), "upload cn rows");
+        ++i;
+      }
+    }
+  }
   int ncc = m.minLUT ? 0 : m.chk_trees.n_deg;
   cn_classes = std::vector<NodeClass>(ncc);
   if (ncc) {
@@ -271,7 +292,12 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     const int t = m.var_tree_idx_iter[ii];
     const int want = psc && ii > 0;
     // check-node pass (:304-310); its sign parities complete the early-exit test of VN pass ii-1
-    if (m.minLUT) {
+    if (m.minLUT && use_cn_exact) {
+      for (auto& cl : cn_exact) {
+        CK(launch_cn_exact(cl.degree, cl.list.p, cl.n, b, code_bits(m.Nq_Msg[ii]), want, st), "cn_exact");
+        launched(KIND_CN);
+      }
+    } else if (m.minLUT) {
       CK(launch_cn_minsum(g, b, code_bits(m.Nq_Msg[ii]), want, st), "cn_minsum"); launched(KIND_CN);
     } else {
       for (int c = 0; c < ncc; ++c) {

@@ -81,6 +81,8 @@ struct lutldpc_decoder {
   lutldpc::DevBuf<uint8_t> d_prog_blob, d_gen;
   lutldpc::GraphArrays g;
   std::vector<lutldpc::NodeClass> vn_classes, cn_classes;
+  std::vector<lutldpc::NodeClass> cn_exact;  // min-sum: checks grouped by degree, list = edge rows [n][degree]
+  bool use_cn_exact = false;
   std::vector<lutldpc::ProgRef> var_progs;  // [iter slot][vn class]; last slot = decision trees
   std::vector<lutldpc::ProgRef> chk_progs;  // [iter slot][cn class]
   int n_iter_slots = 0;

@@ -268,6 +268,52 @@ __global__ void __launch_bounds__(128) k_cn_minsum_v(const int32_t* __restrict__
   }
 }
 
+// Exact-degree variant: all checks of one launch have degree DC and their edge rows are stored back to
+// back (rows[i*DC + k]), so the load chain is rows -> messages (no cn_start / predication) and the
+// whole pass is straight-line code.
+template <int DC, int VEC>
+__global__ void __launch_bounds__(128) k_cn_exact(const int32_t* __restrict__ rows, int W, int q,
+                                                  uint32_t* __restrict__ msgs, const uint32_t* __restrict__ done,
+                                                  uint32_t* __restrict__ cn_fail, int want_fail) {
+  typedef typename WordVec<VEC>::T V;
+  const int w = (blockIdx.y * blockDim.x + threadIdx.x) * VEC;
+  if (w >= W) return;
+  union U { V v; uint32_t u[VEC]; };
+  U dn;
+  dn.v = *reinterpret_cast<const V*>(done + w);
+  bool all_done = true;
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) all_done &= dn.u[j] == kNibOnes;
+  if (all_done) return;
+  const QMask qm = make_qmask(q);
+  const int32_t* r = rows + (size_t)blockIdx.x * DC;
+  uint32_t* p[DC];
+#pragma unroll
+  for (int k = 0; k < DC; ++k) p[k] = msgs + (size_t)r[k] * W + w;
+  U x[DC];
+#pragma unroll
+  for (int k = 0; k < DC; ++k) x[k].v = __ldcs(reinterpret_cast<const V*>(p[k]));
+  CnAccG a[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) cng_init(a[j], x[0].u[j], x[1].u[j], qm);
+#pragma unroll
+  for (int k = 2; k < DC; ++k) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) cng_accum(a[j], x[k].u[j], qm);
+  }
+#pragma unroll
+  for (int k = 0; k < DC; ++k) {
+    U o;
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) o.u[j] = cng_emit(a[j], x[k].u[j], qm);
+    __stcs(reinterpret_cast<V*>(p[k]), o.v);
+  }
+  if (want_fail) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) flag_or(&cn_fail[w + j], (a[j].par >> qm.s) & kNibOnes);
+  }
+}
+
 // any degree (up to the reference's max_cnd = 200, src/LDPC_Code_LUT.hpp:363): second pass re-reads
 __global__ void __launch_bounds__(128) k_cn_minsum_any(const int32_t* __restrict__ cn_start,
                                                        const int32_t* __restrict__ cn_msg_idx, int nchk, int W,
@@ -639,6 +685,28 @@ cudaError_t launch_cn_minsum(const GraphArrays& g, const BatchBuffers& b, int q,
   else if (g.max_dc <= 32) k_cn_minsum<32><<<grid, 128, 0, st>>>(CN_ARGS);
   else k_cn_minsum_any<<<grid, 128, 0, st>>>(CN_ARGS);
 #undef CN_ARGS
+  return cudaGetLastError();
+}
+
+#define LUTLDPC_EXACT_DCS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
+bool cn_exact_supported(int dc) { return dc >= 2 && dc <= 16; }
+
+cudaError_t launch_cn_exact(int dc, const int32_t* d_rows, int n_checks, const BatchBuffers& b, int q, int want_fail,
+                            cudaStream_t st) {
+  if (n_checks == 0) return cudaSuccess;
+  static const int vec = env_int("LUTLDPC_CN_VEC", 2) == 4 ? 4 : 2;
+  dim3 grid(n_checks, cdiv(b.W, 128 * vec));
+  switch (dc) {
+#define X(D)                                                                                                  \
+  case D:                                                                                                     \
+    if (vec == 2) k_cn_exact<D, 2><<<grid, 128, 0, st>>>(d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail); \
+    else k_cn_exact<D, 4><<<grid, 128, 0, st>>>(d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail);          \
+    break;
+    LUTLDPC_EXACT_DCS(X)
+#undef X
+    default:
+      return cudaErrorInvalidValue;
+  }
   return cudaGetLastError();
 }
 

@@ -52,6 +52,10 @@ cudaError_t launch_pack(const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, cons
                         const BatchBuffers& b, int Nq_cha, int Nq_msg, cudaStream_t st);
 cudaError_t launch_reset_flags(const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_cn_minsum(const GraphArrays& g, const BatchBuffers& b, int q, int want_fail, cudaStream_t st);
+// exact-degree min-sum pass over the checks whose edge rows are listed back to back in d_rows
+bool cn_exact_supported(int dc);
+cudaError_t launch_cn_exact(int dc, const int32_t* d_rows, int n_checks, const BatchBuffers& b, int q, int want_fail,
+                            cudaStream_t st);
 cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& g, const BatchBuffers& b,
                         int want_flags, cudaStream_t st);
 // compile-time specialised VN pass (vn_fast.cuh); d_tables = the program image's table blob
