@@ -177,6 +177,8 @@ def run_b200(args):
     per_frame_iter = {"cn_minsum": float(E)}
     for d, n in zip(dec.vn_class_degree, dec.vn_class_nodes):
         per_frame_iter["vn_dv%d" % d] = n * (d + 0.5 + 0.125)   # dv nibbles in+out, channel nibble, hard-bit byte
+    # the fused launch runs every specialised class: all their nodes in one kernel
+    per_frame_iter["vn_fused"] = sum(v for k, v in per_frame_iter.items() if k.startswith("vn_dv"))
     units = {"cn_minsum": sum_iters}
     alg = per_frame_iter.get(dom, 0.0) * units.get(dom, vn_passes) * args.steps
     dom_ms = prof[dom][0]

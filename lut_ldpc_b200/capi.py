@@ -249,7 +249,9 @@ class Decoder:
                 name = PROFILE_NAMES.get(k, "kind%d" % k)
             else:
                 name = "%s_c%d" % (("vn", "dec", "chk")[k // 16 - 1], k % 16)
-                if k < 48:
+                if k == 31:
+                    name = "vn_fused"
+                elif k < 48:
                     name = "%s_dv%d" % (("vn", "dec")[k // 16 - 1], deg[k % 16])
             out[name] = (float(ms[k]), int(n[k]))
         self.vn_class_degree = [int(d) for d in deg if d]

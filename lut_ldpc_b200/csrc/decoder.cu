@@ -140,6 +140,35 @@ int lutldpc_decoder::init_device() {
       if (!dec && use_fast_vn && fast_vn_matches(p)) var_progs[(size_t)t * nvc + c].fast_dv = vn_classes[c].degree;
     }
   }
+  {  // fused VN launch plan: classes whose program is the specialised one in every iteration slot
+    const char* e = getenv("LUTLDPC_VN_UNFUSED");
+    bool want = !(e && e[0] == '1');
+    std::vector<std::pair<double, int4>> tiles;
+    for (int c = 0; c < nvc && want; ++c) {
+      if (!vn_classes[c].n) continue;
+      bool all_fast = true;
+      for (int t = 0; t + 1 < n_iter_slots; ++t) all_fast &= var_progs[(size_t)t * nvc + c].fast_dv != 0;
+      if (!all_fast || n_iter_slots < 2 || fused_classes.size() >= 8 || vn_classes[c].degree > 20) continue;
+      int j = (int)fused_classes.size();
+      fused_classes.push_back(c);
+      fused_max_dv = std::max(fused_max_dv, vn_classes[c].degree);
+      int ops = (int)var_progs[c].n_ops;
+      int per = std::max(1, 64 / std::max(1, ops));
+      int nt = (vn_classes[c].n + per - 1) / per;
+      for (int i = 0; i < nt; ++i)
+        tiles.push_back({(i + 0.5) / nt, make_int4(j, i * per, std::min(per, vn_classes[c].n - i * per), 0)});
+    }
+    if (fused_classes.size() < 2) fused_classes.clear();  // a single class gains nothing from fusion
+    else {
+      std::stable_sort(tiles.begin(), tiles.end(), [](const std::pair<double, int4>& a, const std::pair<double, int4>& b2) {
+        return a.first < b2.first;
+      });
+      std::vector<int4> flat;
+      for (auto& t : tiles) flat.push_back(t.second);
+      n_fused_tiles = (int)flat.size();
+      CK(d_fused_tiles.upload(flat), "upload fused tiles");
+    }
+  }
   chk_progs.assign((size_t)n_iter_slots * ncc, ProgRef());
   for (int t = 0; t < n_iter_slots && ncc; ++t) {
     int ii = slot_first_iter[t];
@@ -323,8 +352,20 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
       }
     }
     if (ii != max_iters - 1) {  // variable-node pass (:320-325)
+      if (!fused_classes.empty()) {
+        FusedVnParams P;
+        memset(&P, 0, sizeof P);
+        for (size_t j = 0; j < fused_classes.size(); ++j) {
+          const int c = fused_classes[j];
+          const ProgRef& r = var_progs[(size_t)t * nvc + c];
+          P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].list.p, r.fast_dv, r.q_out};
+        }
+        CK(launch_vn_fused(P, fused_max_dv, d_fused_tiles.p, n_fused_tiles, g, b, psc, st), "var_fused");
+        launched(KIND_VN0 + 15);
+      }
       for (int c = 0; c < nvc; ++c) {
         if (!vn_classes[c].n) continue;
+        if (std::find(fused_classes.begin(), fused_classes.end(), c) != fused_classes.end()) continue;
         const ProgRef& r = var_progs[(size_t)t * nvc + c];
         NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
         if (r.fast_dv) CK(launch_vn_fast(r.fast_dv, blob + r.off + r.tables_off, r.q_out, nl, g, b, psc, st), "var_fast");

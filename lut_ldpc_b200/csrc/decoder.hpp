@@ -83,6 +83,10 @@ struct lutldpc_decoder {
   std::vector<lutldpc::NodeClass> vn_classes, cn_classes;
   std::vector<lutldpc::NodeClass> cn_exact;  // min-sum: checks grouped by degree, list = edge rows [n][degree]
   bool use_cn_exact = false;
+  // fused VN launch: the classes that run on the specialised kernel, and their interleaved tiles
+  std::vector<int> fused_classes;
+  lutldpc::DevBuf<int4> d_fused_tiles;
+  int n_fused_tiles = 0, fused_max_dv = 0;
   std::vector<lutldpc::ProgRef> var_progs;  // [iter slot][vn class]; last slot = decision trees
   std::vector<lutldpc::ProgRef> chk_progs;  // [iter slot][cn class]
   int n_iter_slots = 0;

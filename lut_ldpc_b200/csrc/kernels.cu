@@ -548,28 +548,15 @@ struct FastStore {
   }
 };
 
+// per-thread work of the specialised VN pass: nodes [i0, i1) of node_list, word column w
 template <int DV>
-__global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restrict__ tables_g,
-                                                           const int32_t* __restrict__ node_list, int n_nodes,
-                                                           int nodes_per_cta, const int32_t* __restrict__ vn_edge0,
-                                                           int W, uint32_t* __restrict__ msgs,
-                                                           const uint32_t* __restrict__ cha, uint8_t* __restrict__ hard,
-                                                           const uint32_t* __restrict__ done,
-                                                           uint32_t* __restrict__ vn_fail, int want_flags, int q_out) {
-  constexpr int NT = fastvn::Static<DV>::P.n_tables;
+__device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int32_t* __restrict__ node_list, int i0, int i1,
+                                             const int32_t* __restrict__ vn_edge0, int W, int w,
+                                             uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
+                                             uint8_t* __restrict__ hard, uint32_t done_byte, int want_flags, int q_out,
+                                             uint32_t& failacc) {
   constexpr int NOPS = fastvn::Static<DV>::P.n_ops;
-  __shared__ __align__(128) uint8_t tabs[NT * 128];
-  __shared__ uint64_t bar;
-  stage_to_smem(tabs, tables_g, NT * 128, &bar);
-  const int w = blockIdx.y * kNodeThreads + threadIdx.x;
-  if (w >= W) return;
-  const uint32_t dn = done[w];
-  if (dn == kNibOnes) return;
-  const uint32_t done_byte = nib_bits_to_byte(dn, 0);
   const int so = q_out - 1, root_shift = 4 - q_out;
-  uint32_t failacc = 0;
-  const int i0 = blockIdx.x * nodes_per_cta;
-  const int i1 = min(i0 + nodes_per_cta, n_nodes);
   for (int i = i0; i < i1; ++i) {
     const int node = node_list[i];
     uint32_t* row0 = msgs + (size_t)vn_edge0[node] * W + w;
@@ -587,10 +574,29 @@ __global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restr
       *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
     }
   }
-  if (want_flags) {
-    failacc &= kNibOnes;
-    flag_or(&vn_fail[w], failacc);
-  }
+}
+
+template <int DV>
+__global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restrict__ tables_g,
+                                                           const int32_t* __restrict__ node_list, int n_nodes,
+                                                           int nodes_per_cta, const int32_t* __restrict__ vn_edge0,
+                                                           int W, uint32_t* __restrict__ msgs,
+                                                           const uint32_t* __restrict__ cha, uint8_t* __restrict__ hard,
+                                                           const uint32_t* __restrict__ done,
+                                                           uint32_t* __restrict__ vn_fail, int want_flags, int q_out) {
+  constexpr int NT = fastvn::Static<DV>::P.n_tables;
+  __shared__ __align__(128) uint8_t tabs[NT * 128];
+  __shared__ uint64_t bar;
+  stage_to_smem(tabs, tables_g, NT * 128, &bar);
+  const int w = blockIdx.y * kNodeThreads + threadIdx.x;
+  if (w >= W) return;
+  const uint32_t dn = done[w];
+  if (dn == kNibOnes) return;
+  uint32_t failacc = 0;
+  const int i0 = blockIdx.x * nodes_per_cta;
+  vn_fast_body<DV>(tabs, node_list, i0, min(i0 + nodes_per_cta, n_nodes), vn_edge0, W, w, msgs, cha, hard,
+                   nib_bits_to_byte(dn, 0), want_flags, q_out, failacc);
+  if (want_flags) flag_or(&vn_fail[w], failacc & kNibOnes);
 }
 
 #define LUTLDPC_FAST_DVS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16) X(17) X(18) X(19) X(20)
@@ -602,6 +608,39 @@ static const fastvn::Prog* fast_prog(int dv) {
 #undef X
   }
   return nullptr;
+}
+
+// All specialised degree classes of one VN pass in ONE launch.  A tile = a few nodes of one class; the
+// host interleaves the tiles of the classes (FusedVnPlan), so CTAs that are bound by HBM latency
+// (dv 2, 3) and CTAs that are bound by shared-memory look-ups (dv 8 ...) are resident on an SM together.
+template <int MAXDV>
+__global__ void __launch_bounds__(kNodeThreads) k_vn_fused(FusedVnParams P, const int4* __restrict__ tiles,
+                                                            const int32_t* __restrict__ vn_edge0, int W,
+                                                            uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
+                                                            uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
+                                                            uint32_t* __restrict__ vn_fail, int want_flags) {
+  __shared__ __align__(128) uint8_t tabs[(MAXDV - 1) * 128];
+  __shared__ uint64_t bar;
+  const int4 tile = tiles[blockIdx.x];  // x = class, y = first node, z = node count
+  const FusedVnClass cls = P.c[tile.x];
+  stage_to_smem(tabs, cls.tables, (uint32_t)(cls.dv - 1) * 128u, &bar);
+  const int w = blockIdx.y * kNodeThreads + threadIdx.x;
+  if (w >= W) return;
+  const uint32_t dn = done[w];
+  if (dn == kNibOnes) return;
+  const uint32_t done_byte = nib_bits_to_byte(dn, 0);
+  uint32_t failacc = 0;
+  switch (cls.dv) {
+#define X(D)                                                                                                     \
+  case D:                                                                                                        \
+    if constexpr (D <= MAXDV)                                                                                    \
+      vn_fast_body<D>(tabs, cls.node_list, tile.y, tile.y + tile.z, vn_edge0, W, w, msgs, cha, hard, done_byte,  \
+                      want_flags, cls.q_out, failacc);                                                           \
+    break;
+    LUTLDPC_FAST_DVS(X)
+#undef X
+  }
+  if (want_flags) flag_or(&vn_fail[w], failacc & kNibOnes);
 }
 
 // True when the program compiled from the decoder's trees is exactly the compile-time one.
@@ -749,6 +788,20 @@ cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const Nod
     default:
       return cudaErrorInvalidValue;
   }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_tiles, int n_tiles, const GraphArrays& g,
+                            const BatchBuffers& b, int want_flags, cudaStream_t st) {
+  if (n_tiles == 0) return cudaSuccess;
+  dim3 grid(n_tiles, cdiv(b.W, kNodeThreads));
+#define FUSED_ARGS P, d_tiles, g.vn_edge0, b.W, b.msgs, b.cha, b.hard, b.done, b.vn_fail, want_flags
+  if (max_dv <= 4) k_vn_fused<4><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
+  else if (max_dv <= 8) k_vn_fused<8><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
+  else if (max_dv <= 12) k_vn_fused<12><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
+  else if (max_dv <= 20) k_vn_fused<20><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
+  else return cudaErrorInvalidValue;
+#undef FUSED_ARGS
   return cudaGetLastError();
 }
 

@@ -63,6 +63,17 @@ struct NodeProgram;
 bool fast_vn_matches(const NodeProgram& p);
 cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const NodeLaunch& nl, const GraphArrays& g,
                            const BatchBuffers& b, int want_flags, cudaStream_t st);
+// all specialised classes of a VN pass in one launch; tiles[i] = (class, first node, node count, 0)
+struct FusedVnClass {
+  const uint8_t* tables;
+  const int32_t* node_list;
+  int dv, q_out;
+};
+struct FusedVnParams {
+  FusedVnClass c[8];
+};
+cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_tiles, int n_tiles, const GraphArrays& g,
+                            const BatchBuffers& b, int want_flags, cudaStream_t st);
 cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_bits, cudaStream_t st);
