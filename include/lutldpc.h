@@ -70,6 +70,10 @@ typedef struct lutldpc_info {
 } lutldpc_info;
 
 int lutldpc_abi_version(void);
+/* CUDA devices visible to the library, and the device the calling thread creates its next handles on
+ * (cudaGetDeviceCount / cudaSetDevice, so that host code needs no CUDA headers) */
+int lutldpc_device_count(void);
+int lutldpc_set_device(int device);
 /* message of the last failure; handle may be NULL for create errors */
 const char* lutldpc_last_error(const lutldpc_decoder* h);
 

@@ -1,0 +1,166 @@
+"""Host-side mirror of the reference's Monte-Carlo harness for the LUT decoder
+(LDPC_BER_Sim / LDPC_BER_Sim_LUT, src/LDPC_BER_Sim.{hpp,cpp}), with the frame loop of
+sim_snr_point (:246-311) running on the GPU through lutldpc_simulate_snr and the frames of every SNR
+point sharded over the ranks of a torch.distributed job (one process per GPU):
+
+  * rank r simulates disjoint Philox frame ranges -- frames are independent trials, no data moves;
+  * after every chunk ONE all_reduce(SUM) of the counter vector (NCCL over NVLink on GPUs, gloo in the
+    CPU tests) makes the stop rules of the reference global:
+        frames >= Nframes, frame_errors > Nfers           (:260, :289)
+        BER < ber_min or FER < fer_min ends the sweep      (:307)
+    Every rank sees the same sums, so every rank takes the same decision without further messages.
+
+Params come from the reference's own .ini (sections [Sim], [LDPC], [LUT]; keys and defaults as
+src/LDPC_BER_Sim.cpp:53-78,386-413).  LUT design is not part of this path: Sim.codec_filename names the
+bundle of a designed decoder.
+"""
+import configparser
+import math
+import os
+
+import numpy as np
+
+from .capi import ITER_HIST_MAX, SimCounters
+
+N_COUNTERS = 8 + ITER_HIST_MAX
+
+
+def parse_vec(s):
+    """IT++ vec string syntax used by Sim.SNRdB: 'a:step:b', 'a:b', '[a b c]', 'a,b,c'."""
+    out = []
+    for tok in s.replace("[", " ").replace("]", " ").replace(",", " ").replace(";", " ").split():
+        if ":" not in tok:
+            out.append(float(tok))
+            continue
+        p = [float(x) for x in tok.split(":")]
+        a, step, b = (p[0], 1.0, p[1]) if len(p) == 2 else p
+        n = int(math.floor((b - a) / step + 1e-9)) if step else 0
+        out.extend(a + i * step for i in range(n + 1))
+    return out
+
+
+def _flag(v):
+    return str(v).strip().lower() in ("1", "true")
+
+
+class SimParams:
+    """[Sim]/[LDPC]/[LUT] keys with the reference's defaults."""
+
+    def __init__(self, path=None, **over):
+        cp = configparser.ConfigParser(inline_comment_prefixes=(";",), comment_prefixes=(";", "#"), strict=False)
+        cp.optionxform = str
+        if path:
+            with open(path) as f:
+                cp.read_file(f)
+        g = lambda s, k, d: cp.get(s, k, fallback=d) if cp.has_section(s) else d
+        self.SNRdB = parse_vec(g("Sim", "SNRdB", "")) if g("Sim", "SNRdB", "") else []
+        self.Nframes = int(float(g("Sim", "Nframes", 1e5)))
+        self.Nfers = int(float(g("Sim", "Nfers", 20)))
+        self.ber_min = float(g("Sim", "ber_min", 1e-7))
+        self.fer_min = float(g("Sim", "fer_min", 1e-5))
+        self.rand_seed_offset = int(float(g("Sim", "rand_seed_offset", 0)))
+        self.results_prefix = g("Sim", "results_prefix", "RES")
+        self.results_dir = g("Sim", "results_dir", "results")
+        self.custom_name = g("Sim", "custom_name", "")
+        self.codec_filename = g("Sim", "codec_filename", "")
+        self.zero_codeword = _flag(g("LDPC", "zero_codeword", "true"))
+        self.parity_check_iter = _flag(g("LDPC", "parity_check_iter", "true"))
+        self.max_iter = int(float(g("LUT", "max_iter", 30)))
+        self.initial_message_mode = g("LUT", "initial_message_mode", "from_continuous_input")
+        self.has_lut_section = cp.has_section("LUT") or g("Sim", "codec_type", "none") == "LUT"
+        for k, v in over.items():
+            setattr(self, k, v)
+
+
+def split_frames(todo, first_frame, rank, world):
+    """Contiguous, disjoint share of `todo` frames starting at global index first_frame."""
+    per = (todo + world - 1) // world
+    lo = min(todo, rank * per)
+    hi = min(todo, lo + per)
+    return first_frame + lo, hi - lo
+
+
+class LDPC_BER_Sim_LUT:
+    """load() / run() / results like the reference class; `simulate` is the per-rank GPU call
+    (snr_db, n_frames, first_frame) -> int64 counter vector, by default Decoder.simulate_snr."""
+
+    def __init__(self, params, rand_seed=0, decoder=None, simulate=None, chunk_frames=8192, dist=None, device=None):
+        self.p, self.rand_seed, self.dec = params, int(rand_seed), decoder
+        self.chunk, self.dist, self.device = int(chunk_frames), dist, device
+        self._sim = simulate
+        self.points = []
+        self.rank = dist.get_rank() if dist is not None and dist.is_initialized() else 0
+        self.world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
+
+    def load(self, basedir="."):
+        """LDPC_BER_Sim_LUT::load (src/LDPC_BER_Sim.cpp:434-550) minus the design step."""
+        from .capi import Decoder, INIT_CONT, INIT_QCHA
+        if not self.p.codec_filename:
+            raise RuntimeError("LDPC_BER_Sim_LUT::load(): Sim.codec_filename (bundle of a designed decoder) is required")
+        path = self.p.codec_filename if os.path.isabs(self.p.codec_filename) else os.path.join(basedir, self.p.codec_filename)
+        self.dec = Decoder(path)
+        self.dec.set_exit_conditions(self.p.max_iter, self.p.parity_check_iter, self.p.parity_check_iter)  # :500
+        self.dec.set_initial_message_mode(INIT_QCHA if self.p.initial_message_mode == "from_quantized_channel_llrs"
+                                          else INIT_CONT)
+        return self
+
+    def _simulate(self, snr, n, first):
+        if self._sim is not None:
+            return np.asarray(self._sim(snr, n, first), dtype=np.int64)
+        if n <= 0:
+            return np.zeros(N_COUNTERS, np.int64)
+        c = self.dec.simulate_snr(snr, n, seed=self.rand_seed + self.p.rand_seed_offset, first_frame=first,
+                                  zero_codeword=self.p.zero_codeword, batch_frames=self.chunk)
+        return c.as_array()
+
+    def _allreduce(self, a):
+        if self.world == 1:
+            return a
+        import torch
+        t = torch.from_numpy(a.copy())
+        if self.device is not None:
+            t = t.to(self.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return t.cpu().numpy()
+
+    def sim_snr_point(self, snr, first_frame):
+        """One SNR point; returns (counters, frames consumed, stop_sweep)."""
+        acc = np.zeros(N_COUNTERS, np.int64)
+        used = 0
+        while acc[0] < self.p.Nframes and acc[1] <= self.p.Nfers:
+            todo = int(min(self.p.Nframes - acc[0], self.chunk * self.world))
+            lo, n = split_frames(todo, first_frame + used, self.rank, self.world)
+            acc += self._allreduce(self._simulate(snr, n, lo))
+            used += todo
+        ber = acc[3] / acc[2] if acc[2] else 0.0
+        fer = acc[1] / acc[0] if acc[0] else 0.0
+        return acc, used, (ber < self.p.ber_min or fer < self.p.fer_min)
+
+    def run(self, verbose=True):
+        """LDPC_BER_Sim::run (src/LDPC_BER_Sim.cpp:121-155)."""
+        self.points, first, stop = [], 0, False
+        for snr in self.p.SNRdB:
+            if stop:  # later points are stored with zero counts (:142-149)
+                self.points.append((snr, np.zeros(N_COUNTERS, np.int64)))
+                continue
+            acc, used, stop = self.sim_snr_point(snr, first)
+            first += used
+            self.points.append((snr, acc))
+            if verbose and self.rank == 0:
+                ubr = acc[5] / acc[4] if acc[4] else 0.0
+                print("SNR = %g  Simulated %d frames and %d data bits. Obtained %d data bit errors.  Data BER: %g "
+                      "Uncoded BER: %g FER: %g" % (snr, acc[0], acc[2], acc[3], acc[3] / acc[2] if acc[2] else 0.0, ubr,
+                                                   acc[1] / acc[0] if acc[0] else 0.0), flush=True)
+        return self.results()
+
+    def results(self):
+        """The variables the reference stores (src/LDPC_BER_Sim.cpp:347-358)."""
+        P = self.points
+        return {"sim_SNRdB": [s for s, _ in P], "sim_Nframes": [int(a[0]) for _, a in P],
+                "sim_frame_errors": [int(a[1]) for _, a in P], "sim_Ndatabits": [int(a[2]) for _, a in P],
+                "sim_data_bit_errors": [int(a[3]) for _, a in P], "sim_uncoded_bit_errors": [int(a[5]) for _, a in P],
+                "sim_sum_iterations": [int(a[6]) for _, a in P], "sim_decode_failures": [int(a[7]) for _, a in P]}
+
+
+def counters_from_array(a):
+    return SimCounters.from_array(a)

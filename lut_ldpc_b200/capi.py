@@ -65,7 +65,7 @@ class SimCounters(C.Structure):
 
 
 _lib = None
-EXPORTS = ["lutldpc_abi_version", "lutldpc_last_error", "lutldpc_create", "lutldpc_create_from_bundle",
+EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", "lutldpc_last_error", "lutldpc_create", "lutldpc_create_from_bundle",
            "lutldpc_destroy", "lutldpc_get_info", "lutldpc_set_exit_conditions", "lutldpc_set_initial_message_mode",
            "lutldpc_set_stream", "lutldpc_set_poll_interval", "lutldpc_decode_quantized",
            "lutldpc_decode_quantized_device", "lutldpc_decode_llr", "lutldpc_decode_llr_device", "lutldpc_quantize",

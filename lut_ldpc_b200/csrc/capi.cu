@@ -20,6 +20,15 @@ extern "C" {
 
 int lutldpc_abi_version(void) { return LUTLDPC_ABI_VERSION; }
 
+int lutldpc_device_count(void) {
+  int n = 0;
+  return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
+}
+int lutldpc_set_device(int device) {
+  if (cudaSetDevice(device) != cudaSuccess) { g_create_error = "cudaSetDevice failed"; return LUTLDPC_ERR_CUDA; }
+  return LUTLDPC_OK;
+}
+
 const char* lutldpc_last_error(const lutldpc_decoder* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
 
 static int finish_create(lutldpc_decoder* h, lutldpc_decoder** out) {

@@ -1,0 +1,255 @@
+// ber_sim for the B200 decoder: same command line and params .ini as the reference's prog/ber_sim.cpp
+// (:46-160) + LDPC_BER_Sim / LDPC_BER_Sim_LUT (src/LDPC_BER_Sim.cpp:42-155,246-311,376-550), with the
+// frame loop of sim_snr_point running on the GPU(s) through the C ABI.
+//
+//   ber_sim -p params.ini [-b basedir] [-s seed] [-c custom-name] [--gpus G] [--batch F]
+//
+// Differences, all at the edges of the hot path:
+//  * the decoder is not designed here: Sim.codec_filename must name a decoder bundle (the dump of a
+//    designed reference LDPC_Code_LUT); LUT.* design keys are read only to cross-check max_iter;
+//  * results are written as JSON with the reference's variable names (sim_SNRdB, sim_Nframes, ...,
+//    src/LDPC_BER_Sim.cpp:347-358) instead of an IT++ .it file;
+//  * with --gpus G the frames of every SNR point are split over G devices (one host thread per GPU,
+//    disjoint Philox frame ranges) and the counters are summed; stop rules act on the sums.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <map>
+#include <memory>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+#include <sys/stat.h>
+
+#include "ldpc_code_lut.hpp"
+
+using namespace lut_ldpc_b200;
+
+// ---------------------------------------------------------------- params .ini (boost::property_tree::ini_parser subset)
+struct Ini {
+  std::map<std::string, std::string> kv;  // "Section.key" -> value
+  static std::string trim(const std::string& s) {
+    size_t a = s.find_first_not_of(" \t\r\n"), b = s.find_last_not_of(" \t\r\n");
+    return a == std::string::npos ? "" : s.substr(a, b - a + 1);
+  }
+  bool read(const std::string& fn) {
+    std::ifstream f(fn.c_str());
+    if (!f) return false;
+    std::string line, sec;
+    while (std::getline(f, line)) {
+      line = trim(line);
+      if (line.empty() || line[0] == ';' || line[0] == '#') continue;
+      if (line[0] == '[') { sec = trim(line.substr(1, line.find(']') - 1)); continue; }
+      size_t eq = line.find('=');
+      if (eq == std::string::npos) continue;
+      kv[sec + "." + trim(line.substr(0, eq))] = trim(line.substr(eq + 1));
+    }
+    return true;
+  }
+  bool has(const std::string& k) const { return kv.count(k) > 0; }
+  bool has_section(const std::string& s) const {
+    for (auto& e : kv) if (e.first.compare(0, s.size() + 1, s + ".") == 0) return true;
+    return false;
+  }
+  std::string get(const std::string& k, const std::string& d) const { auto it = kv.find(k); return it == kv.end() ? d : it->second; }
+  double num(const std::string& k, double d) const { return has(k) ? atof(get(k, "").c_str()) : d; }
+  bool flag(const std::string& k, bool d) const {
+    if (!has(k)) return d;
+    std::string v = get(k, "");
+    return v == "1" || v == "true" || v == "True";
+  }
+};
+
+// IT++ vec string syntax as used for Sim.SNRdB: "a:step:b", "a:b", "[a b c]", "a,b,c"
+static std::vector<double> parse_vec(std::string s) {
+  for (char& c : s) if (c == '[' || c == ']' || c == ',' || c == ';') c = ' ';
+  std::vector<double> out;
+  std::istringstream is(s);
+  std::string tok;
+  while (is >> tok) {
+    size_t c1 = tok.find(':');
+    if (c1 == std::string::npos) { out.push_back(atof(tok.c_str())); continue; }
+    size_t c2 = tok.find(':', c1 + 1);
+    double a = atof(tok.substr(0, c1).c_str()), step = 1, b;
+    if (c2 == std::string::npos) b = atof(tok.substr(c1 + 1).c_str());
+    else { step = atof(tok.substr(c1 + 1, c2 - c1 - 1).c_str()); b = atof(tok.substr(c2 + 1).c_str()); }
+    if (step == 0) { out.push_back(a); continue; }
+    int n = (int)std::floor((b - a) / step + 1e-9);
+    for (int i = 0; i <= n; ++i) out.push_back(a + i * step);
+  }
+  return out;
+}
+
+struct Point {
+  double snr;
+  lutldpc_sim_counters c;
+};
+
+static void usage() {
+  std::cout << "Allowed options:\n"
+               "  -h [ --help ]             produce help message\n"
+               "  -p [ --params ] arg       parameter file (.ini, same keys as the reference's ber_sim)\n"
+               "  -b [ --base-dir ] arg     base directory for relative paths (default: cwd)\n"
+               "  -s [ --seed ] arg (=0)    random seed (frames are Philox streams keyed by seed + rand_seed_offset)\n"
+               "  -c [ --custom-name ] arg  appended to the results name\n"
+               "  --gpus arg (=1)           number of GPUs to split every SNR point over\n"
+               "  --batch arg (=0)          frames in flight per GPU (0 = library default)\n";
+}
+
+int main(int argc, char** argv) {
+  std::string params, basedir = ".", custom;
+  uint64_t seed = 0;
+  int gpus = 1, batch = 0;
+  for (int i = 1; i < argc; ++i) {
+    std::string a = argv[i];
+    auto next = [&]() -> std::string { return i + 1 < argc ? argv[++i] : ""; };
+    if (a == "-h" || a == "--help") { usage(); return 0; }
+    else if (a == "-p" || a == "--params") params = next();
+    else if (a == "-b" || a == "--base-dir") basedir = next();
+    else if (a == "-s" || a == "--seed") seed = strtoull(next().c_str(), nullptr, 10);
+    else if (a == "-c" || a == "--custom-name") custom = next();
+    else if (a == "--gpus") gpus = atoi(next().c_str());
+    else if (a == "--batch") batch = atoi(next().c_str());
+    else { std::cerr << "unknown option " << a << "\n"; usage(); return 1; }
+  }
+  if (params.empty()) { std::cerr << "Parameter file not specified\n"; usage(); return 1; }
+  auto path = [&](const std::string& p) { return (!p.empty() && p[0] == '/') ? p : basedir + "/" + p; };
+  Ini ini;
+  if (!ini.read(path(params))) { std::cerr << "cannot read " << path(params) << "\n"; return 1; }
+  // prog/ber_sim.cpp:134-147: the LUT simulation is selected by a [LUT] section or Sim.codec_type
+  if (!ini.has_section("LUT") && ini.get("Sim.codec_type", "none") != "LUT") {
+    std::cerr << "Only the LUT decoder ([LUT] section) is implemented on the GPU path\n";
+    return 1;
+  }
+  try {
+    // ---- [Sim] / [LDPC] / [LUT], defaults as src/LDPC_BER_Sim.cpp:53-78,386-413
+    if (!ini.has("Sim.SNRdB")) throw std::runtime_error("LDPC_BER_Sim: Sim.SNRdB is required");
+    std::vector<double> snrs = parse_vec(ini.get("Sim.SNRdB", ""));
+    const int64_t Nframes = (int64_t)ini.num("Sim.Nframes", 1e5);
+    const int64_t Nfers = (int64_t)ini.num("Sim.Nfers", 20);
+    const double ber_min = ini.num("Sim.ber_min", 1e-7), fer_min = ini.num("Sim.fer_min", 1e-5);
+    const uint64_t seed_off = (uint64_t)ini.num("Sim.rand_seed_offset", 0);
+    const std::string results_prefix = ini.get("Sim.results_prefix", "RES"), results_dir = ini.get("Sim.results_dir", "results");
+    custom = ini.get("Sim.custom_name", "") + custom;
+    const bool zero_cw = ini.flag("LDPC.zero_codeword", true);
+    const bool pci = ini.flag("LDPC.parity_check_iter", true);
+    const std::string codec = ini.get("Sim.codec_filename", "");
+    if (codec.empty())
+      throw std::runtime_error("LDPC_BER_Sim_LUT::load(): Sim.codec_filename (decoder bundle of a designed LDPC_Code_LUT) is "
+                               "required: LUT design is not part of the GPU path");
+    const std::string imode = ini.get("LUT.initial_message_mode", "from_continuous_input");
+
+    const int ndev = lutldpc_device_count();
+    if (ndev <= 0) throw std::runtime_error("no CUDA device (there is no CPU fallback)");
+    if (gpus < 1 || gpus > ndev) throw std::runtime_error("--gpus exceeds the number of visible devices");
+    std::vector<std::unique_ptr<LDPC_Code_LUT>> C(gpus);
+    for (int g = 0; g < gpus; ++g) {
+      if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
+      C[g].reset(new LDPC_Code_LUT(path(codec)));
+      const int mi = ini.has("LUT.max_iter") ? (int)ini.num("LUT.max_iter", 30) : C[g]->get_nrof_iterations();
+      C[g]->set_exit_conditions(mi, pci, pci);  // psc = pisc = parity_check_iter, src/LDPC_BER_Sim.cpp:500
+      C[g]->set_initial_message_mode(imode == "from_quantized_channel_llrs" ? LDPC_Code_LUT::QCHA : LDPC_Code_LUT::CONT);
+    }
+    if (!zero_cw && !C[0]->has_generator())
+      throw std::runtime_error("LDPC.zero_codeword=false needs a decoder bundle that carries the generator");
+    const int N = C[0]->get_nvar(), K = C[0]->get_ninfo();
+    std::ostringstream name;  // gen_filename, src/LDPC_BER_Sim.cpp:553-568
+    name << results_prefix << "_N" << N << "_R" << C[0]->get_rate() << "_maxIter" << C[0]->get_nrof_iterations() << "_zcw"
+         << (int)zero_cw << "_frames" << Nframes << (C[0]->is_min_lut() ? "_minLUT" : "_LUT") << custom;
+
+    // ---- run(), src/LDPC_BER_Sim.cpp:121-155
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<Point> points;
+    uint64_t next_frame = 0;  // global Philox frame index: disjoint across SNR points, chunks and GPUs
+    const int64_t chunk_per_gpu = batch > 0 ? batch : 8192;
+    bool stop = false;
+    for (double snr : snrs) {
+      Point pt;
+      pt.snr = snr;
+      memset(&pt.c, 0, sizeof pt.c);
+      if (!stop) {
+        // sim_snr_point: frames until Nframes or more than Nfers frame errors (:260-291), at chunk granularity
+        while ((int64_t)pt.c.frames < Nframes && (int64_t)pt.c.frame_errors <= Nfers) {
+          int64_t todo = std::min<int64_t>(Nframes - (int64_t)pt.c.frames, chunk_per_gpu * gpus);
+          std::vector<lutldpc_sim_counters> part(gpus);
+          std::vector<std::thread> th;
+          std::vector<std::string> errs(gpus);
+          int64_t per = (todo + gpus - 1) / gpus, off = 0;
+          for (int g = 0; g < gpus; ++g) {
+            int64_t n = std::min(per, todo - off);
+            memset(&part[g], 0, sizeof part[g]);
+            if (n <= 0) continue;
+            lutldpc_sim_params sp;
+            sp.snr_db = snr; sp.n_frames = n; sp.seed = seed + seed_off; sp.first_frame = next_frame + (uint64_t)off;
+            sp.zero_codeword = zero_cw; sp.batch_frames = batch;
+            th.emplace_back([&, g, sp]() {
+              try { C[g]->simulate_snr(sp, part[g]); } catch (const std::exception& e) { errs[g] = e.what(); }
+            });
+            off += n;
+          }
+          for (auto& t : th) t.join();
+          for (auto& e : errs) if (!e.empty()) throw std::runtime_error(e);
+          next_frame += (uint64_t)todo;
+          for (int g = 0; g < gpus; ++g) {
+            uint64_t* dst = reinterpret_cast<uint64_t*>(&pt.c);
+            const uint64_t* src = reinterpret_cast<const uint64_t*>(&part[g]);
+            for (size_t i = 0; i < sizeof(pt.c) / 8; ++i) dst[i] += src[i];
+          }
+        }
+        const double ber = pt.c.data_bits ? (double)pt.c.data_bit_errors / pt.c.data_bits : 0;
+        const double ubr = pt.c.uncoded_bits ? (double)pt.c.uncoded_bit_errors / pt.c.uncoded_bits : 0;
+        const double fer = pt.c.frames ? (double)pt.c.frame_errors / pt.c.frames : 0;
+        // the reference's line, src/LDPC_BER_Sim.cpp:294-300
+        std::cout << "SNR = " << snr << "  Simulated " << pt.c.frames << " frames and " << pt.c.data_bits << " data bits. "
+                  << "Obtained " << pt.c.data_bit_errors << " data bit errors. "
+                  << " Data BER: " << ber << " Uncoded BER: " << ubr << " FER: " << fer << std::endl;
+        if (ber < ber_min || fer < fer_min) stop = true;  // :307: the point is recorded, later points stay empty (:142-149)
+      }
+      points.push_back(pt);
+    }
+    const double runtime = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+
+    // ---- save(), src/LDPC_BER_Sim.cpp:317-361 (JSON with the reference's variable names)
+    const std::string dir = path(results_dir) + "/" + name.str();
+    mkdir(path(results_dir).c_str(), 0777);
+    mkdir(dir.c_str(), 0777);
+    char sfx[32];
+    snprintf(sfx, sizeof sfx, "_rseed%04llu", (unsigned long long)seed);
+    std::ofstream js((dir + "/" + name.str() + sfx + ".json").c_str());
+    auto arr = [&](const char* key, uint64_t lutldpc_sim_counters::*m) {
+      js << "  \"" << key << "\": [";
+      for (size_t i = 0; i < points.size(); ++i) js << (i ? ", " : "") << points[i].c.*m;
+      js << "],\n";
+    };
+    js << "{\n  \"sim_SNRdB\": [";
+    for (size_t i = 0; i < points.size(); ++i) js << (i ? ", " : "") << points[i].snr;
+    js << "],\n";
+    arr("sim_Nframes", &lutldpc_sim_counters::frames);
+    arr("sim_Ndatabits", &lutldpc_sim_counters::data_bits);
+    arr("sim_frame_errors", &lutldpc_sim_counters::frame_errors);
+    arr("sim_data_bit_errors", &lutldpc_sim_counters::data_bit_errors);
+    arr("sim_uncoded_bit_errors", &lutldpc_sim_counters::uncoded_bit_errors);
+    arr("sim_Nuncodedbits", &lutldpc_sim_counters::uncoded_bits);
+    arr("sim_sum_iterations", &lutldpc_sim_counters::sum_iters);
+    arr("sim_decode_failures", &lutldpc_sim_counters::decode_failures);
+    js << "  \"ldpc_nvar\": " << N << ",\n  \"ldpc_nchk\": " << C[0]->get_nchk() << ",\n  \"ldpc_code_rate\": "
+       << C[0]->get_rate() << ",\n  \"ldpc_ninfo\": " << K << ",\n  \"runtime\": " << runtime << ",\n  \"gpus\": " << gpus
+       << ",\n  \"gitversion\": \"lut_ldpc_b200\"\n}\n";
+    js.close();
+    // copy of the params file next to the results, like the reference (:331-338)
+    std::ifstream src(path(params).c_str(), std::ios::binary);
+    std::string pbase = params.substr(params.find_last_of('/') == std::string::npos ? 0 : params.find_last_of('/') + 1);
+    std::ofstream dst((dir + "/" + pbase).c_str(), std::ios::binary);
+    dst << src.rdbuf();
+    std::cout << "Results written to " << dir << " (runtime " << runtime << " s)" << std::endl;
+  } catch (const std::exception& e) {
+    std::cerr << "ber_sim: " << e.what() << std::endl;
+    return 1;
+  }
+  return 0;
+}

