@@ -31,7 +31,8 @@ class _Info(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("nvar", "nchk", "nchk_lin_indep", "ninfo", "num_edges", "max_iters", "Nq_Cha",
                                          "min_lut", "has_gen", "n_degree_classes")] + \
                [("lookups_per_frame_iter", C.c_int64), ("lookups_per_frame_iter_naive", C.c_int64), ("rate", C.c_double),
-                ("n_var_programs", C.c_int32), ("n_fast_var_programs", C.c_int32)]
+                ("n_var_programs", C.c_int32), ("n_fast_var_programs", C.c_int32),
+                ("staggered_schedule", C.c_int32), ("reserved_", C.c_int32)]
 
 
 class _SimParams(C.Structure):
@@ -73,7 +74,7 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
-                 7: "count", 8: "encode"}
+                 7: "count", 8: "encode", 9: "stagger_step"}
 
 
 def load_library():

@@ -14,8 +14,16 @@ using namespace lutldpc;
     if (e_ != cudaSuccess) return cuda_fail(e_, where); \
   } while (0)
 
+static int env_int(const char* name, int dflt) {
+  const char* s = getenv(name);
+  return s && *s ? atoi(s) : dflt;
+}
+
 lutldpc_decoder::~lutldpc_decoder() {
   if (h_active) cudaFreeHost(h_active);
+  if (h_poll) cudaFreeHost(h_poll);
+  for (auto& e : ev_poll)
+    if (e) cudaEventDestroy(e);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
   for (cudaEvent_t e : evpool) cudaEventDestroy(e);
@@ -169,6 +177,46 @@ int lutldpc_decoder::init_device() {
       CK(d_fused_tiles.upload(flat), "upload fused tiles");
     }
   }
+  {  // staggered schedule: needs every VN class on the specialised code and min-sum checks with row tables
+    const char* e = getenv("LUTLDPC_NO_STAGGER");
+    bool want = m.minLUT && use_cn_exact && cn_exact.size() <= 4 && n_iter_slots >= 2 && !(e && e[0] == '1');
+    std::vector<std::pair<double, int4>> items;
+    const int vn_ops = std::max(1, env_int("LUTLDPC_STAGGER_VN_OPS", 64));
+    const int cn_rows = std::max(1, env_int("LUTLDPC_STAGGER_CN_ROWS", 2));
+    for (int c = 0; c < nvc && want; ++c) {
+      if (!vn_classes[c].n) continue;
+      for (int t = 0; t + 1 < n_iter_slots; ++t) want &= var_progs[(size_t)t * nvc + c].fast_dv != 0;
+      want &= stg_classes.size() < 8;
+      if (!want) break;
+      const int j = (int)stg_classes.size();
+      stg_classes.push_back(c);
+      stg_max_dv = std::max(stg_max_dv, vn_classes[c].degree);
+      const int per = std::max(1, vn_ops / std::max(1, (int)var_progs[c].n_ops));
+      const int nt = (vn_classes[c].n + per - 1) / per;
+      for (int i = 0; i < nt; ++i)
+        items.push_back({(i + 0.5) / nt, make_int4(j, i * per, std::min(per, vn_classes[c].n - i * per), 0)});
+    }
+    want = want && !stg_classes.empty() && stagger_supported(stg_max_dv);
+    for (size_t k = 0; k < cn_exact.size() && want; ++k) {
+      const int nt = (cn_exact[k].n + cn_rows - 1) / cn_rows;
+      for (int i = 0; i < nt; ++i)
+        items.push_back({(i + 0.5) / nt, make_int4(8 + (int)k, i * cn_rows, std::min(cn_rows, cn_exact[k].n - i * cn_rows), 0)});
+    }
+    if (want) {
+      std::stable_sort(items.begin(), items.end(), [](const std::pair<double, int4>& a, const std::pair<double, int4>& b2) {
+        return a.first < b2.first;
+      });
+      std::vector<int4> flat;
+      for (auto& t : items) flat.push_back(t.second);
+      n_stg_items = (int)flat.size();
+      CK(d_stg_items.upload(flat), "upload stagger items");
+      CK(cudaMallocHost((void**)&h_poll, 8 * sizeof(uint32_t)), "cudaMallocHost");
+      for (auto& ev : ev_poll) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming), "cudaEventCreate");
+      stagger_ok = true;
+    } else {
+      stg_classes.clear();
+    }
+  }
   chk_progs.assign((size_t)n_iter_slots * ncc, ProgRef());
   for (int t = 0; t < n_iter_slots && ncc; ++t) {
     int ii = slot_first_iter[t];
@@ -273,6 +321,7 @@ int lutldpc_decoder::run_batch(int n_frames, const uint8_t* d_cha_lab, const uin
 
 // Expects cha / msgs / hard of the current batch to be initialised (pack or the channel kernel).
 int lutldpc_decoder::run_passes(TraceSink* tr) {
+  if (stagger_ok && !tr && b.W >= 2 * kNodeThreads) return run_passes_staggered();
   int rc = 0;
   const int n_frames = b.F;
   const int nvc = (int)vn_classes.size(), ncc = (int)cn_classes.size();
@@ -391,6 +440,116 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   CK(cudaEventRecord(ev1, st), "event");
   have_stats = true;
   last_frames = n_frames;
+  stat_frame_iters = -1;
+  return LUTLDPC_OK;
+}
+
+// lut_decode with the two halves of the batch half an iteration apart (stagger.cu): launch s runs heavy
+// phase s of half 0 and heavy phase s-1 of half 1, where phase 2*ii is the check pass and phase 2*ii+1 the
+// variable pass of iteration ii (src/LDPC_Code_LUT.cpp:302-338).  Per frame the sequence of passes, flag
+// tests and returns is exactly that of run_passes(); frames are independent, so the interleaving of the
+// halves is not observable in the results.  The host looks at the counters of unfinished frames two
+// launches late (ring of pinned slots + events) so that the stream never drains.
+int lutldpc_decoder::run_passes_staggered() {
+  cudaStream_t st = stream;
+  const int nvc = (int)vn_classes.size();
+  const uint8_t* blob = d_prog_blob.p;
+  const int W = b.W;
+  const int Wa = std::min(W, ((W / 2 + kNodeThreads - 1) / kNodeThreads) * kNodeThreads);
+  const int w0[2] = {0, Wa}, w1[2] = {Wa, W};
+  const int n_colblocks = (std::max(Wa, W - Wa) + kStaggerCols - 1) / kStaggerCols;
+  uint32_t* n_act = b.n_active;  // two device slots, one per half
+  bool alive[2] = {true, true};
+  if (pisc) {  // :277
+    CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
+    for (int h = 0; h < 2; ++h) {
+      CK(launch_finalize_range(FIN_INIT, 0, b, w0[h], w1[h], n_act + h, st), "finalize"); launched(KIND_FINALIZE);
+    }
+    if (poll_every > 0) {
+      CK(cudaMemcpyAsync(h_poll, n_act, 8, cudaMemcpyDeviceToHost, st), "poll copy");
+      CK(cudaStreamSynchronize(st), "poll sync");
+      alive[0] = h_poll[0] != 0;
+      alive[1] = h_poll[1] != 0;
+    }
+  }
+  const int n_phases = 2 * max_iters - 1;  // per half: CN(0) VN(0) ... CN(max-1)
+  int ring_head = 0, ring_n = 0, polled = 0;  // lagged polls in flight
+  int ring_mask[4] = {0, 0, 0, 0};            // which halves a slot reports on
+  for (int s = 0; s <= n_phases && (alive[0] || alive[1]); ++s) {
+    StaggerParams P;
+    memset(&P, 0, sizeof P);
+    P.W = W;
+    int fin_half = -1, fin_ii = 0;
+    bool any = false;
+    for (int h = 0; h < 2; ++h) {
+      const int ph = s - h;
+      if (!alive[h] || ph < 0 || ph >= n_phases) continue;
+      const int ii = ph >> 1;
+      any = true;
+      if ((ph & 1) == 0) {
+        P.cn_w0 = w0[h]; P.cn_w1 = w1[h];
+        P.cn_q = code_bits(m.Nq_Msg[ii]);
+        P.cn_want = psc && ii > 0;
+        if (P.cn_want) { fin_half = h; fin_ii = ii; }
+      } else {
+        const int t = m.var_tree_idx_iter[ii];
+        P.vn_w0 = w0[h]; P.vn_w1 = w1[h];
+        P.vn_want = psc;
+        for (size_t j = 0; j < stg_classes.size(); ++j) {
+          const int c = stg_classes[j];
+          const ProgRef& r = var_progs[(size_t)t * nvc + c];
+          P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].list.p, r.fast_dv, r.q_out};
+        }
+      }
+    }
+    if (!any) continue;
+    for (size_t k = 0; k < cn_exact.size(); ++k) {
+      P.cn_rows[k] = cn_exact[k].list.p;
+      P.cn_dc[k] = cn_exact[k].degree;
+    }
+    CK(launch_stagger(P, stg_max_dv, d_stg_items.p, n_stg_items, n_colblocks, g, b, st), "stagger"); launched(KIND_STEP);
+    if (fin_half >= 0) {  // psc: VN pass ii-1 unanimous and syndrome zero -> return ii (:327)
+      CK(launch_finalize_range(FIN_ITER, fin_ii, b, w0[fin_half], w1[fin_half], n_act + fin_half, st), "finalize");
+      launched(KIND_FINALIZE);
+      if (poll_every > 0 && ++polled % poll_every == 0) {
+        if (ring_n == 4) return fail(LUTLDPC_ERR_STATE, "poll ring overflow");
+        const int slot = (ring_head + ring_n) & 3;
+        CK(cudaMemcpyAsync(h_poll + 2 * slot, n_act, 8, cudaMemcpyDeviceToHost, st), "poll copy");
+        CK(cudaEventRecord(ev_poll[slot], st), "poll event");
+        ring_mask[slot] = 1 << fin_half;
+        ++ring_n;
+      }
+    }
+    // consume polls that are at least two launches old (or everything that has already landed)
+    while (ring_n > 0) {
+      const int slot = ring_head;
+      if (ring_n <= 2) {
+        cudaError_t q = cudaEventQuery(ev_poll[slot]);
+        if (q == cudaErrorNotReady) break;
+        CK(q, "poll query");
+      } else {
+        CK(cudaEventSynchronize(ev_poll[slot]), "poll sync");
+      }
+      for (int h = 0; h < 2; ++h)
+        if ((ring_mask[slot] >> h & 1) && h_poll[2 * slot + h] == 0) alive[h] = false;
+      ring_head = (ring_head + 1) & 3;
+      --ring_n;
+    }
+  }
+  if (alive[0] || alive[1]) {  // decision + final syndrome (:340-349); finished words are skipped inside
+    const int t = m.var_tree_idx_iter[max_iters - 1];
+    for (int c = 0; c < nvc; ++c) {
+      if (!vn_classes[c].n) continue;
+      const ProgRef& r = var_progs[(size_t)t * nvc + c];
+      NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
+      CK(launch_node(NODE_DEC, nl, g, b, 0, st), "dec_lut"); launched(KIND_DEC0 + std::min(c, 15));
+    }
+    CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
+    CK(launch_finalize(FIN_LAST, max_iters, b, st), "finalize"); launched(KIND_FINALIZE);
+  }
+  CK(cudaEventRecord(ev1, st), "event");
+  have_stats = true;
+  last_frames = b.F;
   stat_frame_iters = -1;
   return LUTLDPC_OK;
 }

@@ -15,6 +15,7 @@ namespace lutldpc {
 enum ProfileKind {  // indices of lutldpc_get_profile
   KIND_RESET = 0, KIND_PACK = 1, KIND_CHANNEL = 2, KIND_CN = 3, KIND_SYNDROME = 4, KIND_FINALIZE = 5,
   KIND_UNPACK = 6, KIND_COUNT = 7, KIND_ENCODE = 8,
+  KIND_STEP = 9,  // staggered launch: check pass of one half of the batch + variable pass of the other
   KIND_VN0 = 16, KIND_DEC0 = 32, KIND_CHK0 = 48  // + degree-class index
 };
 
@@ -87,6 +88,13 @@ struct lutldpc_decoder {
   std::vector<int> fused_classes;
   lutldpc::DevBuf<int4> d_fused_tiles;
   int n_fused_tiles = 0, fused_max_dv = 0;
+  // staggered schedule (stagger.cu): every VN class specialised, min-sum checks with row tables
+  bool stagger_ok = false;
+  std::vector<int> stg_classes;  // VN class behind StaggerParams::c[j]
+  lutldpc::DevBuf<int4> d_stg_items;
+  int n_stg_items = 0, stg_max_dv = 0;
+  uint32_t* h_poll = nullptr;    // pinned [4][2]: unfinished frames per half, ring of lagged polls
+  cudaEvent_t ev_poll[4] = {nullptr, nullptr, nullptr, nullptr};
   std::vector<lutldpc::ProgRef> var_progs;  // [iter slot][vn class]; last slot = decision trees
   std::vector<lutldpc::ProgRef> chk_progs;  // [iter slot][cn class]
   int n_iter_slots = 0;
@@ -125,5 +133,6 @@ struct lutldpc_decoder {
   int run_batch(int n_frames, const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, lutldpc::TraceSink* tr);
   int begin_batch(int n_frames);            // buffers + flag reset + start event
   int run_passes(lutldpc::TraceSink* tr);   // all iterations + decision on the initialised batch
+  int run_passes_staggered();               // same result, the two halves of the batch half an iteration apart
   int max_batch_frames() const;
 };

@@ -1,0 +1,129 @@
+// Device-side helpers shared by the kernel translation units (kernels.cu, stagger.cu).
+#pragma once
+#include <cstdint>
+
+#include "core.cuh"
+#include "kernels.hpp"
+#include "vn_fast.cuh"
+
+namespace lutldpc {
+
+// ---------------------------------------------------------------------------------------------
+// bulk (TMA engine) global->shared copy of a contiguous, 16-byte aligned block, completion on an
+// mbarrier.  Used to stage a node program (op list + LUTs) and index slices into shared memory.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// Whole-CTA helper: thread 0 issues the copy (in <= 16 KiB pieces), everyone waits for the bytes.
+// `bytes` must be a multiple of 16.  The barrier is single-use (parity 0).
+__device__ __forceinline__ void stage_to_smem(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  if (threadIdx.x == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(bar, bytes);
+    const uint32_t kPiece = 16384;
+    for (uint32_t off = 0; off < bytes; off += kPiece) {
+      uint32_t n = bytes - off < kPiece ? bytes - off : kPiece;
+      bulk_g2s((char*)dst + off, (const char*)src + off, n, bar);
+    }
+  }
+  mbar_wait(bar, 0);
+}
+
+// OR `f` into a per-word flag that thousands of threads of the same pass target: look first (L2) and
+// only issue the atomic when it would set a new bit.  Flags only ever gain bits within a pass, so a
+// stale read can cost an extra atomic but never lose one.  Without this, the 32400 checks of the
+// N=64800 code all hit the same few hundred addresses and the pass is bound by L2 atomic serialisation.
+__device__ __forceinline__ void flag_or(uint32_t* p, uint32_t f) {
+  if (f) {
+    const uint32_t cur = __ldcg(p);
+    if (f & ~cur) atomicOr(p, f);
+  }
+}
+
+
+template <int VEC> struct WordVec;
+template <> struct WordVec<1> { typedef uint32_t T; };
+template <> struct WordVec<2> { typedef uint2 T; };
+template <> struct WordVec<4> { typedef uint4 T; };
+
+#define LUTLDPC_EXACT_DCS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
+#define LUTLDPC_FAST_DVS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16) X(17) X(18) X(19) X(20)
+
+template <int DV, int II>
+struct FastStore {
+  static __device__ __forceinline__ void run(const uint32_t (&v)[DV + 1 + fastvn::Static<DV>::P.n_ops], uint32_t* row0,
+                                             size_t W, uint32_t& A, uint32_t& O) {
+    if constexpr (II < DV) {
+      const uint32_t r = v[fastvn::Static<DV>::P.out[II]];
+      row0[(size_t)II * W] = r;
+      A &= r;
+      O |= r;
+      FastStore<DV, II + 1>::run(v, row0, W, A, O);
+    }
+  }
+};
+
+// per-thread work of the specialised VN pass: nodes [i0, i1) of node_list, word column w
+template <int DV>
+__device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int32_t* __restrict__ node_list, int i0, int i1,
+                                             const int32_t* __restrict__ vn_edge0, int W, int w,
+                                             uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
+                                             uint8_t* __restrict__ hard, uint32_t done_byte, int want_flags, int q_out,
+                                             uint32_t& failacc) {
+  constexpr int NOPS = fastvn::Static<DV>::P.n_ops;
+  const int so = q_out - 1, root_shift = 4 - q_out;
+  for (int i = i0; i < i1; ++i) {
+    const int node = node_list[i];
+    uint32_t* row0 = msgs + (size_t)vn_edge0[node] * W + w;
+    uint32_t v[DV + 1 + NOPS];
+#pragma unroll
+    for (int k = 0; k < DV; ++k) v[k] = row0[(size_t)k * W];
+    v[DV] = cha[(size_t)node * W + w];
+    fastvn::Exec<DV, 0>::run(v, tabs, root_shift);
+    uint32_t A = 0xFFFFFFFFu, O = 0;
+    FastStore<DV, 0>::run(v, row0, (size_t)W, A, O);
+    if (want_flags) {
+      failacc |= (A ^ O) >> so;
+      uint8_t* hp = hard + (size_t)node * W + w;
+      const uint32_t nb = nib_bits_to_byte(v[fastvn::Static<DV>::P.out[0]], so);
+      *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
+    }
+  }
+}
+
+}  // namespace lutldpc

@@ -7,77 +7,9 @@
 #include <cstdio>
 #include <cstdlib>
 
-#include "core.cuh"
-#include "vn_fast.cuh"
+#include "kdev.cuh"
 
 namespace lutldpc {
-
-// ---------------------------------------------------------------------------------------------
-// bulk (TMA engine) global->shared copy of a contiguous, 16-byte aligned block, completion on an
-// mbarrier.  Used to stage a node program (op list + LUTs) and index slices into shared memory.
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void fence_barrier_init() {
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-          smem_u32(dst)),
-      "l"(src), "r"(bytes), "r"(smem_u32(bar))
-      : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
-}
-// Whole-CTA helper: thread 0 issues the copy (in <= 16 KiB pieces), everyone waits for the bytes.
-// `bytes` must be a multiple of 16.  The barrier is single-use (parity 0).
-__device__ __forceinline__ void stage_to_smem(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  if (threadIdx.x == 0) {
-    mbar_init(bar, 1);
-    fence_barrier_init();
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    mbar_expect_tx(bar, bytes);
-    const uint32_t kPiece = 16384;
-    for (uint32_t off = 0; off < bytes; off += kPiece) {
-      uint32_t n = bytes - off < kPiece ? bytes - off : kPiece;
-      bulk_g2s((char*)dst + off, (const char*)src + off, n, bar);
-    }
-  }
-  mbar_wait(bar, 0);
-}
-
-// OR `f` into a per-word flag that thousands of threads of the same pass target: look first (L2) and
-// only issue the atomic when it would set a new bit.  Flags only ever gain bits within a pass, so a
-// stale read can cost an extra atomic but never lose one.  Without this, the 32400 checks of the
-// N=64800 code all hit the same few hundred addresses and the pass is bound by L2 atomic serialisation.
-__device__ __forceinline__ void flag_or(uint32_t* p, uint32_t f) {
-  if (f) {
-    const uint32_t cur = __ldcg(p);
-    if (f & ~cur) atomicOr(p, f);
-  }
-}
 
 // label -> storage code for one byte label (model.hpp)
 __device__ __forceinline__ uint32_t lab2code(uint32_t m, int Nq, int q) {
@@ -210,10 +142,6 @@ __global__ void __launch_bounds__(128) k_cn_minsum(const int32_t* __restrict__ c
 
 // Vectorised variant: each thread owns VEC consecutive words (8*VEC frames) of one check, so a warp
 // moves 128*VEC contiguous bytes per edge row and keeps dc*VEC independent 4-byte loads in flight.
-template <int VEC> struct WordVec;
-template <> struct WordVec<1> { typedef uint32_t T; };
-template <> struct WordVec<2> { typedef uint2 T; };
-template <> struct WordVec<4> { typedef uint4 T; };
 
 template <int MAXDC, int VEC>
 __global__ void __launch_bounds__(128) k_cn_minsum_v(const int32_t* __restrict__ cn_start,
@@ -444,12 +372,12 @@ __global__ void __launch_bounds__(128) k_syndrome(const int32_t* __restrict__ cn
 //   FIN_INIT  pisc: frames whose channel hard decision is a codeword return 0     (:277)
 //   FIN_ITER  psc : unanimous VNs + zero syndrome -> return `value` = ii+1        (:327)
 //   FIN_LAST  after the decision pass: +-max_iters                                (:346-349)
-__global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int W, uint32_t* done, uint32_t* vn_fail,
-                                                   uint32_t* cn_fail, uint32_t* syn_fail, int32_t* iters,
-                                                   uint32_t* n_active) {
+__global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int w0, int w1, uint32_t* done,
+                                                   uint32_t* vn_fail, uint32_t* cn_fail, uint32_t* syn_fail,
+                                                   int32_t* iters, uint32_t* n_active) {
   __shared__ uint32_t red[32];
   uint32_t cnt = 0;
-  for (int w = threadIdx.x; w < W; w += blockDim.x) {
+  for (int w = w0 + threadIdx.x; w < w1; w += blockDim.x) {
     uint32_t d = done[w], conv;
     if (mode == FIN_INIT) {
       conv = ~d & ~syn_fail[w] & kNibOnes;
@@ -534,48 +462,6 @@ __global__ void k_quantize(const double* __restrict__ llr, size_t n, const doubl
 // as k_node<NODE_VAR>; the program is compile-time, values stay in registers, the LUTs of the class
 // (128 B each, one per tree node) are staged into shared memory with one bulk copy.
 // ---------------------------------------------------------------------------------------------
-template <int DV, int II>
-struct FastStore {
-  static __device__ __forceinline__ void run(const uint32_t (&v)[DV + 1 + fastvn::Static<DV>::P.n_ops], uint32_t* row0,
-                                             size_t W, uint32_t& A, uint32_t& O) {
-    if constexpr (II < DV) {
-      const uint32_t r = v[fastvn::Static<DV>::P.out[II]];
-      row0[(size_t)II * W] = r;
-      A &= r;
-      O |= r;
-      FastStore<DV, II + 1>::run(v, row0, W, A, O);
-    }
-  }
-};
-
-// per-thread work of the specialised VN pass: nodes [i0, i1) of node_list, word column w
-template <int DV>
-__device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int32_t* __restrict__ node_list, int i0, int i1,
-                                             const int32_t* __restrict__ vn_edge0, int W, int w,
-                                             uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
-                                             uint8_t* __restrict__ hard, uint32_t done_byte, int want_flags, int q_out,
-                                             uint32_t& failacc) {
-  constexpr int NOPS = fastvn::Static<DV>::P.n_ops;
-  const int so = q_out - 1, root_shift = 4 - q_out;
-  for (int i = i0; i < i1; ++i) {
-    const int node = node_list[i];
-    uint32_t* row0 = msgs + (size_t)vn_edge0[node] * W + w;
-    uint32_t v[DV + 1 + NOPS];
-#pragma unroll
-    for (int k = 0; k < DV; ++k) v[k] = row0[(size_t)k * W];
-    v[DV] = cha[(size_t)node * W + w];
-    fastvn::Exec<DV, 0>::run(v, tabs, root_shift);
-    uint32_t A = 0xFFFFFFFFu, O = 0;
-    FastStore<DV, 0>::run(v, row0, (size_t)W, A, O);
-    if (want_flags) {
-      failacc |= (A ^ O) >> so;
-      uint8_t* hp = hard + (size_t)node * W + w;
-      const uint32_t nb = nib_bits_to_byte(v[fastvn::Static<DV>::P.out[0]], so);
-      *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
-    }
-  }
-}
-
 template <int DV>
 __global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restrict__ tables_g,
                                                            const int32_t* __restrict__ node_list, int n_nodes,
@@ -599,7 +485,6 @@ __global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restr
   if (want_flags) flag_or(&vn_fail[w], failacc & kNibOnes);
 }
 
-#define LUTLDPC_FAST_DVS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16) X(17) X(18) X(19) X(20)
 
 static const fastvn::Prog* fast_prog(int dv) {
   switch (dv) {
@@ -727,7 +612,6 @@ cudaError_t launch_cn_minsum(const GraphArrays& g, const BatchBuffers& b, int q,
   return cudaGetLastError();
 }
 
-#define LUTLDPC_EXACT_DCS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
 bool cn_exact_supported(int dc) { return dc >= 2 && dc <= 16; }
 
 cudaError_t launch_cn_exact(int dc, const int32_t* d_rows, int n_checks, const BatchBuffers& b, int q, int want_fail,
@@ -812,8 +696,13 @@ cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStr
 }
 
 cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b, cudaStream_t st) {
-  k_finalize<<<1, 1024, 0, st>>>((int)mode, value, b.W, b.done, b.vn_fail, b.cn_fail, b.syn_fail, b.iters,
-                                 b.n_active);
+  return launch_finalize_range(mode, value, b, 0, b.W, b.n_active, st);
+}
+
+cudaError_t launch_finalize_range(FinalizeMode mode, int value, const BatchBuffers& b, int w0, int w1,
+                                  uint32_t* n_active, cudaStream_t st) {
+  k_finalize<<<1, 1024, 0, st>>>((int)mode, value, w0, w1, b.done, b.vn_fail, b.cn_fail, b.syn_fail, b.iters,
+                                 n_active);
   return cudaGetLastError();
 }
 

@@ -74,6 +74,32 @@ struct FusedVnParams {
 };
 cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_tiles, int n_tiles, const GraphArrays& g,
                             const BatchBuffers& b, int want_flags, cudaStream_t st);
+// ---- staggered schedule.  The min-sum check pass is bound by HBM and leaves the issue slots idle; the
+// LUT variable pass is bound by shared-memory look-ups and integer issue and leaves HBM idle.  One
+// launch therefore runs the CHECK pass of one column range of the batch and the VARIABLE pass of
+// another (the two halves of a batch run half an iteration apart), with the work items of both kinds
+// interleaved so that every SM holds CTAs of both at any time.
+//   item = (kind, first, count, 0): kind < 8: VN degree class `kind`, nodes [first, first+count) of its
+//   list; kind >= 8: check class kind-8, checks [first, first+count) of its row table.
+// A CTA covers kStaggerCols word columns (blockIdx.y) of its range.
+constexpr int kStaggerCols = 512;
+struct StaggerParams {
+  FusedVnClass c[8];
+  const int32_t* cn_rows[4];  // row tables [n][degree], as for launch_cn_exact
+  int cn_dc[4];
+  int W;                      // row stride of the batch (words)
+  int cn_w0, cn_w1;           // columns that get the check pass (empty range: none)
+  int cn_q, cn_want;          // code width of that pass; 1 = OR sign parities into cn_fail
+  int vn_w0, vn_w1;           // columns that get the variable pass
+  int vn_want;                // 1 = unanimity flags + hard decisions (psc)
+};
+bool stagger_supported(int max_dv);
+int stagger_max_exact_dc();  // larger check degrees run the re-reading loop inside the same kernel
+cudaError_t launch_stagger(const StaggerParams& P, int max_dv, const int4* d_items, int n_items, int n_colblocks,
+                           const GraphArrays& g, const BatchBuffers& b, cudaStream_t st);
+// finalize restricted to columns [w0, w1); *n_active receives the unfinished frames of that range
+cudaError_t launch_finalize_range(FinalizeMode mode, int value, const BatchBuffers& b, int w0, int w1,
+                                  uint32_t* n_active, cudaStream_t st);
 cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_bits, cudaStream_t st);
