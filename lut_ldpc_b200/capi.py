@@ -162,12 +162,16 @@ class Decoder:
         self._ck(self._L.lutldpc_set_poll_interval(self._h, int(every)))
 
     # ---- decode (host buffers)
-    def decode_quantized(self, cha, msg):
+    def decode_quantized(self, cha, msg, out=None, iters=None):
+        """lut_decode for a batch of host label arrays.  `out` [F, nvar] u8 / `iters` [F] i32 may be supplied
+        (e.g. views of pinned memory, so that the copies overlap the decoder); else they are allocated."""
         cha = np.ascontiguousarray(cha, np.uint8).reshape(-1, self.nvar)
         msg = np.ascontiguousarray(msg, np.uint8).reshape(-1, self.nvar)
         assert cha.shape == msg.shape
-        out = np.empty(cha.shape, np.uint8)
-        it = np.empty(cha.shape[0], np.int32)
+        out = np.empty(cha.shape, np.uint8) if out is None else out
+        it = np.empty(cha.shape[0], np.int32) if iters is None else iters
+        assert out.dtype == np.uint8 and out.shape == cha.shape and out.flags.c_contiguous
+        assert it.dtype == np.int32 and it.shape == (cha.shape[0],) and it.flags.c_contiguous
         self._ck(self._L.lutldpc_decode_quantized(self._h, cha.shape[0], _p(cha), _p(msg), _p(out), _p(it)))
         return out, it
 

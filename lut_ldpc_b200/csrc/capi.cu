@@ -1,4 +1,6 @@
 // C ABI (include/lutldpc.h) over the decoder object.  No torch types, no exceptions across the ABI.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -212,36 +214,92 @@ int lutldpc_decode_quantized_device(lutldpc_decoder* h, int n_frames, const uint
   return LUTLDPC_OK;
 }
 
+// Host-buffer decode.  The call is cut into chunks and pipelined over three streams: while chunk c is decoded
+// on the handle's stream, the inputs of chunk c+1 travel host->device and the results of chunk c-1
+// device->host on two copy streams (PCIe is full duplex); device staging is double-buffered.  With pinned
+// host buffers the copies are asynchronous and hide behind the decoder; with pageable buffers the runtime
+// stages them synchronously and the call degrades to copy-then-decode, with the same results.
+static int host_chunk_frames(lutldpc_decoder* h, int n_frames) {
+  const int maxb = h->max_batch_frames();
+  if (const char* e = getenv("LUTLDPC_HOST_CHUNK")) {
+    int v = atoi(e);
+    if (v > 0) return std::min(maxb, std::max(256, (v + 255) / 256 * 256));
+  }
+  // >= 4 chunks once the call is large enough for the copies to matter, never below 2048 frames per chunk
+  int c = ((n_frames + 3) / 4 + 1023) / 1024 * 1024;
+  return std::min(maxb, std::max(2048, c));
+}
+
 static int decode_host(lutldpc_decoder* h, int n_frames, const uint8_t* cha, const uint8_t* msg, const double* llr,
                        uint8_t* out_bits, int32_t* out_iters, TraceSink* tr) {
   CKH(cudaSetDevice(h->device), "cudaSetDevice");
-  const int N = h->m.nvar, maxb = tr ? n_frames : h->max_batch_frames();
+  if (n_frames == 0) return LUTLDPC_OK;
+  const int N = h->m.nvar;
+  const int chunk = tr ? n_frames : host_chunk_frames(h, n_frames);
+  const int n_chunks = (n_frames + chunk - 1) / chunk;
   cudaStream_t st = h->stream;
-  for (int f0 = 0; f0 < n_frames; f0 += maxb) {
-    int nf = std::min(maxb, n_frames - f0);
-    size_t cnt = (size_t)nf * N;
-    CKH(h->buf_lab_cha.ensure(cnt), "alloc labels");
-    CKH(h->buf_lab_msg.ensure(cnt), "alloc labels");
-    CKH(h->buf_out.ensure(cnt), "alloc out");
-    if (llr) {
-      CKH(h->buf_llr.ensure(cnt), "alloc llr");
-      CKH(cudaMemcpyAsync(h->buf_llr.p, llr + (size_t)f0 * N, cnt * 8, cudaMemcpyHostToDevice, st), "H2D llr");
-      CKH(launch_quantize(h->buf_llr.p, cnt, h->d_qb_cha.p, (int)h->m.qb_Cha.size(), h->d_qb_msg.p,
-                          (int)h->m.qb_Msg.size(), h->d_cha2msg.p, h->init_mode == LUTLDPC_INIT_QCHA,
-                          h->buf_lab_cha.p, h->buf_lab_msg.p, st), "quantize");
-    } else {
-      CKH(cudaMemcpyAsync(h->buf_lab_cha.p, cha + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, st), "H2D cha");
-      CKH(cudaMemcpyAsync(h->buf_lab_msg.p, msg + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, st), "H2D msg");
+  HostPipe& hp = h->pipe;
+  if (!hp.s_in) {
+    CKH(cudaStreamCreateWithFlags(&hp.s_in, cudaStreamNonBlocking), "stream");
+    CKH(cudaStreamCreateWithFlags(&hp.s_out, cudaStreamNonBlocking), "stream");
+    for (int i = 0; i < 2; ++i) {
+      CKH(cudaEventCreateWithFlags(&hp.ev_in[i], cudaEventDisableTiming), "event");
+      CKH(cudaEventCreateWithFlags(&hp.ev_used[i], cudaEventDisableTiming), "event");
+      CKH(cudaEventCreateWithFlags(&hp.ev_dec[i], cudaEventDisableTiming), "event");
+      CKH(cudaEventCreateWithFlags(&hp.ev_out[i], cudaEventDisableTiming), "event");
     }
-    int rc = h->run_batch(nf, h->buf_lab_cha.p, h->buf_lab_msg.p, tr);
-    if (rc) return rc;
-    CKH(launch_unpack(h->g, h->b, h->buf_out.p, st), "unpack");
-    h->launched(KIND_UNPACK);
-    CKH(cudaMemcpyAsync(out_bits + (size_t)f0 * N, h->buf_out.p, cnt, cudaMemcpyDeviceToHost, st), "D2H bits");
-    if (out_iters)
-      CKH(cudaMemcpyAsync(out_iters + f0, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToHost, st), "D2H iters");
-    CKH(cudaStreamSynchronize(st), "sync");
   }
+  const size_t cap = (size_t)std::min(chunk, n_frames) * N;
+  for (int i = 0; i < (n_chunks > 1 ? 2 : 1); ++i) {
+    CKH(hp.lab_cha[i].ensure(cap), "alloc labels");
+    CKH(hp.lab_msg[i].ensure(cap), "alloc labels");
+    CKH(hp.out[i].ensure(cap), "alloc out");
+    CKH(hp.its[i].ensure((size_t)std::min(chunk, n_frames)), "alloc iters");
+    if (llr) CKH(hp.llr[i].ensure(cap), "alloc llr");
+  }
+  // inputs of the previous call on the handle's stream may still be in flight: order the first copy after them
+  CKH(cudaEventRecord(hp.ev_used[0], st), "event");
+  CKH(cudaEventRecord(hp.ev_used[1], st), "event");
+  auto h2d = [&](int c) -> int {
+    const int slot = c & 1, f0 = c * chunk, nf = std::min(chunk, n_frames - f0);
+    const size_t cnt = (size_t)nf * N;
+    CKH(cudaStreamWaitEvent(hp.s_in, hp.ev_used[slot], 0), "wait");  // staging slot consumed by chunk c-2
+    if (llr) {
+      CKH(cudaMemcpyAsync(hp.llr[slot].p, llr + (size_t)f0 * N, cnt * 8, cudaMemcpyHostToDevice, hp.s_in), "H2D llr");
+    } else {
+      CKH(cudaMemcpyAsync(hp.lab_cha[slot].p, cha + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, hp.s_in), "H2D cha");
+      CKH(cudaMemcpyAsync(hp.lab_msg[slot].p, msg + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, hp.s_in), "H2D msg");
+    }
+    CKH(cudaEventRecord(hp.ev_in[slot], hp.s_in), "event");
+    return LUTLDPC_OK;
+  };
+  int rc = h2d(0);
+  if (rc) return rc;
+  for (int c = 0; c < n_chunks; ++c) {
+    const int slot = c & 1, f0 = c * chunk, nf = std::min(chunk, n_frames - f0);
+    const size_t cnt = (size_t)nf * N;
+    if (c + 1 < n_chunks && (rc = h2d(c + 1))) return rc;
+    CKH(cudaStreamWaitEvent(st, hp.ev_in[slot], 0), "wait");
+    if (llr)
+      CKH(launch_quantize(hp.llr[slot].p, cnt, h->d_qb_cha.p, (int)h->m.qb_Cha.size(), h->d_qb_msg.p,
+                          (int)h->m.qb_Msg.size(), h->d_cha2msg.p, h->init_mode == LUTLDPC_INIT_QCHA,
+                          hp.lab_cha[slot].p, hp.lab_msg[slot].p, st), "quantize");
+    rc = h->run_batch(nf, hp.lab_cha[slot].p, hp.lab_msg[slot].p, tr);
+    if (rc) return rc;
+    CKH(cudaEventRecord(hp.ev_used[slot], st), "event");
+    if (c >= 2) CKH(cudaStreamWaitEvent(st, hp.ev_out[slot], 0), "wait");  // results of chunk c-2 have left
+    CKH(launch_unpack(h->g, h->b, hp.out[slot].p, st), "unpack");
+    h->launched(KIND_UNPACK);
+    CKH(cudaMemcpyAsync(hp.its[slot].p, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToDevice, st), "iters copy");
+    CKH(cudaEventRecord(hp.ev_dec[slot], st), "event");
+    CKH(cudaStreamWaitEvent(hp.s_out, hp.ev_dec[slot], 0), "wait");
+    CKH(cudaMemcpyAsync(out_bits + (size_t)f0 * N, hp.out[slot].p, cnt, cudaMemcpyDeviceToHost, hp.s_out), "D2H bits");
+    if (out_iters)
+      CKH(cudaMemcpyAsync(out_iters + f0, hp.its[slot].p, (size_t)nf * 4, cudaMemcpyDeviceToHost, hp.s_out), "D2H iters");
+    CKH(cudaEventRecord(hp.ev_out[slot], hp.s_out), "event");
+  }
+  CKH(cudaStreamSynchronize(hp.s_out), "sync");
+  CKH(cudaStreamSynchronize(st), "sync");
   return LUTLDPC_OK;
 }
 

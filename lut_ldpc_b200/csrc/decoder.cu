@@ -178,11 +178,15 @@ int lutldpc_decoder::init_device() {
     }
   }
   {  // staggered schedule: needs every VN class on the specialised code and min-sum checks with row tables
-    const char* e = getenv("LUTLDPC_NO_STAGGER");
-    bool want = m.minLUT && use_cn_exact && cn_exact.size() <= 4 && n_iter_slots >= 2 && !(e && e[0] == '1');
+    // Opt-in (LUTLDPC_STAGGER=1): measured on B200 the combined launch is bound by the integer ALU pipe, which
+    // both passes load (N=64800: 0.82 ms per half-iteration pair of launches vs 0.84 ms back to back), so the
+    // sequential schedule stays the default.  DESIGN.md section 5 has the ncu numbers.
+    const char* e = getenv("LUTLDPC_STAGGER");
+    bool want = m.minLUT && use_cn_exact && cn_exact.size() <= 4 && n_iter_slots >= 2 && e && e[0] == '1';
     std::vector<std::pair<double, int4>> items;
-    const int vn_ops = std::max(1, env_int("LUTLDPC_STAGGER_VN_OPS", 64));
-    const int cn_rows = std::max(1, env_int("LUTLDPC_STAGGER_CN_ROWS", 2));
+    const int vn_ops = std::max(1, env_int("LUTLDPC_STAGGER_VN_OPS", 32));
+    const int cn_rows = std::max(1, env_int("LUTLDPC_STAGGER_CN_ROWS", 16));
+    stg_cn_warps = std::max(1, std::min(8, env_int("LUTLDPC_STAGGER_CN_WARPS", 2)));
     for (int c = 0; c < nvc && want; ++c) {
       if (!vn_classes[c].n) continue;
       for (int t = 0; t + 1 < n_iter_slots; ++t) want &= var_progs[(size_t)t * nvc + c].fast_dv != 0;
@@ -196,20 +200,28 @@ int lutldpc_decoder::init_device() {
       for (int i = 0; i < nt; ++i)
         items.push_back({(i + 0.5) / nt, make_int4(j, i * per, std::min(per, vn_classes[c].n - i * per), 0)});
     }
-    want = want && !stg_classes.empty() && stagger_supported(stg_max_dv);
-    for (size_t k = 0; k < cn_exact.size() && want; ++k) {
-      const int nt = (cn_exact[k].n + cn_rows - 1) / cn_rows;
-      for (int i = 0; i < nt; ++i)
-        items.push_back({(i + 0.5) / nt, make_int4(8 + (int)k, i * cn_rows, std::min(cn_rows, cn_exact[k].n - i * cn_rows), 0)});
-    }
+    for (auto& cl : cn_exact) stg_max_dc = std::max(stg_max_dc, cl.degree);
+    want = want && !stg_classes.empty() && stagger_supported(stg_max_dv, stg_max_dc);
     if (want) {
+      // classes interleaved, so that the long tiles of the high degrees are spread over the whole launch
       std::stable_sort(items.begin(), items.end(), [](const std::pair<double, int4>& a, const std::pair<double, int4>& b2) {
         return a.first < b2.first;
       });
       std::vector<int4> flat;
       for (auto& t : items) flat.push_back(t.second);
-      n_stg_items = (int)flat.size();
-      CK(d_stg_items.upload(flat), "upload stagger items");
+      n_stg_vn_items = (int)flat.size();
+      CK(d_stg_vn_items.upload(flat), "upload stagger items");
+      flat.clear();
+      for (size_t k = 0; k < cn_exact.size(); ++k)
+        for (int i = 0; i < cn_exact[k].n; i += cn_rows)
+          flat.push_back(make_int4((int)k, i, std::min(cn_rows, cn_exact[k].n - i), 0));
+      n_stg_cn_items = (int)flat.size();
+      CK(d_stg_cn_items.upload(flat), "upload stagger items");
+      CK(d_stg_ctr.ensure((size_t)2 * (2 * m.max_iters + 4)), "alloc stagger counters");
+      int sms = 0;
+      CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device), "device attribute");
+      stg_ctas = 2 * sms;
+      CK(configure_stagger(), "configure stagger kernel");
       CK(cudaMallocHost((void**)&h_poll, 8 * sizeof(uint32_t)), "cudaMallocHost");
       for (auto& ev : ev_poll) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming), "cudaEventCreate");
       stagger_ok = true;
@@ -457,7 +469,7 @@ int lutldpc_decoder::run_passes_staggered() {
   const int W = b.W;
   const int Wa = std::min(W, ((W / 2 + kNodeThreads - 1) / kNodeThreads) * kNodeThreads);
   const int w0[2] = {0, Wa}, w1[2] = {Wa, W};
-  const int n_colblocks = (std::max(Wa, W - Wa) + kStaggerCols - 1) / kStaggerCols;
+  CK(cudaMemsetAsync(d_stg_ctr.p, 0, d_stg_ctr.n * sizeof(unsigned int), st), "memset counters");
   uint32_t* n_act = b.n_active;  // two device slots, one per half
   bool alive[2] = {true, true};
   if (pisc) {  // :277
@@ -479,6 +491,11 @@ int lutldpc_decoder::run_passes_staggered() {
     StaggerParams P;
     memset(&P, 0, sizeof P);
     P.W = W;
+    P.vn_items = d_stg_vn_items.p; P.n_vn_items = n_stg_vn_items;
+    P.cn_items = d_stg_cn_items.p; P.n_cn_items = n_stg_cn_items;
+    P.n_cn_warps = stg_cn_warps;
+    P.ring_rows = stagger_ring_rows(stg_max_dc);
+    P.ctr = d_stg_ctr.p + 2 * s;
     int fin_half = -1, fin_ii = 0;
     bool any = false;
     for (int h = 0; h < 2; ++h) {
@@ -499,6 +516,8 @@ int lutldpc_decoder::run_passes_staggered() {
           const int c = stg_classes[j];
           const ProgRef& r = var_progs[(size_t)t * nvc + c];
           P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].list.p, r.fast_dv, r.q_out};
+          P.tab_off[j] = P.tab_bytes;
+          P.tab_bytes += (r.fast_dv - 1) * 128;
         }
       }
     }
@@ -507,7 +526,7 @@ int lutldpc_decoder::run_passes_staggered() {
       P.cn_rows[k] = cn_exact[k].list.p;
       P.cn_dc[k] = cn_exact[k].degree;
     }
-    CK(launch_stagger(P, stg_max_dv, d_stg_items.p, n_stg_items, n_colblocks, g, b, st), "stagger"); launched(KIND_STEP);
+    CK(launch_stagger(P, stg_max_dv, stg_ctas, g, b, st), "stagger"); launched(KIND_STEP);
     if (fin_half >= 0) {  // psc: VN pass ii-1 unanimous and syndrome zero -> return ii (:327)
       CK(launch_finalize_range(FIN_ITER, fin_ii, b, w0[fin_half], w1[fin_half], n_act + fin_half, st), "finalize");
       launched(KIND_FINALIZE);

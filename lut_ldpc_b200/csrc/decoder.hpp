@@ -60,6 +60,23 @@ struct NodeClass {  // all variable (or check) nodes of one degree slot
   DevBuf<int32_t> list;
 };
 
+// streams, events and double-buffered device staging of the pipelined host-buffer decode (capi.cu: decode_host)
+struct HostPipe {
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_used[2] = {nullptr, nullptr}, ev_dec[2] = {nullptr, nullptr},
+              ev_out[2] = {nullptr, nullptr};
+  DevBuf<uint8_t> lab_cha[2], lab_msg[2], out[2];
+  DevBuf<int32_t> its[2];
+  DevBuf<double> llr[2];
+  ~HostPipe() {
+    for (int i = 0; i < 2; ++i)
+      for (cudaEvent_t e : {ev_in[i], ev_used[i], ev_dec[i], ev_out[i]})
+        if (e) cudaEventDestroy(e);
+    if (s_in) cudaStreamDestroy(s_in);
+    if (s_out) cudaStreamDestroy(s_out);
+  }
+};
+
 struct TraceSink {
   int frame = -1, max_rec = 0, n_rec = 0;
   uint8_t* msgs = nullptr;
@@ -91,8 +108,9 @@ struct lutldpc_decoder {
   // staggered schedule (stagger.cu): every VN class specialised, min-sum checks with row tables
   bool stagger_ok = false;
   std::vector<int> stg_classes;  // VN class behind StaggerParams::c[j]
-  lutldpc::DevBuf<int4> d_stg_items;
-  int n_stg_items = 0, stg_max_dv = 0;
+  lutldpc::DevBuf<int4> d_stg_vn_items, d_stg_cn_items;
+  lutldpc::DevBuf<unsigned int> d_stg_ctr;  // two tile counters per launch of a batch
+  int n_stg_vn_items = 0, n_stg_cn_items = 0, stg_max_dv = 0, stg_max_dc = 0, stg_ctas = 0, stg_cn_warps = 2;
   uint32_t* h_poll = nullptr;    // pinned [4][2]: unfinished frames per half, ring of lagged polls
   cudaEvent_t ev_poll[4] = {nullptr, nullptr, nullptr, nullptr};
   std::vector<lutldpc::ProgRef> var_progs;  // [iter slot][vn class]; last slot = decision trees
@@ -104,6 +122,7 @@ struct lutldpc_decoder {
   lutldpc::BatchBuffers b;
   lutldpc::DevBuf<uint32_t> buf_msgs, buf_cha, buf_flags;
   lutldpc::DevBuf<uint8_t> buf_hard, buf_lab_cha, buf_lab_msg, buf_out, buf_trace;
+  lutldpc::HostPipe pipe;
   lutldpc::DevBuf<int32_t> buf_iters;
   lutldpc::DevBuf<double> buf_llr;
   lutldpc::DevBuf<uint8_t> buf_cw;                 // transmitted codeword bits, [nvar][W] like hard

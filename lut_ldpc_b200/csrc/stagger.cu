@@ -16,171 +16,198 @@
 
 namespace lutldpc {
 
-// checks [r0, r1) of an exact-degree row table, VEC consecutive word columns starting at w
-template <int DC, int VEC>
-__device__ __forceinline__ void cn_exact_rows(const int32_t* __restrict__ rows, int r0, int r1, int W, int w,
-                                              const QMask qm, uint32_t* __restrict__ msgs, uint32_t (&fail)[VEC]) {
-  typedef typename WordVec<VEC>::T V;
-  union U { V v; uint32_t u[VEC]; };
-  for (int i = r0; i < r1; ++i) {
-    const int32_t* r = rows + (size_t)i * DC;
-    uint32_t* p[DC];
-#pragma unroll
-    for (int k = 0; k < DC; ++k) p[k] = msgs + (size_t)r[k] * W + w;
-    U x[DC];
-#pragma unroll
-    for (int k = 0; k < DC; ++k) x[k].v = __ldcs(reinterpret_cast<const V*>(p[k]));
-    CnAccG a[VEC];
-#pragma unroll
-    for (int j = 0; j < VEC; ++j) cng_init(a[j], x[0].u[j], x[1].u[j], qm);
-#pragma unroll
-    for (int k = 2; k < DC; ++k) {
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) cng_accum(a[j], x[k].u[j], qm);
-    }
-#pragma unroll
-    for (int k = 0; k < DC; ++k) {
-      U o;
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) o.u[j] = cng_emit(a[j], x[k].u[j], qm);
-      __stcs(reinterpret_cast<V*>(p[k]), o.v);
-    }
-#pragma unroll
-    for (int j = 0; j < VEC; ++j) fail[j] |= a[j].par;
-  }
+// ---------------------------------------------------------------------------------------------
+// Persistent, warp-specialised form.  2 CTAs per SM; every CTA keeps the LUTs of all degree classes of
+// this iteration in shared memory.  Warps pull work from two global queues:
+//   * VARIABLE tiles (a few nodes of one class x 128 word columns): vn_fast_body, values in registers;
+//   * CHECK tiles (a few checks x 128 word columns, 4 columns per lane): the edge rows are fetched with
+//     cp.async (LDGSTS, no registers held while in flight) into a per-warp ring of S rows, so two or
+//     three check warps per CTA keep enough bytes in flight for the whole pass while the other ~22
+//     warps spend the issue slots on look-ups.  Check warps join the variable queue when theirs is dry.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-// any degree: accumulate, then re-read (the lines are in L1/L2) and emit; few registers
-template <int VEC>
-__device__ __forceinline__ void cn_any_rows(const int32_t* __restrict__ rows, int dc, int r0, int r1, int W, int w,
-                                            const QMask qm, uint32_t* __restrict__ msgs, uint32_t (&fail)[VEC]) {
-  typedef typename WordVec<VEC>::T V;
-  union U { V v; uint32_t u[VEC]; };
-  for (int i = r0; i < r1; ++i) {
-    const int32_t* r = rows + (size_t)i * dc;
-    U x0, x1;
-    x0.v = *reinterpret_cast<const V*>(msgs + (size_t)r[0] * W + w);
-    x1.v = *reinterpret_cast<const V*>(msgs + (size_t)r[1] * W + w);
-    CnAccG a[VEC];
-#pragma unroll
-    for (int j = 0; j < VEC; ++j) cng_init(a[j], x0.u[j], x1.u[j], qm);
-    for (int k = 2; k < dc; ++k) {
-      U x;
-      x.v = *reinterpret_cast<const V*>(msgs + (size_t)r[k] * W + w);
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) cng_accum(a[j], x.u[j], qm);
+constexpr int kRingBytes = 16384;             // S * dc * 512 B of edge rows per check warp
+constexpr int kRingStride = kRingBytes + 512;  // + S * 32 edge indices
+
+// checks [r0, r0+n) of a row table, 4 word columns per lane starting at w; any degree <= 32
+template <int S>
+__device__ __forceinline__ void cn_tile(const int32_t* __restrict__ rows, int dc, int r0, int n, int W, int w,
+                                        bool active, const QMask qm, uint32_t* __restrict__ msgs, uint4* ring,
+                                        int32_t* idx, uint32_t (&fail)[4]) {
+  const int lane = threadIdx.x & 31;
+  union U { uint4 v; uint32_t u[4]; };
+  auto issue = [&](int i, int slot) {
+    if (i < n) {
+      if (lane < dc) idx[slot * 32 + lane] = rows[(size_t)(r0 + i) * dc + lane];
+      __syncwarp();
+      if (active) {
+        for (int k = 0; k < dc; ++k)
+          cp_async16(&ring[(slot * dc + k) * 32 + lane], msgs + (size_t)idx[slot * 32 + k] * W + w);
+      }
     }
-    for (int k = 0; k < dc; ++k) {
-      V* p = reinterpret_cast<V*>(msgs + (size_t)r[k] * W + w);
-      U x, o;
-      x.v = *p;
+    cp_async_commit();
+  };
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) o.u[j] = cng_emit(a[j], x.u[j], qm);
-      *p = o.v;
+  for (int s = 0; s < S; ++s) issue(s, s);
+  for (int i = 0; i < n; ++i) {
+    const int slot = i % S;
+    cp_async_wait<S - 1>();
+    if (active) {
+      const uint4* rr = ring + (size_t)slot * dc * 32 + lane;
+      U x0, x1;
+      x0.v = rr[0];
+      x1.v = rr[32];
+      CnAccG a[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) cng_init(a[j], x0.u[j], x1.u[j], qm);
+      for (int k = 2; k < dc; ++k) {
+        U x;
+        x.v = rr[k * 32];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) cng_accum(a[j], x.u[j], qm);
+      }
+      for (int k = 0; k < dc; ++k) {
+        U x, o;
+        x.v = rr[k * 32];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o.u[j] = cng_emit(a[j], x.u[j], qm);
+        __stcs(reinterpret_cast<uint4*>(msgs + (size_t)idx[slot * 32 + k] * W + w), o.v);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) fail[j] |= a[j].par;
     }
-#pragma unroll
-    for (int j = 0; j < VEC; ++j) fail[j] |= a[j].par;
+    __syncwarp();
+    issue(i + S, slot);
   }
+  cp_async_wait<0>();
 }
 
-template <int MAXDV, int MAXDC, int VEC>
-__global__ void __launch_bounds__(kNodeThreads) k_stagger(const StaggerParams P, const int4* __restrict__ items,
-                                                           const int32_t* __restrict__ vn_edge0,
-                                                           uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
-                                                           uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
-                                                           uint32_t* __restrict__ vn_fail,
-                                                           uint32_t* __restrict__ cn_fail) {
-  __shared__ __align__(128) uint8_t tabs[(MAXDV - 1) * 128];
+__device__ __forceinline__ unsigned grab(unsigned int* ctr) {
+  unsigned t = 0;
+  if ((threadIdx.x & 31) == 0) t = atomicAdd(ctr, 1u);
+  return __shfl_sync(0xFFFFFFFFu, t, 0);
+}
+
+template <int MAXDV>
+struct StaggerCfg {
+  static constexpr int kThreads = MAXDV <= 8 ? 640 : 512;  // x 2 CTAs per SM: 48 / 64 registers per thread
+};
+
+template <int MAXDV>
+__global__ void __launch_bounds__(StaggerCfg<MAXDV>::kThreads, 2)
+    k_stagger(const StaggerParams P, const int32_t* __restrict__ vn_edge0, uint32_t* __restrict__ msgs,
+              const uint32_t* __restrict__ cha, uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
+              uint32_t* __restrict__ vn_fail, uint32_t* __restrict__ cn_fail) {
+  extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bar;
-  const int4 it = items[blockIdx.x];
   const int W = P.W;
-  if (it.x >= 8) {
-    // ---------------- check pass
-    const int cls = it.x - 8;
-    const int dc = P.cn_dc[cls];
-    const int32_t* rows = P.cn_rows[cls];
+  const bool have_vn = P.vn_w1 > P.vn_w0, have_cn = P.cn_w1 > P.cn_w0;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, n_warps = blockDim.x >> 5;
+  uint8_t* tabs = smem;
+  uint8_t* rings = smem + ((P.tab_bytes + 127) & ~127);
+  if (have_vn) {  // LUTs of every degree class of this iteration: bulk copies, one mbarrier
+    if (threadIdx.x == 0) {
+      mbar_init(&bar, 1);
+      fence_barrier_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      mbar_expect_tx(&bar, (uint32_t)P.tab_bytes);
+      for (int j = 0; j < 8; ++j)
+        if (P.c[j].dv) bulk_g2s(tabs + P.tab_off[j], P.c[j].tables, (uint32_t)(P.c[j].dv - 1) * 128u, &bar);
+    }
+  }
+  // ---------------- check tiles (the last n_cn_warps warps of the CTA start here)
+  if (have_cn && warp >= n_warps - P.n_cn_warps) {
+    const int cw = warp - (n_warps - P.n_cn_warps);
+    uint4* ring = reinterpret_cast<uint4*>(rings + (size_t)cw * kRingStride);
+    int32_t* idx = reinterpret_cast<int32_t*>(rings + (size_t)cw * kRingStride + kRingBytes);
     const QMask qm = make_qmask(P.cn_q);
-    const int base = P.cn_w0 + blockIdx.y * kStaggerCols;
-    typedef typename WordVec<VEC>::T V;
-    union U { V v; uint32_t u[VEC]; };
-#pragma unroll 1
-    for (int s = 0; s < kStaggerCols / (kNodeThreads * VEC); ++s) {
-      const int w = base + (s * kNodeThreads + threadIdx.x) * VEC;
-      if (w >= P.cn_w1) break;
-      U dn;
-      dn.v = *reinterpret_cast<const V*>(done + w);
-      bool all_done = true;
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) all_done &= dn.u[j] == kNibOnes;
-      if (all_done) continue;
-      uint32_t fail[VEC];
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) fail[j] = 0;
-      switch (dc <= MAXDC ? dc : 0) {
-#define X(D)                                                                                   \
-  case D:                                                                                      \
-    if constexpr (D <= MAXDC) cn_exact_rows<D, VEC>(rows, it.y, it.y + it.z, W, w, qm, msgs, fail); \
-    break;
-        LUTLDPC_EXACT_DCS(X)
-#undef X
-        default:
-          cn_any_rows<VEC>(rows, dc, it.y, it.y + it.z, W, w, qm, msgs, fail);
+    const unsigned ncb = (unsigned)(P.cn_w1 - P.cn_w0 + 127) / 128u;
+    const unsigned total = (unsigned)P.n_cn_items * ncb;
+    for (;;) {
+      const unsigned t = grab(P.ctr + 1);
+      if (t >= total) break;
+      const int4 it = P.cn_items[t / ncb];
+      const int w = P.cn_w0 + (int)(t % ncb) * 128 + lane * 4;
+      bool active = w < P.cn_w1;
+      if (active) {
+        const uint4 dn = *reinterpret_cast<const uint4*>(done + w);
+        active = !(dn.x == kNibOnes && dn.y == kNibOnes && dn.z == kNibOnes && dn.w == kNibOnes);
       }
-      if (P.cn_want) {
+      uint32_t fail[4] = {0, 0, 0, 0};
+      const int32_t* rows = P.cn_rows[it.x];
+      const int dc = P.cn_dc[it.x];
+      if (P.ring_rows == 4) cn_tile<4>(rows, dc, it.y, it.z, W, w, active, qm, msgs, ring, idx, fail);
+      else if (P.ring_rows == 2) cn_tile<2>(rows, dc, it.y, it.z, W, w, active, qm, msgs, ring, idx, fail);
+      else cn_tile<1>(rows, dc, it.y, it.z, W, w, active, qm, msgs, ring, idx, fail);
+      if (P.cn_want && active) {
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) flag_or(&cn_fail[w + j], (fail[j] >> qm.s) & kNibOnes);
+        for (int j = 0; j < 4; ++j) flag_or(&cn_fail[w + j], (fail[j] >> qm.s) & kNibOnes);
       }
     }
-    return;
   }
-  // ---------------- variable pass
-  if (P.vn_w0 + (int)blockIdx.y * kStaggerCols >= P.vn_w1) return;
-  const FusedVnClass cls = P.c[it.x];
-  stage_to_smem(tabs, cls.tables, (uint32_t)(cls.dv - 1) * 128u, &bar);
+  if (!have_vn) return;
+  // ---------------- variable tiles
+  mbar_wait(&bar, 0);
+  const unsigned ncb = (unsigned)(P.vn_w1 - P.vn_w0 + 127) / 128u;
+  const unsigned total = (unsigned)P.n_vn_items * ncb;
+  for (;;) {
+    const unsigned t = grab(P.ctr);
+    if (t >= total) break;
+    const int4 it = P.vn_items[t / ncb];
+    const FusedVnClass cls = P.c[it.x];
+    const uint8_t* ctab = tabs + P.tab_off[it.x];
+    const int wb = P.vn_w0 + (int)(t % ncb) * 128 + lane;
 #pragma unroll 1
-  for (int s = 0; s < kStaggerCols / kNodeThreads; ++s) {
-    const int w = P.vn_w0 + blockIdx.y * kStaggerCols + s * kNodeThreads + threadIdx.x;
-    if (w >= P.vn_w1) break;
-    const uint32_t dn = done[w];
-    if (dn == kNibOnes) continue;
-    const uint32_t done_byte = nib_bits_to_byte(dn, 0);
-    uint32_t failacc = 0;
-    switch (cls.dv) {
-#define X(D)                                                                                                    \
-  case D:                                                                                                       \
-    if constexpr (D <= MAXDV)                                                                                   \
-      vn_fast_body<D>(tabs, cls.node_list, it.y, it.y + it.z, vn_edge0, W, w, msgs, cha, hard, done_byte,       \
-                      P.vn_want, cls.q_out, failacc);                                                           \
+    for (int s = 0; s < 4; ++s) {
+      const int w = wb + s * 32;
+      if (w >= P.vn_w1) break;
+      const uint32_t dn = done[w];
+      if (dn == kNibOnes) continue;
+      const uint32_t done_byte = nib_bits_to_byte(dn, 0);
+      uint32_t failacc = 0;
+      switch (cls.dv) {
+#define X(D)                                                                                                 \
+  case D:                                                                                                    \
+    if constexpr (D <= MAXDV)                                                                                \
+      vn_fast_body<D>(ctab, cls.node_list, it.y, it.y + it.z, vn_edge0, W, w, msgs, cha, hard, done_byte,    \
+                      P.vn_want, cls.q_out, failacc);                                                        \
     break;
-      LUTLDPC_FAST_DVS(X)
+        LUTLDPC_FAST_DVS(X)
 #undef X
+      }
+      if (P.vn_want) flag_or(&vn_fail[w], failacc & kNibOnes);
     }
-    if (P.vn_want) flag_or(&vn_fail[w], failacc & kNibOnes);
   }
 }
 
-static int env_int(const char* name, int dflt) {
-  const char* s = getenv(name);
-  return s && *s ? atoi(s) : dflt;
+static constexpr int kStaggerMaxSmem = 160 * 1024;
+
+bool stagger_supported(int max_dv, int max_dc) { return max_dv >= 2 && max_dv <= 20 && max_dc >= 2 && max_dc <= 32; }
+int stagger_ring_rows(int max_dc) { return max_dc <= 8 ? 4 : max_dc <= 16 ? 2 : 1; }
+
+cudaError_t configure_stagger() {
+  cudaError_t e = cudaFuncSetAttribute(k_stagger<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStaggerMaxSmem);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(k_stagger<20>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStaggerMaxSmem);
 }
 
-// exact-degree (fully unrolled) check code is instantiated up to kStaggerMaxExactDc; larger or rare degrees
-// take the re-reading loop, which keeps the register count of the whole kernel low for the VN items
-constexpr int kStaggerMaxExactDc = 8;
-int stagger_max_exact_dc() { return kStaggerMaxExactDc; }
-bool stagger_supported(int max_dv) { return max_dv >= 2 && max_dv <= 20; }
-
-cudaError_t launch_stagger(const StaggerParams& P, int max_dv, const int4* d_items, int n_items, int n_colblocks,
-                           const GraphArrays& g, const BatchBuffers& b, cudaStream_t st) {
-  static const int vec = env_int("LUTLDPC_STAGGER_VEC", 2);
-  dim3 grid(n_items, n_colblocks);
-#define ARGS P, d_items, g.vn_edge0, b.msgs, b.cha, b.hard, b.done, b.vn_fail, b.cn_fail
-  if (max_dv <= 8) {
-    if (vec == 4) k_stagger<8, kStaggerMaxExactDc, 4><<<grid, kNodeThreads, 0, st>>>(ARGS);
-    else k_stagger<8, kStaggerMaxExactDc, 2><<<grid, kNodeThreads, 0, st>>>(ARGS);
-  } else {
-    k_stagger<20, kStaggerMaxExactDc, 2><<<grid, kNodeThreads, 0, st>>>(ARGS);
-  }
+cudaError_t launch_stagger(const StaggerParams& P, int max_dv, int n_ctas, const GraphArrays& g, const BatchBuffers& b,
+                           cudaStream_t st) {
+  const size_t smem = (size_t)((P.tab_bytes + 127) & ~127) + (size_t)P.n_cn_warps * kRingStride;
+  if (smem > (size_t)kStaggerMaxSmem) return cudaErrorInvalidConfiguration;
+#define ARGS P, g.vn_edge0, b.msgs, b.cha, b.hard, b.done, b.vn_fail, b.cn_fail
+  if (max_dv <= 8) k_stagger<8><<<n_ctas, StaggerCfg<8>::kThreads, smem, st>>>(ARGS);
+  else k_stagger<20><<<n_ctas, StaggerCfg<20>::kThreads, smem, st>>>(ARGS);
 #undef ARGS
   return cudaGetLastError();
 }

@@ -92,13 +92,15 @@ def test_counters_are_reproducible_and_split_invariant(L):
 
 
 def test_simulate_matches_decode_of_same_frames(L):
-    """The fused path decodes exactly like lut_decode: count of negative returns == decode_failures, and
-    every frame that converged to a codeword different from the sent one is a frame error."""
+    """Counter sanity of the fused path.  BLERC counts blocks of the K data bits (src/LDPC_BER_Sim.cpp:259,
+    :291), so a decode failure (negative lut_decode return) whose wrong bits are all parity bits is not a
+    frame error: the two counters are not ordered."""
     dec = L.Decoder(_golden.bundle_path("c1b_reg36_n1000"))
     dec.set_exit_conditions(dec.max_iters, True, True)
     c = dec.simulate_snr(2.0, 5000, seed=3, zero_codeword=True)
-    assert c.decode_failures <= c.frame_errors <= c.frames
-    assert c.sum_iters >= c.frames
+    assert 0 < c.decode_failures <= c.frames and 0 < c.frame_errors <= c.frames
+    assert c.data_bit_errors >= c.frame_errors
+    assert c.frames <= c.sum_iters <= c.frames * dec.max_iters
 
 
 def test_ber_sim_command_line(L, tmp_path):

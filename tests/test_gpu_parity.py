@@ -141,35 +141,41 @@ def test_generic_interpreter_still_bit_exact(L):
     assert np.array_equal(it, fx["ret"]) and np.array_equal(out, fx["out"])
 
 
-def _no_stagger_decoder(L, cfg):
+_stg = {}
+
+
+def _stagger_decoder(L, cfg):
+    """Decoder with the opt-in staggered schedule (LUTLDPC_STAGGER=1 at creation)."""
     import os
-    os.environ["LUTLDPC_NO_STAGGER"] = "1"
-    try:
-        d = L.Decoder(_golden.bundle_path(cfg))
-    finally:
-        del os.environ["LUTLDPC_NO_STAGGER"]
-    assert not d.staggered_schedule
-    return d
+    if cfg not in _stg:
+        os.environ["LUTLDPC_STAGGER"] = "1"
+        try:
+            _stg[cfg] = L.Decoder(_golden.bundle_path(cfg))
+        finally:
+            del os.environ["LUTLDPC_STAGGER"]
+    return _stg[cfg]
 
 
 @pytest.mark.parametrize("cfg,tag", [(c, t) for c, t in _golden.all_fixtures()
                                      if c in ("c1b_reg36_n1000", "c2_irr_n500", "c3_irr_n10000", "x_varq_reuse",
                                               "x_qcha_irr_n1000")])
 def test_staggered_schedule_fixture_bit_exact(L, cfg, tag):
-    """Batches of >= 2048 frames run as two halves half an iteration apart (stagger.cu): the reference's
-    fixture frames, shuffled over a ragged batch that spans both halves, still decode bit-exactly."""
+    """Opt-in staggered schedule (stagger.cu): batches of >= 2048 frames run as two halves half an iteration
+    apart.  The reference's fixture frames, shuffled over a ragged batch that spans both halves, still decode
+    bit-exactly (the default sequential schedule sees the same large batches in the other tests)."""
     fx = pyoracle.read_fixture(_golden.fixture_path(cfg, tag))
     a = _golden.fixture_args(cfg, tag)
-    dec = _dec(L, cfg)
+    dec = _stagger_decoder(L, cfg)
     # 4-bit balanced-tree decoders take the staggered schedule; the 3-bit ones stay sequential (same test)
     assert bool(dec.staggered_schedule) == (cfg in ("c1b_reg36_n1000", "c2_irr_n500", "c3_irr_n10000"))
-    dec.set_exit_conditions(dec.max_iters, a["psc"], a["pisc"])
     nfx = fx["cha"].shape[0]
-    for n in (2048, 2309):
-        idx = np.random.default_rng(n).integers(0, nfx, n)
-        out, it = dec.decode_quantized(fx["cha"][idx], fx["msg"][idx])
-        assert np.array_equal(it, fx["ret"][idx])
-        assert np.array_equal(out, fx["out"][idx])
+    for d in (dec, _dec(L, cfg)):
+        d.set_exit_conditions(d.max_iters, a["psc"], a["pisc"])
+        for n in (2048, 2309):
+            idx = np.random.default_rng(n).integers(0, nfx, n)
+            out, it = d.decode_quantized(fx["cha"][idx], fx["msg"][idx])
+            assert np.array_equal(it, fx["ret"][idx])
+            assert np.array_equal(out, fx["out"][idx])
 
 
 @pytest.mark.parametrize("cfg", ["c2_irr_n500", "c3_irr_n10000", "c5_n64800"])
@@ -177,8 +183,9 @@ def test_staggered_equals_sequential_schedule(L, cfg):
     """Same seeded noisy inputs through the staggered and the sequential pass schedule (and, for a few
     frames of the small code, the oracle): identical decisions and lut_decode returns, incl. frames that
     finish early, late and never."""
-    dec = _dec(L, cfg)
-    ref = _no_stagger_decoder(L, cfg)
+    dec = _stagger_decoder(L, cfg)
+    ref = _dec(L, cfg)
+    assert dec.staggered_schedule and not ref.staggered_schedule
     n = 2560 if cfg != "c5_n64800" else 2304
     snr = {"c2_irr_n500": 1.5, "c3_irr_n10000": 1.1, "c5_n64800": 1.2}[cfg]
     rng = np.random.default_rng(11)
