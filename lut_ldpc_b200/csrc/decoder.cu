@@ -251,7 +251,7 @@ int lutldpc_decoder::init_device() {
     if (r.bytes + (size_t)r.n_slots * kNodeThreads * 4 > 200 * 1024)
       return fail(LUTLDPC_ERR_MODEL, "a node program (LUTs + value slots) exceeds the 200 KiB shared-memory budget");
   CK(d_prog_blob.upload(blob), "upload node programs");
-  CK(cudaMallocHost((void**)&h_active, sizeof(uint32_t)), "cudaMallocHost");
+  CK(cudaMallocHost((void**)&h_active, 4 * sizeof(uint32_t)), "cudaMallocHost");
   CK(cudaEventCreate(&ev0), "cudaEventCreate");
   CK(cudaEventCreate(&ev1), "cudaEventCreate");
   return LUTLDPC_OK;
@@ -302,11 +302,14 @@ int lutldpc_decoder::ensure_batch(int n_frames) {
   CK(buf_cha.ensure((size_t)m.nvar * W), "alloc cha");
   CK(buf_hard.ensure((size_t)m.nvar * W), "alloc hard");
   CK(buf_flags.ensure((size_t)4 * W + 32), "alloc flags");
+  CK(buf_cols.ensure((size_t)W + W / 4), "alloc work lists");
   CK(buf_iters.ensure((size_t)8 * W), "alloc iters");
   b.msgs = buf_msgs.p; b.cha = buf_cha.p; b.hard = buf_hard.p;
   b.done = buf_flags.p; b.vn_fail = buf_flags.p + W; b.cn_fail = buf_flags.p + 2 * W; b.syn_fail = buf_flags.p + 3 * W;
   b.n_active = buf_flags.p + 4 * W;
   b.iters = buf_iters.p;
+  b.cols = buf_cols.p; b.grp4 = buf_cols.p + W;
+  b.host_cols = W; b.host_grp4 = W / 4;  // upper bounds until the first poll
   b.W = W; b.F = n_frames;
   return LUTLDPC_OK;
 }
@@ -363,9 +366,12 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   auto poll = [&](bool& all_done) -> int {
     all_done = false;
     if (poll_every <= 0) return 0;
-    CK(cudaMemcpyAsync(h_active, b.n_active, 4, cudaMemcpyDeviceToHost, st), "poll copy");
+    CK(cudaMemcpyAsync(h_active, b.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
     CK(cudaStreamSynchronize(st), "poll sync");
-    all_done = *h_active == 0;
+    all_done = h_active[0] == 0;
+    // the work lists only shrink, so their lengths at this poll bound every later launch
+    b.host_cols = (int)h_active[2];
+    b.host_grp4 = (int)h_active[3];
     return 0;
   };
   bool all_done = false;

@@ -120,7 +120,7 @@ struct lutldpc_decoder {
 
   // batch state
   lutldpc::BatchBuffers b;
-  lutldpc::DevBuf<uint32_t> buf_msgs, buf_cha, buf_flags;
+  lutldpc::DevBuf<uint32_t> buf_msgs, buf_cha, buf_flags, buf_cols;
   lutldpc::DevBuf<uint8_t> buf_hard, buf_lab_cha, buf_lab_msg, buf_out, buf_trace;
   lutldpc::HostPipe pipe;
   lutldpc::DevBuf<int32_t> buf_iters;

@@ -202,10 +202,14 @@ __global__ void __launch_bounds__(128) k_cn_minsum_v(const int32_t* __restrict__
 template <int DC, int VEC>
 __global__ void __launch_bounds__(128) k_cn_exact(const int32_t* __restrict__ rows, int W, int q,
                                                   uint32_t* __restrict__ msgs, const uint32_t* __restrict__ done,
-                                                  uint32_t* __restrict__ cn_fail, int want_fail) {
+                                                  uint32_t* __restrict__ cn_fail, int want_fail,
+                                                  const uint32_t* __restrict__ grp4,
+                                                  const uint32_t* __restrict__ n_lists) {
   typedef typename WordVec<VEC>::T V;
-  const int w = (blockIdx.y * blockDim.x + threadIdx.x) * VEC;
-  if (w >= W) return;
+  // thread i of the pass owns VEC adjacent columns of live group grp4[i / (4 / VEC)]
+  const int i = blockIdx.y * blockDim.x + threadIdx.x;
+  if (i >= (int)n_lists[3] * (4 / VEC)) return;
+  const int w = (int)grp4[i / (4 / VEC)] * 4 + (i % (4 / VEC)) * VEC;
   union U { V v; uint32_t u[VEC]; };
   U dn;
   dn.v = *reinterpret_cast<const V*>(done + w);
@@ -368,13 +372,62 @@ __global__ void __launch_bounds__(128) k_syndrome(const int32_t* __restrict__ cn
   if (x) flag_or(&syn_fail[w], byte_to_nib_bits(x));
 }
 
+// Single-CTA (1024 threads) order-preserving compaction of the live columns: cols = words with an
+// unfinished frame, grp4 = groups of 4 adjacent words with any such word; counts to n_active[2], [3].
+__device__ void build_lists(int W, const uint32_t* done, uint32_t* cols, uint32_t* grp4, uint32_t* n_active) {
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t base_s;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (int pass = 0; pass < 2; ++pass) {
+    const int n = pass == 0 ? W : W / 4;
+    uint32_t* list = pass == 0 ? cols : grp4;
+    if (threadIdx.x == 0) base_s = 0;
+    __syncthreads();
+    for (int c0 = 0; c0 < n; c0 += 1024) {
+      const int i = c0 + threadIdx.x;
+      bool live = false;
+      if (i < n) {
+        if (pass == 0) {
+          live = done[i] != kNibOnes;
+        } else {
+          const uint4 d = *reinterpret_cast<const uint4*>(done + 4 * i);
+          live = !(d.x == kNibOnes && d.y == kNibOnes && d.z == kNibOnes && d.w == kNibOnes);
+        }
+      }
+      const uint32_t bal = __ballot_sync(0xFFFFFFFFu, live);
+      if (lane == 0) wsum[wid] = __popc(bal);
+      __syncthreads();
+      uint32_t before = 0, total = 0;
+      for (int j = 0; j < 32; ++j) {
+        const uint32_t v = wsum[j];
+        before += j < wid ? v : 0;
+        total += v;
+      }
+      const uint32_t base = base_s;
+      if (live) list[base + before + __popc(bal & ((1u << lane) - 1u))] = (uint32_t)i;
+      __syncthreads();
+      if (threadIdx.x == 0) base_s = base + total;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) n_active[2 + pass] = base_s;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_build_lists(int W, const uint32_t* done, uint32_t* cols, uint32_t* grp4,
+                                                      uint32_t* n_active) {
+  build_lists(W, done, cols, grp4, n_active);
+}
+
 // Per-frame bookkeeping between passes (single CTA; W is at most a few thousand words).
 //   FIN_INIT  pisc: frames whose channel hard decision is a codeword return 0     (:277)
 //   FIN_ITER  psc : unanimous VNs + zero syndrome -> return `value` = ii+1        (:327)
 //   FIN_LAST  after the decision pass: +-max_iters                                (:346-349)
+// Covers columns [w0, w1); when that is the whole batch (W_lists > 0) the work lists are rebuilt.
 __global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int w0, int w1, uint32_t* done,
                                                    uint32_t* vn_fail, uint32_t* cn_fail, uint32_t* syn_fail,
-                                                   int32_t* iters, uint32_t* n_active) {
+                                                   int32_t* iters, uint32_t* n_active, int W_lists, uint32_t* cols,
+                                                   uint32_t* grp4, uint32_t* n_lists) {
   __shared__ uint32_t red[32];
   uint32_t cnt = 0;
   for (int w = w0 + threadIdx.x; w < w1; w += blockDim.x) {
@@ -406,6 +459,10 @@ __global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int w0, 
     cnt = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0;
     for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, o);
     if (threadIdx.x == 0) *n_active = cnt;
+  }
+  if (W_lists > 0) {
+    __syncthreads();  // done[] of this CTA's writes is visible to the CTA
+    build_lists(W_lists, done, cols, grp4, n_lists);
   }
 }
 
@@ -469,13 +526,18 @@ __global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restr
                                                            int W, uint32_t* __restrict__ msgs,
                                                            const uint32_t* __restrict__ cha, uint8_t* __restrict__ hard,
                                                            const uint32_t* __restrict__ done,
-                                                           uint32_t* __restrict__ vn_fail, int want_flags, int q_out) {
+                                                           uint32_t* __restrict__ vn_fail, int want_flags, int q_out,
+                                                           const uint32_t* __restrict__ cols,
+                                                           const uint32_t* __restrict__ n_lists) {
   constexpr int NT = fastvn::Static<DV>::P.n_tables;
   __shared__ __align__(128) uint8_t tabs[NT * 128];
   __shared__ uint64_t bar;
+  const int n_cols = (int)n_lists[2];
+  if ((int)(blockIdx.y * kNodeThreads) >= n_cols) return;  // whole CTA beyond the live columns
   stage_to_smem(tabs, tables_g, NT * 128, &bar);
-  const int w = blockIdx.y * kNodeThreads + threadIdx.x;
-  if (w >= W) return;
+  const int i = blockIdx.y * kNodeThreads + threadIdx.x;
+  if (i >= n_cols) return;
+  const int w = (int)cols[i];
   const uint32_t dn = done[w];
   if (dn == kNibOnes) return;
   uint32_t failacc = 0;
@@ -484,7 +546,6 @@ __global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restr
                    nib_bits_to_byte(dn, 0), want_flags, q_out, failacc);
   if (want_flags) flag_or(&vn_fail[w], failacc & kNibOnes);
 }
-
 
 static const fastvn::Prog* fast_prog(int dv) {
   switch (dv) {
@@ -503,14 +564,19 @@ __global__ void __launch_bounds__(kNodeThreads) k_vn_fused(FusedVnParams P, cons
                                                             const int32_t* __restrict__ vn_edge0, int W,
                                                             uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
                                                             uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
-                                                            uint32_t* __restrict__ vn_fail, int want_flags) {
+                                                            uint32_t* __restrict__ vn_fail, int want_flags,
+                                                            const uint32_t* __restrict__ cols,
+                                                            const uint32_t* __restrict__ n_lists) {
   __shared__ __align__(128) uint8_t tabs[(MAXDV - 1) * 128];
   __shared__ uint64_t bar;
+  const int n_cols = (int)n_lists[2];
+  if ((int)(blockIdx.y * kNodeThreads) >= n_cols) return;  // whole CTA beyond the live columns
   const int4 tile = tiles[blockIdx.x];  // x = class, y = first node, z = node count
   const FusedVnClass cls = P.c[tile.x];
   stage_to_smem(tabs, cls.tables, (uint32_t)(cls.dv - 1) * 128u, &bar);
-  const int w = blockIdx.y * kNodeThreads + threadIdx.x;
-  if (w >= W) return;
+  const int i = blockIdx.y * kNodeThreads + threadIdx.x;
+  if (i >= n_cols) return;
+  const int w = (int)cols[i];
   const uint32_t dn = done[w];
   if (dn == kNibOnes) return;
   const uint32_t done_byte = nib_bits_to_byte(dn, 0);
@@ -581,6 +647,7 @@ cudaError_t launch_pack_bits(const uint8_t* d_bits, const GraphArrays& g, const 
 cudaError_t launch_reset_flags(const BatchBuffers& b, cudaStream_t st) {
   k_reset_flags<<<cdiv(b.W, 128), 128, 0, st>>>(b.done, b.vn_fail, b.cn_fail, b.syn_fail, b.iters, b.n_active, b.W,
                                                  b.F);
+  k_build_lists<<<1, 1024, 0, st>>>(b.W, b.done, b.cols, b.grp4, b.n_active);
   return cudaGetLastError();
 }
 
@@ -618,12 +685,14 @@ cudaError_t launch_cn_exact(int dc, const int32_t* d_rows, int n_checks, const B
                             cudaStream_t st) {
   if (n_checks == 0) return cudaSuccess;
   static const int vec = env_int("LUTLDPC_CN_VEC", 2) == 4 ? 4 : 2;
-  dim3 grid(n_checks, cdiv(b.W, 128 * vec));
+  if (b.host_grp4 <= 0) return cudaSuccess;
+  dim3 grid(n_checks, cdiv(b.host_grp4 * (4 / vec), 128));
+#define CN_X_ARGS d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail, b.grp4, b.n_active
   switch (dc) {
-#define X(D)                                                                                                  \
-  case D:                                                                                                     \
-    if (vec == 2) k_cn_exact<D, 2><<<grid, 128, 0, st>>>(d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail); \
-    else k_cn_exact<D, 4><<<grid, 128, 0, st>>>(d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail);          \
+#define X(D)                                                              \
+  case D:                                                                 \
+    if (vec == 2) k_cn_exact<D, 2><<<grid, 128, 0, st>>>(CN_X_ARGS);      \
+    else k_cn_exact<D, 4><<<grid, 128, 0, st>>>(CN_X_ARGS);               \
     break;
     LUTLDPC_EXACT_DCS(X)
 #undef X
@@ -657,7 +726,8 @@ cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& 
 cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const NodeLaunch& nl, const GraphArrays& g,
                            const BatchBuffers& b, int want_flags, cudaStream_t st) {
   if (nl.n_nodes == 0) return cudaSuccess;
-  int ycols = cdiv(b.W, kNodeThreads);
+  if (b.host_cols <= 0) return cudaSuccess;
+  int ycols = cdiv(b.host_cols, kNodeThreads);
   int per = (int)(((long long)nl.n_nodes * ycols) / (148 * 24));
   per = per < 1 ? 1 : (per > 32 ? 32 : per);
   dim3 grid(cdiv(nl.n_nodes, per), ycols);
@@ -665,7 +735,8 @@ cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const Nod
 #define X(D)                                                                                                       \
   case D:                                                                                                          \
     k_vn_fast<D><<<grid, kNodeThreads, 0, st>>>(d_tables, nl.node_list, nl.n_nodes, per, g.vn_edge0, b.W, b.msgs, \
-                                                b.cha, b.hard, b.done, b.vn_fail, want_flags, q_out);              \
+                                                b.cha, b.hard, b.done, b.vn_fail, want_flags, q_out, b.cols,      \
+                                                b.n_active);                                                       \
     break;
     LUTLDPC_FAST_DVS(X)
 #undef X
@@ -677,9 +748,9 @@ cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const Nod
 
 cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_tiles, int n_tiles, const GraphArrays& g,
                             const BatchBuffers& b, int want_flags, cudaStream_t st) {
-  if (n_tiles == 0) return cudaSuccess;
-  dim3 grid(n_tiles, cdiv(b.W, kNodeThreads));
-#define FUSED_ARGS P, d_tiles, g.vn_edge0, b.W, b.msgs, b.cha, b.hard, b.done, b.vn_fail, want_flags
+  if (n_tiles == 0 || b.host_cols <= 0) return cudaSuccess;
+  dim3 grid(n_tiles, cdiv(b.host_cols, kNodeThreads));
+#define FUSED_ARGS P, d_tiles, g.vn_edge0, b.W, b.msgs, b.cha, b.hard, b.done, b.vn_fail, want_flags, b.cols, b.n_active
   if (max_dv <= 4) k_vn_fused<4><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
   else if (max_dv <= 8) k_vn_fused<8><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
   else if (max_dv <= 12) k_vn_fused<12><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
@@ -701,8 +772,9 @@ cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b,
 
 cudaError_t launch_finalize_range(FinalizeMode mode, int value, const BatchBuffers& b, int w0, int w1,
                                   uint32_t* n_active, cudaStream_t st) {
+  const int full = w0 == 0 && w1 == b.W;
   k_finalize<<<1, 1024, 0, st>>>((int)mode, value, w0, w1, b.done, b.vn_fail, b.cn_fail, b.syn_fail, b.iters,
-                                 n_active);
+                                 n_active, full ? b.W : 0, b.cols, b.grp4, b.n_active);
   return cudaGetLastError();
 }
 

@@ -23,7 +23,14 @@ struct BatchBuffers {
   uint32_t* cn_fail = nullptr;
   uint32_t* syn_fail = nullptr;
   int32_t* iters = nullptr;
-  uint32_t* n_active = nullptr;  // device counter written by finalize
+  uint32_t* n_active = nullptr;  // device counters written by finalize: [0] unfinished frames, [1] scratch of the
+                                 // staggered schedule, [2] entries of cols, [3] entries of grp4
+  // Work lists rebuilt by every finalize: word columns that still hold an unfinished frame, and groups of 4
+  // adjacent columns (vector accesses) with any such word.  The hot kernels map thread i to cols[i] / grp4[i],
+  // so the issue slots follow the number of live words instead of the number of live warps.
+  uint32_t* cols = nullptr;      // [W]
+  uint32_t* grp4 = nullptr;      // [W/4]
+  int host_cols = 0, host_grp4 = 0;  // host-side upper bounds of the list lengths (grid sizing)
   int W = 0;                     // words per row
   int F = 0;                     // real frames (<= 8W)
 };
