@@ -25,7 +25,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 WORKLOADS = {
     # name -> (golden cfg, default snr dB, default frames per step per GPU, description)
-    "c5_n64800": ("c5_n64800", 1.3, 8192,
+    "c5_n64800": ("c5_n64800", 1.3, 16384,
                   "rate0.50_dv02-08_dc07-08_lut_q4_N64800, LUT q=4/4, max_iter 50, psc=pisc=1"),
     "c3_irr_n10000": ("c3_irr_n10000", 1.3, 32768, "rate0.50_dv02-17_dc08-09_lut_q4_N10000, LUT q=4/4, max_iter 50"),
     "c1b_reg36_n1000": ("c1b_reg36_n1000", 2.0, 65536, "rate0.50_dv03_dc06_N1000 (3,6), LUT q=4/4, max_iter 50"),

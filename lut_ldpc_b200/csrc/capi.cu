@@ -225,8 +225,10 @@ static int host_chunk_frames(lutldpc_decoder* h, int n_frames) {
     int v = atoi(e);
     if (v > 0) return std::min(maxb, std::max(256, (v + 255) / 256 * 256));
   }
-  // >= 4 chunks once the call is large enough for the copies to matter, never below 2048 frames per chunk
-  int c = ((n_frames + 3) / 4 + 1023) / 1024 * 1024;
+  // ~256 MB of labels per chunk: large enough for the kernels to run at batch efficiency (N=64800: 4096 frames),
+  // small enough that the first copy in and the last copy out -- the only ones not hidden -- stay short
+  int c = (int)std::min<long long>(maxb, ((1LL << 28) / std::max(1, h->m.nvar) + 512) / 1024 * 1024);
+  (void)n_frames;
   return std::min(maxb, std::max(2048, c));
 }
 
