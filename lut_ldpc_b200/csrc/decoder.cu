@@ -161,7 +161,7 @@ int lutldpc_decoder::init_device() {
       fused_classes.push_back(c);
       fused_max_dv = std::max(fused_max_dv, vn_classes[c].degree);
       int ops = (int)var_progs[c].n_ops;
-      int per = std::max(1, 64 / std::max(1, ops));
+      int per = std::max(1, env_int("LUTLDPC_VN_TILE_OPS", 128) / std::max(1, ops));
       int nt = (vn_classes[c].n + per - 1) / per;
       for (int i = 0; i < nt; ++i)
         tiles.push_back({(i + 0.5) / nt, make_int4(j, i * per, std::min(per, vn_classes[c].n - i * per), 0)});
@@ -292,6 +292,9 @@ int lutldpc_decoder::max_batch_frames() const {
   double per_frame = m.num_edges / 2.0 + m.nvar / 2.0 + m.nvar / 8.0 + 8;
   long f = (long)(16.0 * 1024 * 1024 * 1024 / per_frame);
   f = std::min(f, 65536L);
+  // the hot kernels index msgs / cha / hard with 32-bit element offsets: rows * W must stay below 2^32
+  const long rows = std::max<long>(std::max(m.num_edges, m.nvar), 1);
+  f = std::min(f, ((1L << 32) - 1) / rows * 8 - 256);
   f = std::max(256L, f / 256 * 256);
   return (int)f;
 }

@@ -84,16 +84,19 @@ template <> struct WordVec<4> { typedef uint4 T; };
 #define LUTLDPC_EXACT_DCS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
 #define LUTLDPC_FAST_DVS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16) X(17) X(18) X(19) X(20)
 
+// Offsets into msgs / cha / hard are 32-bit element indices: a batch is bounded so that num_edges * W < 2^32
+// (lutldpc_decoder::max_batch_frames), which keeps the address arithmetic of the hot loop to one IMAD +
+// one IMAD.WIDE per access.
 template <int DV, int II>
 struct FastStore {
-  static __device__ __forceinline__ void run(const uint32_t (&v)[DV + 1 + fastvn::Static<DV>::P.n_ops], uint32_t* row0,
-                                             size_t W, uint32_t& A, uint32_t& O) {
+  static __device__ __forceinline__ void run(const uint32_t (&v)[DV + 1 + fastvn::Static<DV>::P.n_ops],
+                                             uint32_t* __restrict__ msgs, uint32_t off0, uint32_t W, uint32_t r0,
+                                             uint32_t& D) {
     if constexpr (II < DV) {
       const uint32_t r = v[fastvn::Static<DV>::P.out[II]];
-      row0[(size_t)II * W] = r;
-      A &= r;
-      O |= r;
-      FastStore<DV, II + 1>::run(v, row0, W, A, O);
+      msgs[off0 + (uint32_t)II * W] = r;
+      if constexpr (II > 0) D |= r ^ r0;  // bits where an outgoing message differs from the first one
+      FastStore<DV, II + 1>::run(v, msgs, off0, W, r0, D);
     }
   }
 };
@@ -107,20 +110,23 @@ __device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int32_t*
                                              uint32_t& failacc) {
   constexpr int NOPS = fastvn::Static<DV>::P.n_ops;
   const int so = q_out - 1, root_shift = 4 - q_out;
+  const uint32_t uW = (uint32_t)W, uw = (uint32_t)w;
   for (int i = i0; i < i1; ++i) {
-    const int node = node_list[i];
-    uint32_t* row0 = msgs + (size_t)vn_edge0[node] * W + w;
+    const uint32_t node = (uint32_t)node_list[i];
+    const uint32_t off0 = (uint32_t)vn_edge0[node] * uW + uw;
+    const uint32_t offn = node * uW + uw;
     uint32_t v[DV + 1 + NOPS];
 #pragma unroll
-    for (int k = 0; k < DV; ++k) v[k] = row0[(size_t)k * W];
-    v[DV] = cha[(size_t)node * W + w];
+    for (int k = 0; k < DV; ++k) v[k] = msgs[off0 + (uint32_t)k * uW];
+    v[DV] = cha[offn];
     fastvn::Exec<DV, 0>::run(v, tabs, root_shift);
-    uint32_t A = 0xFFFFFFFFu, O = 0;
-    FastStore<DV, 0>::run(v, row0, (size_t)W, A, O);
+    const uint32_t r0 = v[fastvn::Static<DV>::P.out[0]];
+    uint32_t D = 0;
+    FastStore<DV, 0>::run(v, msgs, off0, uW, r0, D);
     if (want_flags) {
-      failacc |= (A ^ O) >> so;
-      uint8_t* hp = hard + (size_t)node * W + w;
-      const uint32_t nb = nib_bits_to_byte(v[fastvn::Static<DV>::P.out[0]], so);
+      failacc |= D >> so;  // sign position of the outputs; the caller masks with kNibOnes
+      uint8_t* hp = hard + offn;
+      const uint32_t nb = nib_bits_to_byte(r0, so);
       *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
     }
   }

@@ -520,7 +520,7 @@ __global__ void k_quantize(const double* __restrict__ llr, size_t n, const doubl
 // (128 B each, one per tree node) are staged into shared memory with one bulk copy.
 // ---------------------------------------------------------------------------------------------
 template <int DV>
-__global__ void __launch_bounds__(kNodeThreads) k_vn_fast(const uint8_t* __restrict__ tables_g,
+__global__ void __launch_bounds__(kNodeThreads, (DV <= 8 ? 12 : 1)) k_vn_fast(const uint8_t* __restrict__ tables_g,
                                                            const int32_t* __restrict__ node_list, int n_nodes,
                                                            int nodes_per_cta, const int32_t* __restrict__ vn_edge0,
                                                            int W, uint32_t* __restrict__ msgs,
@@ -560,7 +560,7 @@ static const fastvn::Prog* fast_prog(int dv) {
 // host interleaves the tiles of the classes (FusedVnPlan), so CTAs that are bound by HBM latency
 // (dv 2, 3) and CTAs that are bound by shared-memory look-ups (dv 8 ...) are resident on an SM together.
 template <int MAXDV>
-__global__ void __launch_bounds__(kNodeThreads) k_vn_fused(FusedVnParams P, const int4* __restrict__ tiles,
+__global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 1)) k_vn_fused(FusedVnParams P, const int4* __restrict__ tiles,
                                                             const int32_t* __restrict__ vn_edge0, int W,
                                                             uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
                                                             uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
