@@ -156,7 +156,9 @@ int lutldpc_decoder::init_device() {
       if (!vn_classes[c].n) continue;
       bool all_fast = true;
       for (int t = 0; t + 1 < n_iter_slots; ++t) all_fast &= var_progs[(size_t)t * nvc + c].fast_dv != 0;
-      if (!all_fast || n_iter_slots < 2 || fused_classes.size() >= 8 || vn_classes[c].degree > 20) continue;
+      // only the low degrees share a launch: their code fits 40 registers (12 CTAs per SM); a high-degree class in
+      // the same kernel would drag every class down to its register count, so it keeps its own k_vn_fast<D> launch
+      if (!all_fast || n_iter_slots < 2 || fused_classes.size() >= 8 || vn_classes[c].degree > 8) continue;
       int j = (int)fused_classes.size();
       fused_classes.push_back(c);
       fused_max_dv = std::max(fused_max_dv, vn_classes[c].degree);

@@ -293,9 +293,13 @@ __global__ void __launch_bounds__(kNodeThreads) k_node(const uint8_t* __restrict
                                                         const int32_t* __restrict__ cn_msg_idx, int W,
                                                         uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
                                                         uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
-                                                        uint32_t* __restrict__ fail, int want_flags) {
+                                                        uint32_t* __restrict__ fail, int want_flags,
+                                                        const uint32_t* __restrict__ cols,
+                                                        const uint32_t* __restrict__ n_lists) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bar;
+  const int n_cols = (int)n_lists[2];
+  if ((int)(blockIdx.y * kNodeThreads) >= n_cols) return;  // whole CTA beyond the live columns
   stage_to_smem(smem, prog, prog_bytes, &bar);
   const DevProgHeader* hdr = reinterpret_cast<const DevProgHeader*>(smem);
   const DevOp* ops = reinterpret_cast<const DevOp*>(smem + hdr->ops_off);
@@ -305,8 +309,9 @@ __global__ void __launch_bounds__(kNodeThreads) k_node(const uint8_t* __restrict
   const int n_in = (int)hdr->n_in, n_out = (int)hdr->n_out;
   SmemVals vals{reinterpret_cast<uint32_t*>(smem + prog_bytes) + threadIdx.x};
 
-  const int w = blockIdx.y * kNodeThreads + threadIdx.x;
-  if (w >= W) return;
+  const int ci = blockIdx.y * kNodeThreads + threadIdx.x;
+  if (ci >= n_cols) return;
+  const int w = (int)cols[ci];
   const uint32_t dn = done[w];
   if (dn == kNibOnes) return;
   const uint32_t done_byte = nib_bits_to_byte(dn, 0);
@@ -361,10 +366,12 @@ __global__ void __launch_bounds__(kNodeThreads) k_node(const uint8_t* __restrict
 __global__ void __launch_bounds__(128) k_syndrome(const int32_t* __restrict__ cn_start,
                                                   const int32_t* __restrict__ chk_equ_idx, int W,
                                                   const uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
-                                                  uint32_t* __restrict__ syn_fail) {
+                                                  uint32_t* __restrict__ syn_fail, const uint32_t* __restrict__ cols,
+                                                  const uint32_t* __restrict__ n_lists) {
   const int c = blockIdx.x;
-  const int w = blockIdx.y * blockDim.x + threadIdx.x;
-  if (w >= W) return;
+  const int ci = blockIdx.y * blockDim.x + threadIdx.x;
+  if (ci >= (int)n_lists[2]) return;
+  const int w = (int)cols[ci];
   if (done[w] == kNibOnes) return;
   const int s = cn_start[c], e = cn_start[c + 1];
   uint32_t x = 0;
@@ -520,7 +527,7 @@ __global__ void k_quantize(const double* __restrict__ llr, size_t n, const doubl
 // (128 B each, one per tree node) are staged into shared memory with one bulk copy.
 // ---------------------------------------------------------------------------------------------
 template <int DV>
-__global__ void __launch_bounds__(kNodeThreads, (DV <= 8 ? 12 : 1)) k_vn_fast(const uint8_t* __restrict__ tables_g,
+__global__ void __launch_bounds__(kNodeThreads, (DV <= 8 ? 12 : 0)) k_vn_fast(const uint8_t* __restrict__ tables_g,
                                                            const int32_t* __restrict__ node_list, int n_nodes,
                                                            int nodes_per_cta, const int32_t* __restrict__ vn_edge0,
                                                            int W, uint32_t* __restrict__ msgs,
@@ -560,7 +567,7 @@ static const fastvn::Prog* fast_prog(int dv) {
 // host interleaves the tiles of the classes (FusedVnPlan), so CTAs that are bound by HBM latency
 // (dv 2, 3) and CTAs that are bound by shared-memory look-ups (dv 8 ...) are resident on an SM together.
 template <int MAXDV>
-__global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 1)) k_vn_fused(FusedVnParams P, const int4* __restrict__ tiles,
+__global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fused(FusedVnParams P, const int4* __restrict__ tiles,
                                                             const int32_t* __restrict__ vn_edge0, int W,
                                                             uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
                                                             uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
@@ -707,7 +714,8 @@ cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& 
   if (nl.n_nodes == 0) return cudaSuccess;
   size_t smem = (size_t)nl.prog_bytes + (size_t)nl.n_slots * kNodeThreads * sizeof(uint32_t);
   if (smem > (size_t)kMaxNodeSmem) return cudaErrorInvalidValue;
-  int ycols = cdiv(b.W, kNodeThreads);
+  if (b.host_cols <= 0) return cudaSuccess;
+  int ycols = cdiv(b.host_cols, kNodeThreads);
   // enough CTAs to fill 148 SMs several times over, few enough that the program staging amortises
   int per = (int)(((long long)nl.n_nodes * ycols) / (148 * 24));
   per = per < 1 ? 1 : (per > 32 ? 32 : per);
@@ -715,7 +723,7 @@ cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& 
   uint32_t* fail = mode == NODE_CHK ? b.cn_fail : b.vn_fail;
   const int32_t* start = mode == NODE_CHK ? g.cn_start : g.vn_edge0;
 #define NODE_ARGS nl.prog, nl.prog_bytes, nl.node_list, nl.n_nodes, per, start, g.cn_msg_idx, b.W, b.msgs, b.cha, \
-                  b.hard, b.done, fail, want_flags
+                  b.hard, b.done, fail, want_flags, b.cols, b.n_active
   if (mode == NODE_VAR) k_node<NODE_VAR><<<grid, kNodeThreads, smem, st>>>(NODE_ARGS);
   else if (mode == NODE_DEC) k_node<NODE_DEC><<<grid, kNodeThreads, smem, st>>>(NODE_ARGS);
   else k_node<NODE_CHK><<<grid, kNodeThreads, smem, st>>>(NODE_ARGS);
@@ -761,8 +769,9 @@ cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_ti
 }
 
 cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st) {
-  dim3 grid(g.nchk, cdiv(b.W, 128));
-  k_syndrome<<<grid, 128, 0, st>>>(g.cn_start, g.chk_equ_idx, b.W, b.hard, b.done, b.syn_fail);
+  if (b.host_cols <= 0) return cudaSuccess;
+  dim3 grid(g.nchk, cdiv(b.host_cols, 128));
+  k_syndrome<<<grid, 128, 0, st>>>(g.cn_start, g.chk_equ_idx, b.W, b.hard, b.done, b.syn_fail, b.cols, b.n_active);
   return cudaGetLastError();
 }
 
