@@ -208,3 +208,30 @@ def test_staggered_equals_sequential_schedule(L, cfg):
         sel = np.r_[0:40, n - 40:n]
         want_out, want_it = orc.lut_decode_batch(cha[sel], msg[sel])
         assert np.array_equal(want_it, it[sel]) and np.array_equal(want_out, out[sel])
+
+
+def test_host_path_is_chunked_and_pipelined_bit_exact(L, monkeypatch):
+    """lutldpc_decode_quantized / _llr cut a call into chunks that overlap their copies with the decoder
+    (double-buffered staging, three streams).  Forced to 256-frame chunks: 5 chunks incl. a ragged last one,
+    pageable host memory, results identical to the oracle frame by frame and to the one-chunk call."""
+    cfg = "c2_irr_n500"
+    orc = pyoracle.Oracle(_golden.bundle_path(cfg))
+    dec = _dec(L, cfg)
+    dec.set_exit_conditions(dec.max_iters, 1, 1)
+    orc.set_exit_conditions(orc.max_iters, 1, 1)
+    n = 1100
+    rng = np.random.default_rng(21)
+    sigma = np.sqrt(0.5 / (dec.rate * 10 ** (1.5 / 10)))
+    llr = (2.0 / sigma ** 2) * (1.0 + sigma * rng.standard_normal((n, dec.nvar)))
+    cha, msg = dec.quantize(llr)
+    whole_out, whole_it = dec.decode_quantized(cha, msg)
+    monkeypatch.setenv("LUTLDPC_HOST_CHUNK", "256")
+    for _ in range(2):  # second call reuses the staging buffers and events
+        out, it = dec.decode_quantized(cha, msg)
+        assert np.array_equal(it, whole_it) and np.array_equal(out, whole_out)
+    out2, it2 = dec.decode_llr(llr)
+    assert np.array_equal(it2, whole_it) and np.array_equal(out2, whole_out)
+    monkeypatch.delenv("LUTLDPC_HOST_CHUNK")
+    want_out, want_it = orc.lut_decode_batch(cha, msg)
+    assert np.array_equal(want_it, whole_it) and np.array_equal(want_out, whole_out)
+    assert len(np.unique(whole_it)) > 3
