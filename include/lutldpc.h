@@ -80,8 +80,11 @@ int lutldpc_set_device(int device);
 /* message of the last failure; handle may be NULL for create errors */
 const char* lutldpc_last_error(const lutldpc_decoder* h);
 
-/* ---- construction: LDPC_Code_LUT ctor + set_code + set_trees (src/LDPC_Code_LUT.cpp:51-169,488-541),
- *      from-file ctor / load_code (:568-641) for the bundle form of the codec */
+/* ---- construction: LDPC_Code_LUT ctor + set_code + set_trees (src/LDPC_Code_LUT.cpp:51-169,488-541) from a
+ *      lutldpc_desc, or the from-file ctor / load_code (:60-66,568-641) from a file.  The file is either the
+ *      reference's own codec file (the IT++ it_file that LDPC_Code_LUT::save_code writes, :643-697, e.g. the
+ *      lut_codec.it that ber_sim leaves in its results directory and Sim.codec_filename names) or the flat
+ *      "bundle" dump of oracle/ref_driver.cpp; the two are told apart by their magic bytes. */
 int lutldpc_create(const lutldpc_desc* desc, lutldpc_decoder** out);
 int lutldpc_create_from_bundle(const char* bundle_path, lutldpc_decoder** out);
 void lutldpc_destroy(lutldpc_decoder* h);

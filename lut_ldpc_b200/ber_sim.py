@@ -11,8 +11,8 @@ point sharded over the ranks of a torch.distributed job (one process per GPU):
     Every rank sees the same sums, so every rank takes the same decision without further messages.
 
 Params come from the reference's own .ini (sections [Sim], [LDPC], [LUT]; keys and defaults as
-src/LDPC_BER_Sim.cpp:53-78,386-413).  LUT design is not part of this path: Sim.codec_filename names the
-bundle of a designed decoder.
+src/LDPC_BER_Sim.cpp:53-78,386-413).  LUT design is not part of this path: Sim.codec_filename names a
+designed decoder, i.e. the lut_codec.it a reference run saved (LDPC_Code_LUT::save_code) or a bundle.
 """
 import configparser
 import math
@@ -96,7 +96,7 @@ class LDPC_BER_Sim_LUT:
         """LDPC_BER_Sim_LUT::load (src/LDPC_BER_Sim.cpp:434-550) minus the design step."""
         from .capi import Decoder, INIT_CONT, INIT_QCHA
         if not self.p.codec_filename:
-            raise RuntimeError("LDPC_BER_Sim_LUT::load(): Sim.codec_filename (bundle of a designed decoder) is required")
+            raise RuntimeError("LDPC_BER_Sim_LUT::load(): Sim.codec_filename (lut_codec.it or bundle of a designed decoder) is required")
         path = self.p.codec_filename if os.path.isabs(self.p.codec_filename) else os.path.join(basedir, self.p.codec_filename)
         self.dec = Decoder(path)
         self.dec.set_exit_conditions(self.p.max_iter, self.p.parity_check_iter, self.p.parity_check_iter)  # :500

@@ -123,6 +123,7 @@ class Decoder:
     """One lutldpc_decoder handle (an LDPC_Code_LUT bound to the current CUDA device)."""
 
     def __init__(self, bundle_path):
+        """bundle_path: the reference's codec file (lut_codec.it, IT++ it_file) or a decoder bundle."""
         self._L = load_library()
         h = C.c_void_p()
         rc = self._L.lutldpc_create_from_bundle(os.fsencode(bundle_path), C.byref(h))

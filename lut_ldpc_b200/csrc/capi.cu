@@ -50,7 +50,7 @@ int lutldpc_create_from_bundle(const char* bundle_path, lutldpc_decoder** out) {
   lutldpc_decoder* h = new (std::nothrow) lutldpc_decoder();
   if (!h) { g_create_error = "out of memory"; return LUTLDPC_ERR_ARG; }
   std::string err;
-  if (!load_bundle_file(bundle_path, h->m, err)) {
+  if (!load_decoder_file(bundle_path, h->m, err)) {
     g_create_error = err;
     delete h;
     return LUTLDPC_ERR_MODEL;

@@ -132,6 +132,158 @@ bool load_bundle_file(const char* path, DecoderModel& m, std::string& err) {
   return finalize_model(m, err);
 }
 
+// ---------------------------------------------------------------------------------------------
+// The reference's own codec file: IT++ it_file (format version 3) holding the variables that
+// LDPC_Code_LUT::save_code writes (src/LDPC_Code_LUT.cpp:643-697) and load_code reads (:568-641).
+// Layout (itpp/itpp/base/itfile.h:98-125, itfile.cpp): "IT++" 0x03, then blocks of
+//   u64 hdr_bytes, u64 data_bytes, u64 block_bytes, name\0 type\0 desc\0, data
+// little endian; int32 = 4 bytes, bool = 1 byte, ivec/dvec/bvec/string = u64 count + elements
+// (int32 / f64 / 1 byte / char).  chk_equ_idx (ivecArray) is not needed: it is re-derived from
+// cn_msg_idx like in decoder_parameterization (:515-535).
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct ItVar {
+  std::string type;
+  const uint8_t* p = nullptr;
+  uint64_t n = 0;
+};
+struct ItFile {
+  std::vector<uint8_t> buf;
+  std::vector<std::pair<std::string, ItVar>> vars;  // file order; names may repeat (the generator appends its own)
+  const ItVar* find(const char* name, const char* type) const {
+    for (auto& kv : vars)
+      if (kv.first == name && kv.second.type == type) return &kv.second;
+    return nullptr;
+  }
+  bool i32(const char* name, int32_t& v) const {
+    const ItVar* x = find(name, "int32");
+    if (!x || x->n != 4) return false;
+    memcpy(&v, x->p, 4);
+    return true;
+  }
+  bool flag(const char* name, bool& v) const {
+    const ItVar* x = find(name, "bool");
+    if (!x || x->n != 1) return false;
+    v = x->p[0] != 0;
+    return true;
+  }
+  template <class T>
+  bool arr(const char* name, const char* type, size_t elem, std::vector<T>& out) const {
+    const ItVar* x = find(name, type);
+    uint64_t cnt = 0;
+    if (!x || x->n < 8) return false;
+    memcpy(&cnt, x->p, 8);
+    if (cnt > (1ull << 31) || x->n != 8 + cnt * elem) return false;
+    out.resize((size_t)cnt);
+    for (size_t i = 0; i < (size_t)cnt; ++i) {
+      if (elem == 4) { int32_t v; memcpy(&v, x->p + 8 + 4 * i, 4); out[i] = (T)v; }
+      else if (elem == 8) { double v; memcpy(&v, x->p + 8 + 8 * i, 8); out[i] = (T)v; }
+      else out[i] = (T)x->p[8 + i];
+    }
+    return true;
+  }
+};
+
+bool read_it_file(const char* path, ItFile& f, std::string& err) {
+  FILE* fp = fopen(path, "rb");
+  if (!fp) { err = std::string("cannot open codec file ") + path; return false; }
+  fseek(fp, 0, SEEK_END);
+  long sz = ftell(fp);
+  fseek(fp, 0, SEEK_SET);
+  if (sz < 5) { fclose(fp); err = "codec file: too short"; return false; }
+  f.buf.resize((size_t)sz);
+  size_t got = fread(f.buf.data(), 1, (size_t)sz, fp);
+  fclose(fp);
+  if (got != (size_t)sz) { err = "codec file: read error"; return false; }
+  if (memcmp(f.buf.data(), "IT++", 4) != 0 || f.buf[4] != 3) { err = "codec file: not an IT++ file of format version 3"; return false; }
+  size_t off = 5;
+  while (off + 24 <= f.buf.size()) {
+    uint64_t h[3];
+    memcpy(h, f.buf.data() + off, 24);
+    if (h[2] < 24 || h[0] < 27 || h[0] + h[1] > h[2] || off + h[2] > f.buf.size()) { err = "codec file: corrupt block header"; return false; }
+    const char* s = reinterpret_cast<const char*>(f.buf.data() + off + 24);
+    const char* end = reinterpret_cast<const char*>(f.buf.data() + off + h[0]);
+    std::string str[3];
+    for (int k = 0; k < 3; ++k) {
+      const void* z = memchr(s, 0, (size_t)(end - s));
+      if (!z) { err = "codec file: corrupt block strings"; return false; }
+      str[k].assign(s, (const char*)z);
+      s = (const char*)z + 1;
+    }
+    ItVar v;
+    v.type = str[1];
+    v.p = f.buf.data() + off + h[0];
+    v.n = h[1];
+    if (!v.type.empty()) f.vars.push_back({str[0], v});  // type "" marks a deleted variable
+    off += (size_t)h[2];
+  }
+  return true;
+}
+}  // namespace
+
+bool load_it_codec_file(const char* path, DecoderModel& m, std::string& err) {
+  ItFile f;
+  if (!read_it_file(path, f, err)) return false;
+  int32_t ver = 0, nvar = 0, nchk = 0, nli = 0, max_iters = 0, nq_cha = 0;
+  bool h_def = false, luts_def = false, min_lut = false;
+  if (!f.i32("Fileversion", ver) || ver != 1) { err = "codec file: unsupported Fileversion (src/LDPC_Code_LUT.cpp:35)"; return false; }
+  if (!f.flag("H_defined", h_def) || !f.flag("LUTs_defined", luts_def) || !h_def || !luts_def) {
+    err = "codec file: no parity-check matrix or no LUTs stored";
+    return false;
+  }
+  m = DecoderModel();
+  std::vector<uint8_t> reuse;
+  std::vector<char> vt, ct;
+  bool ok = f.i32("nvar", nvar) && f.i32("nchk", nchk) && f.i32("nchk_lin_indep", nli) && f.i32("max_iters", max_iters) &&
+            f.i32("Nq_Cha", nq_cha) && f.flag("minLUT", min_lut) && f.arr("dv_vec", "ivec", 4, m.dv) &&
+            f.arr("dc_vec", "ivec", 4, m.dc) && f.arr("cn_msg_idx", "ivec", 4, m.cn_msg_idx) &&
+            f.arr("Nq_Msg", "ivec", 4, m.Nq_Msg) && f.arr("qb_Cha", "dvec", 8, m.qb_Cha) && f.arr("reuse_vec", "bvec", 1, reuse) &&
+            f.arr("var_tree_string", "string", 1, vt);
+  if (!ok) { err = "codec file: a variable of LDPC_Code_LUT::save_code is missing or has the wrong type"; return false; }
+  f.arr("qb_Msg", "dvec", 8, m.qb_Msg);
+  f.arr("Nq_Cha_2_Nq_Msg_map", "ivec", 4, m.cha2msg);
+  f.arr("chk_tree_string", "string", 1, ct);
+  m.nvar = nvar; m.nchk = nchk; m.nchk_lin_indep = nli; m.max_iters = max_iters; m.Nq_Cha = nq_cha; m.minLUT = min_lut;
+  m.num_edges = (int)m.cn_msg_idx.size();
+  m.reuse.assign(reuse.begin(), reuse.end());
+  if (m.nvar <= 0 || m.nchk <= 0 || m.num_edges <= 0 || m.max_iters <= 0 || m.nvar > (1 << 26) || m.num_edges > (1 << 28)) {
+    err = "codec file: header out of range";
+    return false;
+  }
+  std::string perr;
+  if (!parse_tree_array(vt.data(), vt.size(), m.var_trees, perr)) { err = "codec file: var trees: " + perr; return false; }
+  if (!ct.empty()) {
+    TreeArray ta;
+    if (parse_tree_array(ct.data(), ct.size(), ta, perr)) m.chk_trees = std::move(ta);
+    else if (!m.minLUT) { err = "codec file: chk trees: " + perr; return false; }
+  }
+  // generator appended by LDPC_Generator_Systematic::save (itpp/itpp/comm/ldpc.cpp:1002-1009): GF2mat "G" =
+  // u64 nrows, ncols, nwords + rows of bytes, bit k of byte j = column 8j+k (itpp/itpp/base/gf2mat.cpp:1066-1082)
+  if (const ItVar* g = f.find("G", "GF2mat")) {
+    uint64_t d[3] = {0, 0, 0};
+    if (g->n >= 24) memcpy(d, g->p, 24);
+    if (g->n >= 24 && d[0] > 0 && d[1] > 0 && d[2] == (d[1] + 7) / 8 && g->n == 24 + d[0] * d[2] && d[0] * d[1] < (1ull << 33)) {
+      m.gen_rows = (int)d[0]; m.gen_cols = (int)d[1];
+      m.gen.assign((size_t)d[0] * d[1], 0);
+      for (uint64_t r = 0; r < d[0]; ++r)
+        for (uint64_t c = 0; c < d[1]; ++c)
+          m.gen[(size_t)(r * d[1] + c)] = (g->p[24 + r * d[2] + (c >> 3)] >> (c & 7)) & 1;
+    }
+  }
+  return finalize_model(m, err);
+}
+
+// bundle ("LUTLDPC1", oracle/ref_driver.cpp) or the reference's codec file ("IT++"), by magic
+bool load_decoder_file(const char* path, DecoderModel& m, std::string& err) {
+  FILE* fp = fopen(path, "rb");
+  if (!fp) { err = std::string("cannot open ") + path; return false; }
+  char magic[4] = {0, 0, 0, 0};
+  size_t got = fread(magic, 1, 4, fp);
+  fclose(fp);
+  if (got == 4 && memcmp(magic, "IT++", 4) == 0) return load_it_codec_file(path, m, err);
+  return load_bundle_file(path, m, err);
+}
+
 bool finalize_model(DecoderModel& m, std::string& err) {
   char buf[256];
   if ((int)m.dv.size() != m.nvar || (int)m.dc.size() != m.nchk || (int)m.cn_msg_idx.size() != m.num_edges ||

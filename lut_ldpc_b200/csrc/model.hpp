@@ -51,6 +51,10 @@ struct DecoderModel {
 
 bool parse_tree_array(const char* txt, size_t len, TreeArray& out, std::string& err);
 bool load_bundle_file(const char* path, DecoderModel& m, std::string& err);
+// the reference's codec file written by LDPC_Code_LUT::save_code (IT++ it_file, src/LDPC_Code_LUT.cpp:643-697)
+bool load_it_codec_file(const char* path, DecoderModel& m, std::string& err);
+// either of the two, told apart by the file magic
+bool load_decoder_file(const char* path, DecoderModel& m, std::string& err);
 // fills the derived members and validates; false + err on unsupported/inconsistent input
 bool finalize_model(DecoderModel& m, std::string& err);
 

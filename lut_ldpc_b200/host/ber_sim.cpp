@@ -5,8 +5,9 @@
 //   ber_sim -p params.ini [-b basedir] [-s seed] [-c custom-name] [--gpus G] [--batch F]
 //
 // Differences, all at the edges of the hot path:
-//  * the decoder is not designed here: Sim.codec_filename must name a decoder bundle (the dump of a
-//    designed reference LDPC_Code_LUT); LUT.* design keys are read only to cross-check max_iter;
+//  * the decoder is not designed here: Sim.codec_filename must name a designed decoder -- the lut_codec.it
+//    a reference run saved (LDPC_Code_LUT::save_code; looked up under Sim.codes_dir like the reference does,
+//    src/LDPC_BER_Sim.cpp:63,84-86,524) or a decoder bundle; LUT.* design keys only cross-check max_iter;
 //  * results are written as JSON with the reference's variable names (sim_SNRdB, sim_Nframes, ...,
 //    src/LDPC_BER_Sim.cpp:347-358) instead of an IT++ .it file;
 //  * with --gpus G the frames of every SNR point are split over G devices (one host thread per GPU,
@@ -140,8 +141,14 @@ int main(int argc, char** argv) {
     const bool pci = ini.flag("LDPC.parity_check_iter", true);
     const std::string codec = ini.get("Sim.codec_filename", "");
     if (codec.empty())
-      throw std::runtime_error("LDPC_BER_Sim_LUT::load(): Sim.codec_filename (decoder bundle of a designed LDPC_Code_LUT) is "
-                               "required: LUT design is not part of the GPU path");
+      throw std::runtime_error("LDPC_BER_Sim_LUT::load(): Sim.codec_filename (lut_codec.it or decoder bundle of a designed "
+                               "LDPC_Code_LUT) is required: LUT design is not part of the GPU path");
+    // codes_path / codec_filename (src/LDPC_BER_Sim.cpp:524), else relative to the base directory
+    std::string codec_file = path(ini.get("Sim.codes_dir", "codes") + "/" + codec);
+    {
+      struct stat sb;
+      if (codec[0] == '/' || stat(codec_file.c_str(), &sb) != 0) codec_file = path(codec);
+    }
     const std::string imode = ini.get("LUT.initial_message_mode", "from_continuous_input");
 
     const int ndev = lutldpc_device_count();
@@ -150,7 +157,7 @@ int main(int argc, char** argv) {
     std::vector<std::unique_ptr<LDPC_Code_LUT>> C(gpus);
     for (int g = 0; g < gpus; ++g) {
       if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
-      C[g].reset(new LDPC_Code_LUT(path(codec)));
+      C[g].reset(new LDPC_Code_LUT(codec_file));
       const int mi = ini.has("LUT.max_iter") ? (int)ini.num("LUT.max_iter", 30) : C[g]->get_nrof_iterations();
       C[g]->set_exit_conditions(mi, pci, pci);  // psc = pisc = parity_check_iter, src/LDPC_BER_Sim.cpp:500
       C[g]->set_initial_message_mode(imode == "from_quantized_channel_llrs" ? LDPC_Code_LUT::QCHA : LDPC_Code_LUT::CONT);

@@ -38,9 +38,9 @@ class LDPC_Code_LUT : public Channel_Code {
   enum initial_message_mode_t { CONT = LUTLDPC_INIT_CONT, QCHA = LUTLDPC_INIT_QCHA };  // src/LDPC_Code_LUT.hpp:76-79
 
   // LDPC_Code_LUT(const std::string& filename, LDPC_Generator*) (src/LDPC_Code_LUT.cpp:60-66): a stored
-  // codec.  Here the file is the flat bundle of a designed reference decoder (oracle/ref_driver.cpp).
-  explicit LDPC_Code_LUT(const std::string& bundle_filename) : h_(nullptr) {
-    int rc = lutldpc_create_from_bundle(bundle_filename.c_str(), &h_);
+  // codec -- the reference's own lut_codec.it (save_code, :643-697) or the flat bundle of oracle/ref_driver.cpp.
+  explicit LDPC_Code_LUT(const std::string& codec_filename) : h_(nullptr) {
+    int rc = lutldpc_create_from_bundle(codec_filename.c_str(), &h_);
     if (rc != LUTLDPC_OK) throw std::runtime_error(std::string("LDPC_Code_LUT::load_code(): ") + lutldpc_last_error(nullptr));
     fetch_info();
   }

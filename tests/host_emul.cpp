@@ -50,7 +50,7 @@ void* emul_create(const char* bundle, char* err, int errlen) {
     delete e;
     return nullptr;
   };
-  if (!load_bundle_file(bundle, e->m, s)) return failed(s);
+  if (!load_decoder_file(bundle, e->m, s)) return failed(s);
   DecoderModel& m = e->m;
   int nvc = m.var_trees.n_deg, ncc = m.minLUT ? 0 : m.chk_trees.n_deg, ns = m.var_trees.n_iter;
   e->vn_lists.resize(nvc); e->cn_lists.resize(ncc);

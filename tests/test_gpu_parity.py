@@ -235,3 +235,19 @@ def test_host_path_is_chunked_and_pipelined_bit_exact(L, monkeypatch):
     want_out, want_it = orc.lut_decode_batch(cha, msg)
     assert np.array_equal(want_it, whole_it) and np.array_equal(want_out, whole_out)
     assert len(np.unique(whole_it)) > 3
+
+
+@pytest.mark.parametrize("cfg", ["c1b_reg36_n1000", "c3_irr_n10000", "c5_n64800"])
+def test_decoder_from_reference_codec_file(L, cfg):
+    """lutldpc_create_from_bundle on the reference's own lut_codec.it (LDPC_Code_LUT::save_code): same
+    decoder as from the bundle, bit-exact on the reference's fixture frames."""
+    d = L.Decoder(_golden.codec_path(cfg))
+    b = _dec(L, cfg)
+    assert (d.nvar, d.nchk, d.num_edges, d.max_iters, d.lookups_per_frame_iter) == \
+           (b.nvar, b.nchk, b.num_edges, b.max_iters, b.lookups_per_frame_iter)
+    for tag in sorted(_golden.MANIFEST[cfg]["fixtures"]):
+        fx = pyoracle.read_fixture(_golden.fixture_path(cfg, tag))
+        a = _golden.fixture_args(cfg, tag)
+        d.set_exit_conditions(d.max_iters, a["psc"], a["pisc"])
+        out, it = d.decode_quantized(fx["cha"], fx["msg"])
+        assert np.array_equal(it, fx["ret"]) and np.array_equal(out, fx["out"])
