@@ -8,8 +8,9 @@
 //  * the decoder is not designed here: Sim.codec_filename must name a designed decoder -- the lut_codec.it
 //    a reference run saved (LDPC_Code_LUT::save_code; looked up under Sim.codes_dir like the reference does,
 //    src/LDPC_BER_Sim.cpp:63,84-86,524) or a decoder bundle; LUT.* design keys only cross-check max_iter;
-//  * results are written as JSON with the reference's variable names (sim_SNRdB, sim_Nframes, ...,
-//    src/LDPC_BER_Sim.cpp:347-358) instead of an IT++ .it file;
+//  * results are written both as the reference's IT++ results file (<name>_rseedNNNN.it, the variables of
+//    LDPC_BER_Sim_Results::write_itfile, src/LDPC_BER_Sim.cpp:342-361, readable by scripts/analyze_results.m)
+//    and as JSON with the same variable names plus the counters only the GPU path keeps;
 //  * with --gpus G the frames of every SNR point are split over G devices (one host thread per GPU,
 //    disjoint Philox frame ranges) and the counters are summed; stop rules act on the sums.
 #include <chrono>
@@ -28,6 +29,41 @@
 #include <sys/stat.h>
 
 #include "ldpc_code_lut.hpp"
+
+// Minimal IT++ it_file (format version 3) writer: "IT++" 0x03, then per variable u64 hdr_bytes, data_bytes,
+// block_bytes, name\0 type\0 desc\0, data -- little endian (itpp/itpp/base/itfile.h:98-125).  Only the three
+// types LDPC_BER_Sim_Results::write_itfile uses: vec ("dvec": u64 count + f64), double ("float64"), string.
+struct ItWriter {
+  std::ofstream f;
+  explicit ItWriter(const std::string& fn) : f(fn.c_str(), std::ios::binary) {
+    const char h[5] = {'I', 'T', '+', '+', 3};
+    f.write(h, 5);
+  }
+  void block(const std::string& name, const std::string& type, const std::string& data) {
+    const uint64_t hdr = 24 + name.size() + 1 + type.size() + 1 + 1, db = data.size(), blk = hdr + db;
+    f.write(reinterpret_cast<const char*>(&hdr), 8);
+    f.write(reinterpret_cast<const char*>(&db), 8);
+    f.write(reinterpret_cast<const char*>(&blk), 8);
+    f.write(name.c_str(), name.size() + 1);
+    f.write(type.c_str(), type.size() + 1);
+    f.put('\0');  // empty description
+    f.write(data.data(), data.size());
+  }
+  void vec(const std::string& name, const std::vector<double>& v) {
+    std::string d(8 + 8 * v.size(), '\0');
+    const uint64_t n = v.size();
+    memcpy(&d[0], &n, 8);
+    if (n) memcpy(&d[8], v.data(), 8 * v.size());
+    block(name, "dvec", d);
+  }
+  void f64(const std::string& name, double x) { block(name, "float64", std::string(reinterpret_cast<const char*>(&x), 8)); }
+  void str(const std::string& name, const std::string& s) {
+    std::string d(8, '\0');
+    const uint64_t n = s.size();
+    memcpy(&d[0], &n, 8);
+    block(name, "string", d + s);
+  }
+};
 
 using namespace lut_ldpc_b200;
 
@@ -226,7 +262,7 @@ int main(int argc, char** argv) {
     mkdir(path(results_dir).c_str(), 0777);
     mkdir(dir.c_str(), 0777);
     char sfx[32];
-    snprintf(sfx, sizeof sfx, "_rseed%04llu", (unsigned long long)seed);
+    snprintf(sfx, sizeof sfx, "_rseed%04llu", (unsigned long long)(seed + seed_off));  // :327
     std::ofstream js((dir + "/" + name.str() + sfx + ".json").c_str());
     auto arr = [&](const char* key, uint64_t lutldpc_sim_counters::*m) {
       js << "  \"" << key << "\": [";
@@ -248,6 +284,27 @@ int main(int argc, char** argv) {
        << C[0]->get_rate() << ",\n  \"ldpc_ninfo\": " << K << ",\n  \"runtime\": " << runtime << ",\n  \"gpus\": " << gpus
        << ",\n  \"gitversion\": \"lut_ldpc_b200\"\n}\n";
     js.close();
+    {  // LDPC_BER_Sim_Results::write_itfile, src/LDPC_BER_Sim.cpp:342-361
+      ItWriter it(dir + "/" + name.str() + sfx + ".it");
+      auto col = [&](uint64_t lutldpc_sim_counters::*m) {
+        std::vector<double> v;
+        for (auto& p : points) v.push_back((double)(p.c.*m));
+        return v;
+      };
+      std::vector<double> snr_v;
+      for (auto& p : points) snr_v.push_back(p.snr);
+      it.vec("sim_SNRdB", snr_v);
+      it.vec("sim_Nframes", col(&lutldpc_sim_counters::frames));
+      it.vec("sim_Ndatabits", col(&lutldpc_sim_counters::data_bits));
+      it.vec("sim_frame_errors", col(&lutldpc_sim_counters::frame_errors));
+      it.vec("sim_data_bit_errors", col(&lutldpc_sim_counters::data_bit_errors));
+      it.vec("sim_uncoded_bit_errors", col(&lutldpc_sim_counters::uncoded_bit_errors));
+      it.vec("ldpc_nvar", {(double)N});
+      it.vec("ldpc_nchk", {(double)C[0]->get_nchk()});
+      it.vec("ldpc_code_rate", {C[0]->get_rate()});
+      it.f64("runtime", runtime);
+      it.str("gitversion", "lut_ldpc_b200");
+    }
     // copy of the params file next to the results, like the reference (:331-338)
     std::ifstream src(path(params).c_str(), std::ios::binary);
     std::string pbase = params.substr(params.find_last_of('/') == std::string::npos ? 0 : params.find_last_of('/') + 1);

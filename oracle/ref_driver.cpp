@@ -334,9 +334,33 @@ static int cmd_sim(const Args& a) {
   return 0;
 }
 
+// results <file.it>: read a results file the way the reference's tooling does (IT++ it_ifile; variables of
+// LDPC_BER_Sim_Results::write_itfile, src/LDPC_BER_Sim.cpp:342-361) and print it as one JSON line.  Used to
+// check the results writer of lut_ldpc_b200/host/ber_sim.cpp against IT++'s own reader.
+static int cmd_results(const Args& a) {
+  if (a.pos.size() < 1) { fprintf(stderr, "results <file.it>\n"); return 2; }
+  it_ifile f(a.pos[0]);
+  const char* vecs[] = {"sim_SNRdB", "sim_Nframes", "sim_Ndatabits", "sim_frame_errors", "sim_data_bit_errors",
+                        "sim_uncoded_bit_errors", "ldpc_nvar", "ldpc_nchk", "ldpc_code_rate"};
+  printf("{");
+  for (const char* n : vecs) {
+    vec v;
+    f >> Name(n) >> v;
+    printf("\"%s\": [", n);
+    for (int i = 0; i < v.size(); ++i) printf("%s%.17g", i ? ", " : "", v(i));
+    printf("], ");
+  }
+  double runtime = 0;
+  std::string git;
+  f >> Name("runtime") >> runtime;
+  f >> Name("gitversion") >> git;
+  printf("\"runtime\": %.17g, \"gitversion\": \"%s\"}\n", runtime, git.c_str());
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 2) {
-    fprintf(stderr, "usage: lutldpc_ref design|bundle|fixture|sim ...\n");
+    fprintf(stderr, "usage: lutldpc_ref design|bundle|fixture|sim|results ...\n");
     return 2;
   }
   std::string cmd = argv[1];
@@ -345,6 +369,7 @@ int main(int argc, char** argv) {
   if (cmd == "bundle") return cmd_bundle(a);
   if (cmd == "fixture") return cmd_fixture(a);
   if (cmd == "sim") return cmd_sim(a);
+  if (cmd == "results") return cmd_results(a);
   fprintf(stderr, "unknown command %s\n", cmd.c_str());
   return 2;
 }

@@ -121,6 +121,43 @@ def test_ber_sim_command_line(L, tmp_path):
     assert r["sim_frame_errors"][0] > 100 and r["sim_Nframes"][0] < 4000 + 8192  # Nfers stop
     # error rates fall with SNR; once FER < fer_min the sweep stops and later points stay empty
     assert r["sim_frame_errors"][1] < r["sim_frame_errors"][0]
+    # the IT++ results file (LDPC_BER_Sim_Results::write_itfile) holds the same numbers: read back with IT++'s own
+    # it_ifile through the compiled reference when it is there, and with a plain parser of the v3 layout always
+    itf = res[0][:-5] + ".it"
+    assert os.path.exists(itf)
+    got = _read_itfile(itf)
+    for k in ("sim_SNRdB", "sim_Nframes", "sim_Ndatabits", "sim_frame_errors", "sim_data_bit_errors", "sim_uncoded_bit_errors"):
+        assert got[k] == [float(x) for x in r[k]], k
+    assert got["ldpc_nvar"] == [500.0] and got["ldpc_nchk"] == [250.0] and isinstance(got["gitversion"], str)
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "lutldpc_ref")
+    if os.path.exists(ref_bin):
+        o = subprocess.run([ref_bin, "results", itf], capture_output=True, text=True, timeout=60)
+        assert o.returncode == 0, o.stderr
+        viaitpp = json.loads(o.stdout.strip().splitlines()[-1])
+        for k in ("sim_SNRdB", "sim_Nframes", "sim_frame_errors", "sim_data_bit_errors", "ldpc_code_rate"):
+            assert viaitpp[k] == got[k], k
+
+
+def _read_itfile(path):
+    """IT++ it_file v3: 'IT++' 3, then blocks u64 hdr, data, block; name, type, desc (NUL terminated); data."""
+    import struct
+    b = open(path, "rb").read()
+    assert b[:5] == b"IT++\x03"
+    off, out = 5, {}
+    while off < len(b):
+        hdr, data, block = struct.unpack("<QQQ", b[off:off + 24])
+        name, typ, _ = b[off + 24:off + hdr].split(b"\0")[:3]
+        d = b[off + hdr:off + hdr + data]
+        if typ == b"dvec":
+            (n,) = struct.unpack("<Q", d[:8])
+            out[name.decode()] = list(struct.unpack("<%dd" % n, d[8:8 + 8 * n]))
+        elif typ == b"float64":
+            out[name.decode()] = struct.unpack("<d", d)[0]
+        elif typ == b"string":
+            (n,) = struct.unpack("<Q", d[:8])
+            out[name.decode()] = d[8:8 + n].decode()
+        off += block
+    return out
 
 
 def test_python_harness_single_gpu(L):
