@@ -70,6 +70,9 @@ int lutldpc_decoder::init_device() {
       vn_classes[c].degree = m.var_trees.at(0, c).num_leaves;
       vn_classes[c].n = (int)lists[c].size();
       CK(vn_classes[c].list.upload(lists[c]), "upload vn class list");
+      std::vector<int2> pr(lists[c].size());
+      for (size_t i = 0; i < pr.size(); ++i) pr[i] = make_int2(lists[c][i], m.vn_edge0[lists[c][i]]);
+      CK(vn_classes[c].pairs.upload(pr), "upload vn class pairs");
     }
   }
   if (m.minLUT) {  // min-sum: checks grouped by exact degree, edge rows stored back to back
@@ -403,7 +406,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     } else {
       for (int c = 0; c < ncc; ++c) {
         const ProgRef& r = chk_progs[(size_t)t * ncc + c];
-        NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, cn_classes[c].list.p, cn_classes[c].n};
+        NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, cn_classes[c].list.p, nullptr, cn_classes[c].n};
         CK(launch_node(NODE_CHK, nl, g, b, want, st), "chk_lut"); launched(KIND_CHK0 + std::min(c, 15));
       }
     }
@@ -430,7 +433,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
         for (size_t j = 0; j < fused_classes.size(); ++j) {
           const int c = fused_classes[j];
           const ProgRef& r = var_progs[(size_t)t * nvc + c];
-          P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].list.p, r.fast_dv, r.q_out};
+          P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].pairs.p, r.fast_dv, r.q_out};
         }
         CK(launch_vn_fused(P, fused_max_dv, d_fused_tiles.p, n_fused_tiles, g, b, psc, st), "var_fused");
         launched(KIND_VN0 + 15);
@@ -439,7 +442,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
         if (!vn_classes[c].n) continue;
         if (std::find(fused_classes.begin(), fused_classes.end(), c) != fused_classes.end()) continue;
         const ProgRef& r = var_progs[(size_t)t * nvc + c];
-        NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
+        NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].pairs.p, vn_classes[c].n};
         if (r.fast_dv) CK(launch_vn_fast(r.fast_dv, blob + r.off + r.tables_off, r.q_out, nl, g, b, psc, st), "var_fast");
         else CK(launch_node(NODE_VAR, nl, g, b, psc, st), "var_lut");
         launched(KIND_VN0 + std::min(c, 15));
@@ -454,7 +457,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     for (int c = 0; c < nvc; ++c) {
       if (!vn_classes[c].n) continue;
       const ProgRef& r = var_progs[(size_t)t * nvc + c];
-      NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
+      NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].pairs.p, vn_classes[c].n};
       CK(launch_node(NODE_DEC, nl, g, b, 0, st), "dec_lut"); launched(KIND_DEC0 + std::min(c, 15));
     }
     CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
@@ -526,7 +529,7 @@ int lutldpc_decoder::run_passes_staggered() {
         for (size_t j = 0; j < stg_classes.size(); ++j) {
           const int c = stg_classes[j];
           const ProgRef& r = var_progs[(size_t)t * nvc + c];
-          P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].list.p, r.fast_dv, r.q_out};
+          P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].pairs.p, r.fast_dv, r.q_out};
           P.tab_off[j] = P.tab_bytes;
           P.tab_bytes += (r.fast_dv - 1) * 128;
         }
@@ -571,7 +574,7 @@ int lutldpc_decoder::run_passes_staggered() {
     for (int c = 0; c < nvc; ++c) {
       if (!vn_classes[c].n) continue;
       const ProgRef& r = var_progs[(size_t)t * nvc + c];
-      NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].n};
+      NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].pairs.p, vn_classes[c].n};
       CK(launch_node(NODE_DEC, nl, g, b, 0, st), "dec_lut"); launched(KIND_DEC0 + std::min(c, 15));
     }
     CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);

@@ -58,6 +58,7 @@ struct ProgRef {
 struct NodeClass {  // all variable (or check) nodes of one degree slot
   int degree = 0, n = 0;
   DevBuf<int32_t> list;
+  DevBuf<int2> pairs;  // variable classes: (node, first edge id) in list order
 };
 
 // streams, events and double-buffered device staging of the pipelined host-buffer decode (capi.cu: decode_host)

@@ -101,24 +101,42 @@ struct FastStore {
   }
 };
 
-// per-thread work of the specialised VN pass: nodes [i0, i1) of node_list, word column w
+// per-thread work of the specialised VN pass: nodes [i0, i1) of the class list, word column w.
+// Software-pipelined two nodes deep: while node i is evaluated, the messages of node i+1 are already in
+// flight and the (node, first edge) pair of node i+2 is being fetched, so the dependent chain
+// list -> messages (two global round trips) never sits in front of the look-ups.
 template <int DV>
-__device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int32_t* __restrict__ node_list, int i0, int i1,
-                                             const int32_t* __restrict__ vn_edge0, int W, int w,
-                                             uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
-                                             uint8_t* __restrict__ hard, uint32_t done_byte, int want_flags, int q_out,
-                                             uint32_t& failacc) {
+__device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int2* __restrict__ nodes, int i0, int i1,
+                                             int W, int w, uint32_t* __restrict__ msgs,
+                                             const uint32_t* __restrict__ cha, uint8_t* __restrict__ hard,
+                                             uint32_t done_byte, int want_flags, int q_out, uint32_t& failacc) {
   constexpr int NOPS = fastvn::Static<DV>::P.n_ops;
   const int so = q_out - 1, root_shift = 4 - q_out;
   const uint32_t uW = (uint32_t)W, uw = (uint32_t)w;
+  if (i0 >= i1) return;
+  uint32_t nxt[DV + 1];
+  int2 cur = nodes[i0];
+  int2 ahead = nodes[min(i0 + 1, i1 - 1)];
+  {
+    const uint32_t off0 = (uint32_t)cur.y * uW + uw;
+#pragma unroll
+    for (int k = 0; k < DV; ++k) nxt[k] = msgs[off0 + (uint32_t)k * uW];
+    nxt[DV] = cha[(uint32_t)cur.x * uW + uw];
+  }
   for (int i = i0; i < i1; ++i) {
-    const uint32_t node = (uint32_t)node_list[i];
-    const uint32_t off0 = (uint32_t)vn_edge0[node] * uW + uw;
-    const uint32_t offn = node * uW + uw;
+    const uint32_t off0 = (uint32_t)cur.y * uW + uw;
+    const uint32_t offn = (uint32_t)cur.x * uW + uw;
     uint32_t v[DV + 1 + NOPS];
 #pragma unroll
-    for (int k = 0; k < DV; ++k) v[k] = msgs[off0 + (uint32_t)k * uW];
-    v[DV] = cha[offn];
+    for (int k = 0; k <= DV; ++k) v[k] = nxt[k];
+    cur = ahead;
+    if (i + 1 < i1) {  // node i+1: its pair arrived during the previous iteration
+      const uint32_t o1 = (uint32_t)cur.y * uW + uw;
+#pragma unroll
+      for (int k = 0; k < DV; ++k) nxt[k] = msgs[o1 + (uint32_t)k * uW];
+      nxt[DV] = cha[(uint32_t)cur.x * uW + uw];
+      ahead = nodes[min(i + 2, i1 - 1)];
+    }
     fastvn::Exec<DV, 0>::run(v, tabs, root_shift);
     const uint32_t r0 = v[fastvn::Static<DV>::P.out[0]];
     uint32_t D = 0;

@@ -528,9 +528,8 @@ __global__ void k_quantize(const double* __restrict__ llr, size_t n, const doubl
 // ---------------------------------------------------------------------------------------------
 template <int DV>
 __global__ void __launch_bounds__(kNodeThreads, (DV <= 8 ? 12 : 0)) k_vn_fast(const uint8_t* __restrict__ tables_g,
-                                                           const int32_t* __restrict__ node_list, int n_nodes,
-                                                           int nodes_per_cta, const int32_t* __restrict__ vn_edge0,
-                                                           int W, uint32_t* __restrict__ msgs,
+                                                           const int2* __restrict__ nodes, int n_nodes,
+                                                           int nodes_per_cta, int W, uint32_t* __restrict__ msgs,
                                                            const uint32_t* __restrict__ cha, uint8_t* __restrict__ hard,
                                                            const uint32_t* __restrict__ done,
                                                            uint32_t* __restrict__ vn_fail, int want_flags, int q_out,
@@ -549,7 +548,7 @@ __global__ void __launch_bounds__(kNodeThreads, (DV <= 8 ? 12 : 0)) k_vn_fast(co
   if (dn == kNibOnes) return;
   uint32_t failacc = 0;
   const int i0 = blockIdx.x * nodes_per_cta;
-  vn_fast_body<DV>(tabs, node_list, i0, min(i0 + nodes_per_cta, n_nodes), vn_edge0, W, w, msgs, cha, hard,
+  vn_fast_body<DV>(tabs, nodes, i0, min(i0 + nodes_per_cta, n_nodes), W, w, msgs, cha, hard,
                    nib_bits_to_byte(dn, 0), want_flags, q_out, failacc);
   if (want_flags) flag_or(&vn_fail[w], failacc & kNibOnes);
 }
@@ -592,7 +591,7 @@ __global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fuse
 #define X(D)                                                                                                     \
   case D:                                                                                                        \
     if constexpr (D <= MAXDV)                                                                                    \
-      vn_fast_body<D>(tabs, cls.node_list, tile.y, tile.y + tile.z, vn_edge0, W, w, msgs, cha, hard, done_byte,  \
+      vn_fast_body<D>(tabs, cls.nodes, tile.y, tile.y + tile.z, W, w, msgs, cha, hard, done_byte,               \
                       want_flags, cls.q_out, failacc);                                                           \
     break;
     LUTLDPC_FAST_DVS(X)
@@ -742,7 +741,7 @@ cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const Nod
   switch (dv) {
 #define X(D)                                                                                                       \
   case D:                                                                                                          \
-    k_vn_fast<D><<<grid, kNodeThreads, 0, st>>>(d_tables, nl.node_list, nl.n_nodes, per, g.vn_edge0, b.W, b.msgs, \
+    k_vn_fast<D><<<grid, kNodeThreads, 0, st>>>(d_tables, nl.node_pairs, nl.n_nodes, per, b.W, b.msgs,            \
                                                 b.cha, b.hard, b.done, b.vn_fail, want_flags, q_out, b.cols,      \
                                                 b.n_active);                                                       \
     break;

@@ -48,6 +48,7 @@ struct NodeLaunch {       // one degree class of one pass
   const uint8_t* prog = nullptr;   // device image: DevProgHeader | ops | outs | tables
   uint32_t prog_bytes = 0, n_slots = 0, n_in = 0;
   const int32_t* node_list = nullptr;  // [n_nodes] VN (or check) indices of this class
+  const int2* node_pairs = nullptr;    // [n_nodes] (VN index, first edge) of the same nodes (specialised VN pass)
   int n_nodes = 0;
 };
 
@@ -73,7 +74,7 @@ cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const Nod
 // all specialised classes of a VN pass in one launch; tiles[i] = (class, first node, node count, 0)
 struct FusedVnClass {
   const uint8_t* tables;
-  const int32_t* node_list;
+  const int2* nodes;  // (VN index, first edge id) per node of the class: one load instead of two dependent ones
   int dv, q_out;
 };
 struct FusedVnParams {

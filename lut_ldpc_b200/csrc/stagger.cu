@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(StaggerCfg<MAXDV>::kThreads, 2)
 #define X(D)                                                                                                 \
   case D:                                                                                                    \
     if constexpr (D <= MAXDV)                                                                                \
-      vn_fast_body<D>(ctab, cls.node_list, it.y, it.y + it.z, vn_edge0, W, w, msgs, cha, hard, done_byte,    \
+      vn_fast_body<D>(ctab, cls.nodes, it.y, it.y + it.z, W, w, msgs, cha, hard, done_byte,                 \
                       P.vn_want, cls.q_out, failacc);                                                        \
     break;
         LUTLDPC_FAST_DVS(X)
