@@ -167,7 +167,7 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
  * of the handle; lutldpc_get_profile returns, per kind, the summed device milliseconds and launch
  * counts since profiling was switched on.  Kinds: 0 reset, 1 pack, 2 channel, 3 min-sum check pass,
  * 4 syndrome, 5 finalize, 6 unpack, 7 count, 8 encode, 9 staggered launch (check pass of one half of the
- * batch + variable pass of the other), 16+c variable-node pass of degree class c,
+ * batch + variable pass of the other), 10 frame repack, 11 retire (results of repacked frames back), 16+c variable-node pass of degree class c,
  * 32+c decision pass, 48+c LUT check pass.  class_degree/class_nodes [16] describe the VN classes. */
 #define LUTLDPC_PROFILE_KINDS 64
 int lutldpc_set_profiling(lutldpc_decoder* h, int on);
@@ -178,6 +178,15 @@ int lutldpc_get_profile(lutldpc_decoder* h, double* ms, int64_t* launches, int32
  * with CUDA events on the handle's stream, and number of kernels it launched */
 int lutldpc_last_call_stats(const lutldpc_decoder* h, double* device_ms, int64_t* kernel_launches,
                             int64_t* frame_iterations);
+
+/* ---- frame repacking (no counterpart in the reference, which decodes one frame at a time).  A frame that
+ * has returned keeps occupying its slot of the frame-interleaved batch; when fewer than `alpha` (0..1, default
+ * 0.8) of the slots in the words that still hold an unfinished frame are in use, the unfinished frames are
+ * gathered into a narrower layout and the remaining iterations run there.  Results are identical with
+ * repacking on or off (frames are independent); it needs the per-iteration poll (lutldpc_set_poll_interval
+ * >= 1).  on = 0 switches it off.  lutldpc_get_repack_count: repacks done by the handle so far. */
+int lutldpc_set_repack(lutldpc_decoder* h, int on, double alpha);
+int lutldpc_get_repack_count(const lutldpc_decoder* h, int64_t* repacks);
 
 #ifdef __cplusplus
 }

@@ -71,10 +71,11 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_set_stream", "lutldpc_set_poll_interval", "lutldpc_decode_quantized",
            "lutldpc_decode_quantized_device", "lutldpc_decode_llr", "lutldpc_decode_llr_device", "lutldpc_quantize",
            "lutldpc_decode_quantized_traced", "lutldpc_encode", "lutldpc_syndrome_check", "lutldpc_simulate_snr",
-           "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device"]
+           "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device",
+           "lutldpc_set_repack", "lutldpc_get_repack_count"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
-                 7: "count", 8: "encode", 9: "stagger_step"}
+                 7: "count", 8: "encode", 9: "stagger_step", 10: "repack", 11: "retire"}
 
 
 def load_library():
@@ -98,6 +99,8 @@ def load_library():
     L.lutldpc_set_initial_message_mode.argtypes = [vp, i32]
     L.lutldpc_set_stream.argtypes = [vp, vp]
     L.lutldpc_set_poll_interval.argtypes = [vp, i32]
+    L.lutldpc_set_repack.argtypes = [vp, i32, C.c_double]
+    L.lutldpc_get_repack_count.argtypes = [vp, vp]
     L.lutldpc_decode_quantized.argtypes = [vp, i32, vp, vp, vp, vp]
     L.lutldpc_decode_quantized_device.argtypes = [vp, i32, vp, vp, vp, vp]
     L.lutldpc_decode_llr.argtypes = [vp, i32, vp, vp, vp]
@@ -161,6 +164,16 @@ class Decoder:
 
     def set_poll_interval(self, every):
         self._ck(self._L.lutldpc_set_poll_interval(self._h, int(every)))
+
+    def set_repack(self, on, alpha=0.8):
+        """Frame repacking (gather of the unfinished frames into a narrower layout); results do not depend on it."""
+        self._ck(self._L.lutldpc_set_repack(self._h, int(bool(on)), float(alpha)))
+
+    @property
+    def repack_count(self):
+        n = C.c_int64(0)
+        self._ck(self._L.lutldpc_get_repack_count(self._h, C.byref(n)))
+        return int(n.value)
 
     # ---- decode (host buffers)
     def decode_quantized(self, cha, msg, out=None, iters=None):

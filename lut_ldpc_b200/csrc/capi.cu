@@ -433,4 +433,18 @@ int lutldpc_last_call_stats(const lutldpc_decoder* h, double* device_ms, int64_t
   return LUTLDPC_OK;
 }
 
+int lutldpc_set_repack(lutldpc_decoder* h, int on, double alpha) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (on && !(alpha > 0.0 && alpha <= 1.0)) return h->fail(LUTLDPC_ERR_ARG, "repack alpha must be in (0, 1]");
+  h->repack_on = on != 0;
+  if (on) h->repack_alpha = alpha;
+  return LUTLDPC_OK;
+}
+
+int lutldpc_get_repack_count(const lutldpc_decoder* h, int64_t* repacks) {
+  if (!h || !repacks) return LUTLDPC_ERR_ARG;
+  *repacks = h->repacks;
+  return LUTLDPC_OK;
+}
+
 }  // extern "C"

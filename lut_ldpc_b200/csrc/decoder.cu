@@ -2,6 +2,7 @@
 #include "decoder.hpp"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -109,6 +110,8 @@ int lutldpc_decoder::init_device() {
   }
 
   if (const char* e = getenv("LUTLDPC_GENERIC_VN")) use_fast_vn = !(e[0] == '1');
+  repack_on = env_int("LUTLDPC_REPACK", 1) != 0;
+  if (const char* e = getenv("LUTLDPC_REPACK_ALPHA")) repack_alpha = atof(e);
   // compile every (iteration slot, degree class) tree into a node program
   n_iter_slots = m.var_trees.n_iter;
   std::vector<int> slot_first_iter(n_iter_slots, -1);
@@ -280,12 +283,14 @@ void lutldpc_decoder::launched(int kind) {
 int lutldpc_decoder::flush_profile() {
   if (evn > 0) {
     CK(cudaEventSynchronize(evpool[evn - 1]), "profile sync");
+    static const bool dump = env_int("LUTLDPC_PROFILE_DUMP", 0) != 0;  // per-launch timeline on stderr
     for (int i = 1; i < evn; ++i) {
       if (evkind[i] < 0) continue;
       float ms = 0;
       CK(cudaEventElapsedTime(&ms, evpool[i - 1], evpool[i]), "profile elapsed");
       prof_ms[evkind[i]] += ms;
       prof_n[evkind[i]] += 1;
+      if (dump) fprintf(stderr, "launch %d kind %d ms %.4f\n", i, evkind[i], ms);
     }
   }
   evn = 0;
@@ -335,6 +340,47 @@ int lutldpc_decoder::begin_batch(int n_frames) {
   return LUTLDPC_OK;
 }
 
+int lutldpc_decoder::repack_into(BatchBuffers& cur, int slot, int n_live) {
+  RepackCtx& c = rctx[slot];
+  const int W = std::max(32, ((n_live + 255) / 256) * 32);
+  CK(c.msgs.ensure((size_t)m.num_edges * W), "alloc repack msgs");
+  CK(c.cha.ensure((size_t)m.nvar * W), "alloc repack cha");
+  CK(c.hard.ensure((size_t)m.nvar * W), "alloc repack hard");
+  CK(c.flags.ensure((size_t)4 * W + 32), "alloc repack flags");
+  CK(c.cols.ensure((size_t)W + W / 4), "alloc repack lists");
+  CK(c.iters.ensure((size_t)8 * W), "alloc repack iters");
+  CK(c.fid.ensure((size_t)8 * W), "alloc repack frame ids");
+  CK(buf_rsrc.ensure((size_t)8 * W), "alloc repack plan");
+  BatchBuffers n;
+  n.msgs = c.msgs.p; n.cha = c.cha.p; n.hard = c.hard.p;
+  n.done = c.flags.p; n.vn_fail = c.flags.p + W; n.cn_fail = c.flags.p + 2 * W; n.syn_fail = c.flags.p + 3 * W;
+  n.n_active = c.flags.p + 4 * W;
+  n.iters = c.iters.p; n.fid = c.fid.p;
+  n.cols = c.cols.p; n.grp4 = c.cols.p + W;
+  n.host_cols = (n_live + 7) / 8; n.host_grp4 = (n.host_cols + 3) / 4;
+  n.W = W; n.F = n_live;
+  // frames that finished in a repacked layout leave it now: their results go back to the original one
+  if (cur.fid) {
+    int rc = retire_from(cur);
+    if (rc) return rc;
+  }
+  CK(launch_repack(g, cur, n, buf_rsrc.p, stream), "repack"); launched(KIND_REPACK);
+  launches += 3;  // plan + msgs rows + cha rows + memset
+  cur = n;
+  ++repacks;
+  return LUTLDPC_OK;
+}
+
+int lutldpc_decoder::retire_from(const BatchBuffers& cur) {
+  if (!cur.fid) return LUTLDPC_OK;
+  CK(buf_ow_first.ensure((size_t)2 * b.W + 1), "alloc retire plan");
+  CK(buf_ow_mask.ensure((size_t)2 * b.W), "alloc retire plan");
+  CK(launch_retire(g, cur, b, buf_ow_first.p, buf_ow_mask.p, stream), "retire");
+  launched(KIND_RETIRE);
+  launches += 1;
+  return LUTLDPC_OK;
+}
+
 int lutldpc_decoder::run_batch(int n_frames, const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, TraceSink* tr) {
   int rc = begin_batch(n_frames);
   if (rc) return rc;
@@ -347,13 +393,15 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   if (stagger_ok && !tr && b.W >= 2 * kNodeThreads) return run_passes_staggered();
   int rc = 0;
   const int n_frames = b.F;
+  BatchBuffers cur = b;  // working layout: the batch itself until the first repack
+  int rslot = 0;
   const int nvc = (int)vn_classes.size(), ncc = (int)cn_classes.size();
   const uint8_t* blob = d_prog_blob.p;
   cudaStream_t st = stream;
   auto record = [&](int kind, int it, int Nq) -> int {
     if (!tr || !tr->live || tr->n_rec >= tr->max_rec) return 0;
     CK(buf_trace.ensure((size_t)m.num_edges), "alloc trace");
-    CK(launch_extract_frame(b, m.num_edges, tr->frame, Nq, buf_trace.p, st), "extract_frame");
+    CK(launch_extract_frame(cur, m.num_edges, tr->frame, Nq, buf_trace.p, st), "extract_frame");
     CK(cudaMemcpyAsync(tr->msgs + (size_t)tr->n_rec * m.num_edges, buf_trace.p, m.num_edges, cudaMemcpyDeviceToHost, st),
        "trace copy");
     CK(cudaStreamSynchronize(st), "trace sync");
@@ -365,8 +413,8 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   auto traced_frame_done = [&](bool& done) -> int {  // after a finalize
     int32_t it = 0;
     uint32_t dw = 0;
-    CK(cudaMemcpyAsync(&dw, b.done + (tr->frame >> 3), 4, cudaMemcpyDeviceToHost, st), "trace done copy");
-    CK(cudaMemcpyAsync(&it, b.iters + tr->frame, 4, cudaMemcpyDeviceToHost, st), "trace iters copy");
+    CK(cudaMemcpyAsync(&dw, cur.done + (tr->frame >> 3), 4, cudaMemcpyDeviceToHost, st), "trace done copy");
+    CK(cudaMemcpyAsync(&it, cur.iters + tr->frame, 4, cudaMemcpyDeviceToHost, st), "trace iters copy");
     CK(cudaStreamSynchronize(st), "trace sync");
     done = (dw >> (4 * (tr->frame & 7))) & 1;
     return 0;
@@ -374,19 +422,28 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   auto poll = [&](bool& all_done) -> int {
     all_done = false;
     if (poll_every <= 0) return 0;
-    CK(cudaMemcpyAsync(h_active, b.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
+    CK(cudaMemcpyAsync(h_active, cur.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
     CK(cudaStreamSynchronize(st), "poll sync");
     all_done = h_active[0] == 0;
     // the work lists only shrink, so their lengths at this poll bound every later launch
-    b.host_cols = (int)h_active[2];
-    b.host_grp4 = (int)h_active[3];
+    cur.host_cols = (int)h_active[2];
+    cur.host_grp4 = (int)h_active[3];
+    // frame repacking: too many slots of the live words belong to frames that have already returned
+    const int n_live = (int)h_active[0];
+    const int dense_cols = (n_live + 7) / 8;
+    if (repack_on && !tr && n_live > 0 && (double)n_live < repack_alpha * 8.0 * cur.host_cols &&
+        (std::max(32, ((n_live + 255) / 256) * 32) < cur.W || 2 * dense_cols <= cur.host_cols)) {
+      int rc2 = repack_into(cur, rslot, n_live);
+      if (rc2) return rc2;
+      rslot ^= 1;
+    }
     return 0;
   };
   bool all_done = false;
   if (tr) tr->live = true;
   if (pisc) {  // :277
-    CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
-    CK(launch_finalize(FIN_INIT, 0, b, st), "finalize"); launched(KIND_FINALIZE);
+    CK(launch_syndrome(g, cur, st), "syndrome"); launched(KIND_SYNDROME);
+    CK(launch_finalize(FIN_INIT, 0, cur, st), "finalize"); launched(KIND_FINALIZE);
     if (tr) { bool d = false; if ((rc = traced_frame_done(d))) return rc; if (d) tr->live = false; }
     if ((rc = poll(all_done))) return rc;
   }
@@ -398,21 +455,21 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     // check-node pass (:304-310); its sign parities complete the early-exit test of VN pass ii-1
     if (m.minLUT && use_cn_exact) {
       for (auto& cl : cn_exact) {
-        CK(launch_cn_exact(cl.degree, cl.list.p, cl.n, b, code_bits(m.Nq_Msg[ii]), want, st), "cn_exact");
+        CK(launch_cn_exact(cl.degree, cl.list.p, cl.n, cur, code_bits(m.Nq_Msg[ii]), want, st), "cn_exact");
         launched(KIND_CN);
       }
     } else if (m.minLUT) {
-      CK(launch_cn_minsum(g, b, code_bits(m.Nq_Msg[ii]), want, st), "cn_minsum"); launched(KIND_CN);
+      CK(launch_cn_minsum(g, cur, code_bits(m.Nq_Msg[ii]), want, st), "cn_minsum"); launched(KIND_CN);
     } else {
       for (int c = 0; c < ncc; ++c) {
         const ProgRef& r = chk_progs[(size_t)t * ncc + c];
         NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, cn_classes[c].list.p, nullptr, cn_classes[c].n};
-        CK(launch_node(NODE_CHK, nl, g, b, want, st), "chk_lut"); launched(KIND_CHK0 + std::min(c, 15));
+        CK(launch_node(NODE_CHK, nl, g, cur, want, st), "chk_lut"); launched(KIND_CHK0 + std::min(c, 15));
       }
     }
     if ((rc = record(LUTLDPC_TRACE_CN, ii, m.Nq_Msg[ii]))) return rc;
     if (want) {  // psc: VN pass ii-1 unanimous and syndrome zero -> return ii (:327)
-      CK(launch_finalize(FIN_ITER, ii, b, st), "finalize"); launched(KIND_FINALIZE);
+      CK(launch_finalize(FIN_ITER, ii, cur, st), "finalize"); launched(KIND_FINALIZE);
       if (tr && tr->live) {
         bool d = false;
         if ((rc = traced_frame_done(d))) return rc;
@@ -435,7 +492,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
           const ProgRef& r = var_progs[(size_t)t * nvc + c];
           P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].pairs.p, r.fast_dv, r.q_out};
         }
-        CK(launch_vn_fused(P, fused_max_dv, d_fused_tiles.p, n_fused_tiles, g, b, psc, st), "var_fused");
+        CK(launch_vn_fused(P, fused_max_dv, d_fused_tiles.p, n_fused_tiles, g, cur, psc, st), "var_fused");
         launched(KIND_VN0 + 15);
       }
       for (int c = 0; c < nvc; ++c) {
@@ -443,8 +500,8 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
         if (std::find(fused_classes.begin(), fused_classes.end(), c) != fused_classes.end()) continue;
         const ProgRef& r = var_progs[(size_t)t * nvc + c];
         NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].pairs.p, vn_classes[c].n};
-        if (r.fast_dv) CK(launch_vn_fast(r.fast_dv, blob + r.off + r.tables_off, r.q_out, nl, g, b, psc, st), "var_fast");
-        else CK(launch_node(NODE_VAR, nl, g, b, psc, st), "var_lut");
+        if (r.fast_dv) CK(launch_vn_fast(r.fast_dv, blob + r.off + r.tables_off, r.q_out, nl, g, cur, psc, st), "var_fast");
+        else CK(launch_node(NODE_VAR, nl, g, cur, psc, st), "var_lut");
         launched(KIND_VN0 + std::min(c, 15));
       }
       if ((rc = record(LUTLDPC_TRACE_VN, ii, m.Nq_Msg[ii + 1]))) return rc;
@@ -458,11 +515,12 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
       if (!vn_classes[c].n) continue;
       const ProgRef& r = var_progs[(size_t)t * nvc + c];
       NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].pairs.p, vn_classes[c].n};
-      CK(launch_node(NODE_DEC, nl, g, b, 0, st), "dec_lut"); launched(KIND_DEC0 + std::min(c, 15));
+      CK(launch_node(NODE_DEC, nl, g, cur, 0, st), "dec_lut"); launched(KIND_DEC0 + std::min(c, 15));
     }
-    CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
-    CK(launch_finalize(FIN_LAST, max_iters, b, st), "finalize"); launched(KIND_FINALIZE);
+    CK(launch_syndrome(g, cur, st), "syndrome"); launched(KIND_SYNDROME);
+    CK(launch_finalize(FIN_LAST, max_iters, cur, st), "finalize"); launched(KIND_FINALIZE);
   }
+  if ((rc = retire_from(cur))) return rc;
   CK(cudaEventRecord(ev1, st), "event");
   have_stats = true;
   last_frames = n_frames;

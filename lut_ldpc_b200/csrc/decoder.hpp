@@ -16,6 +16,7 @@ enum ProfileKind {  // indices of lutldpc_get_profile
   KIND_RESET = 0, KIND_PACK = 1, KIND_CHANNEL = 2, KIND_CN = 3, KIND_SYNDROME = 4, KIND_FINALIZE = 5,
   KIND_UNPACK = 6, KIND_COUNT = 7, KIND_ENCODE = 8,
   KIND_STEP = 9,  // staggered launch: check pass of one half of the batch + variable pass of the other
+  KIND_REPACK = 10, KIND_RETIRE = 11,  // frame repacking: gather of the unfinished frames / results back
   KIND_VN0 = 16, KIND_DEC0 = 32, KIND_CHK0 = 48  // + degree-class index
 };
 
@@ -78,6 +79,13 @@ struct HostPipe {
   }
 };
 
+// device buffers of one repacked layout (decoder.cu: run_passes); two of them alternate
+struct RepackCtx {
+  DevBuf<uint32_t> msgs, cha, flags, cols;
+  DevBuf<uint8_t> hard;
+  DevBuf<int32_t> iters, fid;
+};
+
 struct TraceSink {
   int frame = -1, max_rec = 0, n_rec = 0;
   uint8_t* msgs = nullptr;
@@ -130,6 +138,14 @@ struct lutldpc_decoder {
   lutldpc::DevBuf<uint32_t> buf_ferr;              // per-word frame-error flags (byte form)
   lutldpc::DevBuf<unsigned long long> buf_cnt;     // device image of lutldpc_sim_counters
   uint32_t* h_active = nullptr;  // pinned
+  // frame repacking: when fewer than repack_alpha of the slots in the live words hold an unfinished frame, the
+  // unfinished frames are gathered into a narrower layout (LUTLDPC_REPACK=0 switches it off)
+  lutldpc::RepackCtx rctx[2];
+  lutldpc::DevBuf<int32_t> buf_rsrc, buf_ow_first;
+  lutldpc::DevBuf<uint8_t> buf_ow_mask;
+  bool repack_on = true;
+  double repack_alpha = 0.8;
+  int64_t repacks = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool have_stats = false;
   int64_t launches = 0, last_frames = 0, stat_frame_iters = -1;
@@ -153,6 +169,9 @@ struct lutldpc_decoder {
   int run_batch(int n_frames, const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, lutldpc::TraceSink* tr);
   int begin_batch(int n_frames);            // buffers + flag reset + start event
   int run_passes(lutldpc::TraceSink* tr);   // all iterations + decision on the initialised batch
+  // gathers the unfinished frames of `cur` (n_live of them) into rctx[slot]; `cur` becomes the new layout
+  int repack_into(lutldpc::BatchBuffers& cur, int slot, int n_live);
+  int retire_from(const lutldpc::BatchBuffers& cur);  // results of a repacked layout back into b
   int run_passes_staggered();               // same result, the two halves of the batch half an iteration apart
   int max_batch_frames() const;
 };

@@ -4,6 +4,7 @@
 // no tensor cores (this is table look-up and compare, not a contraction).
 #include "kernels.hpp"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 
@@ -473,6 +474,203 @@ __global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int w0, 
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Frame repacking.  The reference decodes one frame at a time (src/LDPC_Code_LUT.cpp:259-353), so a frame
+// that returns early simply stops costing anything.  Here 8 frames share a word and a row of W words is
+// the unit of every memory access: a finished frame keeps occupying its nibble, and a lone straggler
+// keeps a whole 32-byte sector per edge alive.  When enough frames of a batch have returned, the
+// unfinished ones are gathered -- order preserved -- into a narrower layout (W_new < W_old) and the
+// remaining iterations run there.  Results of frames that finish in a repacked layout are moved back to
+// the original layout (retire), so everything after the pass schedule still sees hard[nvar][W] / iters of
+// the original batch.  Frames are independent: which word a frame sits in is not observable in its result.
+//
+// plan (single CTA): src[s'] = old slot of new slot s' (-1: padding), fid_new[s'] = original frame id,
+// flags / work lists of the new layout.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) k_repack_plan(int W_old, const uint32_t* __restrict__ done_old,
+                                                      const int32_t* __restrict__ fid_old, int W_new,
+                                                      int32_t* __restrict__ src, int32_t* __restrict__ fid_new,
+                                                      uint32_t* done_new, uint32_t* vn_fail, uint32_t* cn_fail,
+                                                      uint32_t* syn_fail, int32_t* __restrict__ iters_new,
+                                                      uint32_t* n_active_new, uint32_t* cols_new,
+                                                      uint32_t* grp4_new) {
+  __shared__ uint32_t psum[32];
+  __shared__ uint32_t pbase;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int S_new = 8 * W_new;
+  if (threadIdx.x == 0) pbase = 0;
+  __syncthreads();
+  for (int c0 = 0; c0 < W_old; c0 += 1024) {
+    const int w = c0 + threadIdx.x;
+    const uint32_t lm = w < W_old ? (~done_old[w] & kNibOnes) : 0u;
+    const uint32_t cnt = __popc(lm);
+    uint32_t incl = cnt;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) psum[wid] = incl;
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+    for (int j = 0; j < 32; ++j) {
+      const uint32_t v = psum[j];
+      before += j < wid ? v : 0;
+      total += v;
+    }
+    uint32_t at = pbase + before + incl - cnt;
+    for (int j = 0; j < 8; ++j)
+      if ((lm >> (4 * j)) & 1) {
+        if (at < (uint32_t)S_new) {
+          src[at] = 8 * w + j;
+          fid_new[at] = fid_old ? fid_old[8 * w + j] : 8 * w + j;
+        }
+        ++at;
+      }
+    __syncthreads();
+    if (threadIdx.x == 0) pbase += total;
+    __syncthreads();
+  }
+  const int n_live = min((int)pbase, S_new);
+  for (int s = n_live + threadIdx.x; s < S_new; s += 1024) {
+    src[s] = -1;
+    fid_new[s] = -1;
+  }
+  for (int s = threadIdx.x; s < S_new; s += 1024) iters_new[s] = 0;
+  for (int w = threadIdx.x; w < W_new; w += 1024) {
+    uint32_t d = 0;
+    for (int j = 0; j < 8; ++j)
+      if (8 * w + j >= n_live) d |= 1u << (4 * j);
+    done_new[w] = d;
+    vn_fail[w] = 0;
+    cn_fail[w] = 0;
+    syn_fail[w] = 0;
+  }
+  if (threadIdx.x == 0) {
+    n_active_new[0] = (uint32_t)n_live;
+    n_active_new[1] = 0;
+  }
+  __syncthreads();
+  build_lists(W_new, done_new, cols_new, grp4_new, n_active_new);
+}
+
+// rows of msgs / cha: new word w' of row r = the nibbles of old slots src[8w' .. 8w'+7] of the same row.
+// src is increasing, so the 8 sources of a thread lie in a few adjacent old words and neighbouring
+// threads read neighbouring ranges: the old row is streamed once.
+__global__ void __launch_bounds__(128) k_repack_rows(const int32_t* __restrict__ src,
+                                                     const uint32_t* __restrict__ old_rows, int W_old,
+                                                     uint32_t* __restrict__ new_rows, int W_new, int n_rows,
+                                                     int rows_per_cta) {
+  const int w = blockIdx.y * 128 + threadIdx.x;
+  if (w >= W_new) return;
+  const int4 sa = reinterpret_cast<const int4*>(src)[2 * w], sb = reinterpret_cast<const int4*>(src)[2 * w + 1];
+  const int s[8] = {sa.x, sa.y, sa.z, sa.w, sb.x, sb.y, sb.z, sb.w};
+  // padding slots (src < 0, only at the end of the layout) read word 0 and are masked out
+  uint32_t off[8], sh[8], keep[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    off[j] = s[j] >= 0 ? (uint32_t)s[j] >> 3 : 0u;
+    sh[j] = 4u * ((uint32_t)s[j] & 7u);
+    keep[j] = s[j] >= 0 ? 0xFu : 0u;
+  }
+  constexpr int R = 4;  // rows in flight per thread: 32 independent (mostly L1-resident) loads
+  const int r0 = blockIdx.x * rows_per_cta, r1 = min(n_rows, r0 + rows_per_cta);
+  int r = r0;
+  for (; r + R <= r1; r += R) {
+    uint32_t x[R][8];
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      const uint32_t* row = old_rows + (size_t)(r + i) * W_old;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[i][j] = __ldg(row + off[j]);
+    }
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+      uint32_t out = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) out |= ((x[i][j] >> sh[j]) & keep[j]) << (4 * j);
+      __stcs(new_rows + (size_t)(r + i) * W_new + w, out);
+    }
+  }
+  for (; r < r1; ++r) {
+    const uint32_t* row = old_rows + (size_t)r * W_old;
+    uint32_t out = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) out |= ((__ldg(row + off[j]) >> sh[j]) & keep[j]) << (4 * j);
+    __stcs(new_rows + (size_t)r * W_new + w, out);
+  }
+}
+
+// retire, step 1 (thread = slot of the repacked layout): lut_decode returns of the finished frames go to
+// their original frame index; per ORIGINAL word w0 that has frames in this layout: the first slot they
+// occupy (they are consecutive, order is preserved), which of its 8 frames are here (ow_in) and which of
+// those have finished (ow_ret).  ow_ret is zero-filled before the launch.
+__global__ void k_retire_plan(int W_c, const uint32_t* __restrict__ done_c, const int32_t* __restrict__ fid_c,
+                              const int32_t* __restrict__ iters_c, int32_t* __restrict__ iters0,
+                              int32_t* __restrict__ ow_first, uint8_t* __restrict__ ow_in,
+                              uint8_t* __restrict__ ow_ret, int32_t* __restrict__ ret_list,
+                              uint32_t* __restrict__ ret_count) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  const int S = 8 * W_c;
+  if (s >= S) return;
+  const int f = fid_c[s];
+  if (f < 0) return;
+  if ((done_c[s >> 3] >> (4 * (s & 7))) & 1) iters0[f] = iters_c[s];
+  if (s > 0 && (fid_c[s - 1] >> 3) == (f >> 3)) return;
+  const int w0 = f >> 3;
+  uint32_t m_in = 0, m_ret = 0;
+  for (int k = 0; k < 8 && s + k < S; ++k) {
+    const int fk = fid_c[s + k];
+    if (fk < 0 || (fk >> 3) != w0) break;
+    const uint32_t bit = 1u << (fk & 7);
+    m_in |= bit;
+    if ((done_c[(s + k) >> 3] >> (4 * ((s + k) & 7))) & 1) m_ret |= bit;
+  }
+  ow_first[w0] = s;
+  ow_in[w0] = (uint8_t)m_in;
+  ow_ret[w0] = (uint8_t)m_ret;
+  if (m_ret) ret_list[atomicAdd(ret_count, 1u)] = w0;  // order is irrelevant
+}
+
+// retire, step 2 (thread = (rows, listed original word)): hard bits of the finished frames back to hard0[nvar][W0]
+__global__ void __launch_bounds__(128) k_retire_hard(int nvar, int W0, int W_c, const int32_t* __restrict__ ret_list,
+                                                     const uint32_t* __restrict__ ret_count,
+                                                     const int32_t* __restrict__ ow_first,
+                                                     const uint8_t* __restrict__ ow_in,
+                                                     const uint8_t* __restrict__ ow_ret,
+                                                     const uint8_t* __restrict__ hard_c, uint8_t* __restrict__ hard0,
+                                                     int rows_per_cta) {
+  const int i = blockIdx.y * 128 + threadIdx.x;
+  if (i >= (int)*ret_count) return;
+  const int w0 = ret_list[i];
+  const uint32_t m_ret = ow_ret[w0], m_in = ow_in[w0];
+  const int s0 = ow_first[w0];
+  const int byte0 = s0 >> 3, sh = s0 & 7;
+  const int second = byte0 + 1 < W_c ? 1 : 0;
+  const int v0 = blockIdx.x * rows_per_cta, v1 = min(nvar, v0 + rows_per_cta);
+  constexpr int R = 8;
+  for (int v = v0; v < v1; v += R) {
+    uint32_t x[R], o[R];
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      const int vv = min(v + k, v1 - 1);
+      const uint8_t* hc = hard_c + (size_t)vv * W_c + byte0;
+      x[k] = ((uint32_t)hc[0] | ((uint32_t)hc[second] << 8)) >> sh;
+      o[k] = hard0[(size_t)vv * W0 + w0];
+    }
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+      uint32_t out = 0, xx = x[k];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if ((m_in >> j) & 1) {
+          out |= (xx & 1u) << j;
+          xx >>= 1;
+        }
+      if (v + k < v1) hard0[(size_t)(v + k) * W0 + w0] = (uint8_t)((o[k] & ~m_ret) | (out & m_ret));
+    }
+  }
+}
+
 // hard[nvar][W] -> out_bits[F][nvar]
 __global__ void __launch_bounds__(256) k_unpack(const uint8_t* __restrict__ hard, int nvar, int F, int W,
                                                 uint8_t* __restrict__ out) {
@@ -783,6 +981,40 @@ cudaError_t launch_finalize_range(FinalizeMode mode, int value, const BatchBuffe
   const int full = w0 == 0 && w1 == b.W;
   k_finalize<<<1, 1024, 0, st>>>((int)mode, value, w0, w1, b.done, b.vn_fail, b.cn_fail, b.syn_fail, b.iters,
                                  n_active, full ? b.W : 0, b.cols, b.grp4, b.n_active);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_repack(const GraphArrays& g, const BatchBuffers& from, const BatchBuffers& to, int32_t* d_src,
+                          cudaStream_t st) {
+  k_repack_plan<<<1, 1024, 0, st>>>(from.W, from.done, from.fid, to.W, d_src, to.fid, to.done, to.vn_fail, to.cn_fail,
+                                    to.syn_fail, to.iters, to.n_active, to.cols, to.grp4);
+  const int rows_per = 32;
+  dim3 ge(cdiv(g.num_edges, rows_per), cdiv(to.W, 128));
+  k_repack_rows<<<ge, 128, 0, st>>>(d_src, from.msgs, from.W, to.msgs, to.W, g.num_edges, rows_per);
+  dim3 gn(cdiv(g.nvar, rows_per), cdiv(to.W, 128));
+  k_repack_rows<<<gn, 128, 0, st>>>(d_src, from.cha, from.W, to.cha, to.W, g.nvar, rows_per);
+  cudaError_t e = cudaMemsetAsync(to.hard, 0, (size_t)g.nvar * to.W, st);
+  return e != cudaSuccess ? e : cudaGetLastError();
+}
+
+cudaError_t launch_retire(const GraphArrays& g, const BatchBuffers& from, const BatchBuffers& orig, int32_t* d_ow_first,
+                          uint8_t* d_ow_mask, cudaStream_t st) {
+  // d_ow_first: [2 * W0 + 1] ints = first slot per original word | list of original words | count
+  // d_ow_mask:  [2 * W0] bytes    = frames present | frames retiring
+  int32_t* d_list = d_ow_first + orig.W;
+  uint32_t* d_count = reinterpret_cast<uint32_t*>(d_ow_first + 2 * orig.W);
+  uint8_t *d_ow_in = d_ow_mask, *d_ow_ret = d_ow_mask + orig.W;
+  cudaError_t e = cudaMemsetAsync(d_ow_ret, 0, (size_t)orig.W, st);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(d_count, 0, 4, st);
+  if (e != cudaSuccess) return e;
+  k_retire_plan<<<cdiv(8 * from.W, 256), 256, 0, st>>>(from.W, from.done, from.fid, from.iters, orig.iters, d_ow_first,
+                                                      d_ow_in, d_ow_ret, d_list, d_count);
+  const int rows_per = 64;
+  const int max_words = std::min(orig.W, 8 * from.W);
+  dim3 grid(cdiv(g.nvar, rows_per), cdiv(max_words, 128));
+  k_retire_hard<<<grid, 128, 0, st>>>(g.nvar, orig.W, from.W, d_list, d_count, d_ow_first, d_ow_in, d_ow_ret, from.hard,
+                                      orig.hard, rows_per);
   return cudaGetLastError();
 }
 

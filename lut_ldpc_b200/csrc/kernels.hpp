@@ -31,6 +31,7 @@ struct BatchBuffers {
   uint32_t* cols = nullptr;      // [W]
   uint32_t* grp4 = nullptr;      // [W/4]
   int host_cols = 0, host_grp4 = 0;  // host-side upper bounds of the list lengths (grid sizing)
+  int32_t* fid = nullptr;        // repacked layouts: original frame index of every slot (-1 padding); nullptr = identity
   int W = 0;                     // words per row
   int F = 0;                     // real frames (<= 8W)
 };
@@ -117,6 +118,14 @@ cudaError_t launch_finalize_range(FinalizeMode mode, int value, const BatchBuffe
                                   uint32_t* n_active, cudaStream_t st);
 cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st);
 cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b, cudaStream_t st);
+// frame repacking (kernels.cu): gather the unfinished frames of `from` into the narrower layout `to`
+// (flags, work lists, frame ids, msgs and cha rows); d_src = scratch [8 * to.W]
+cudaError_t launch_repack(const GraphArrays& g, const BatchBuffers& from, const BatchBuffers& to, int32_t* d_src,
+                          cudaStream_t st);
+// results (hard bits, lut_decode returns) of the frames that finished in the repacked layout `from` back to the
+// original layout `orig`; scratch: d_ow_first [2 * orig.W + 1] ints, d_ow_mask [2 * orig.W] bytes
+cudaError_t launch_retire(const GraphArrays& g, const BatchBuffers& from, const BatchBuffers& orig, int32_t* d_ow_first,
+                          uint8_t* d_ow_mask, cudaStream_t st);
 cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_bits, cudaStream_t st);
 cudaError_t launch_extract_frame(const BatchBuffers& b, int num_edges, int frame, int Nq, uint8_t* d_out,
                                  cudaStream_t st);

@@ -210,6 +210,47 @@ def test_staggered_equals_sequential_schedule(L, cfg):
         assert np.array_equal(want_it, it[sel]) and np.array_equal(want_out, out[sel])
 
 
+@pytest.mark.parametrize("cfg,snr,n", [("c2_irr_n500", 1.5, 3000), ("c1b_reg36_n1000", 1.8, 2100),
+                                       ("c3_irr_n10000", 1.1, 1300), ("c5_n64800", 1.25, 1100)])
+def test_frame_repacking_is_not_observable(L, cfg, snr, n):
+    """Frames that return early are dropped from the frame-interleaved batch by gathering the unfinished
+    ones into a narrower layout (several times per batch at an aggressive threshold): decisions and
+    lut_decode returns equal those of the fixed layout and, on a sample, the oracle; ragged frame count,
+    frames that finish at the initial check, early, late and never."""
+    dec, ref = L.Decoder(_golden.bundle_path(cfg)), _dec(L, cfg)
+    ref.set_repack(False)
+    ref_count0 = ref.repack_count
+    rng = np.random.default_rng(5)
+    sigma = np.sqrt(0.5 / (dec.rate * 10 ** (snr / 10)))
+    llr = (2.0 / sigma ** 2) * (1.0 + sigma * rng.standard_normal((n, dec.nvar)))
+    llr[::7] = np.abs(llr[::7]) + 1.0  # clean frames: return 0 at the initial syndrome check (pisc)
+    cha, msg = dec.quantize(llr)
+    for alpha in (0.97, 0.8, 0.5):
+        dec.set_repack(True, alpha)
+        for psc, pisc in ((1, 1), (1, 0), (0, 1)):
+            dec.set_exit_conditions(dec.max_iters, psc, pisc)
+            ref.set_exit_conditions(ref.max_iters, psc, pisc)
+            before = dec.repack_count
+            o1, i1 = dec.decode_quantized(cha, msg)
+            o2, i2 = ref.decode_quantized(cha, msg)
+            assert np.array_equal(i1, i2) and np.array_equal(o1, o2), (alpha, psc, pisc)
+            if psc and alpha > 0.9:
+                assert dec.repack_count > before, "no repack happened"
+            if psc and pisc:
+                assert len(np.unique(i1)) > 3
+    assert ref.repack_count == ref_count0
+    ref.set_repack(True)
+    if cfg in ("c2_irr_n500", "c1b_reg36_n1000"):
+        orc = pyoracle.Oracle(_golden.bundle_path(cfg))
+        orc.set_exit_conditions(dec.max_iters, 1, 1)
+        dec.set_exit_conditions(dec.max_iters, 1, 1)
+        dec.set_repack(True, 0.9)
+        out, it = dec.decode_quantized(cha, msg)
+        sel = np.r_[0:60, n - 60:n]
+        want_out, want_it = orc.lut_decode_batch(cha[sel], msg[sel])
+        assert np.array_equal(want_it, it[sel]) and np.array_equal(want_out, out[sel])
+
+
 def test_host_path_is_chunked_and_pipelined_bit_exact(L, monkeypatch):
     """lutldpc_decode_quantized / _llr cut a call into chunks that overlap their copies with the decoder
     (double-buffered staging, three streams).  Forced to 256-frame chunks: 5 chunks incl. a ragged last one,
