@@ -27,6 +27,7 @@ lutldpc_decoder::~lutldpc_decoder() {
     if (e) cudaEventDestroy(e);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
+  if (ev_lag) cudaEventDestroy(ev_lag);
   for (cudaEvent_t e : evpool) cudaEventDestroy(e);
 }
 
@@ -169,7 +170,7 @@ int lutldpc_decoder::init_device() {
       fused_classes.push_back(c);
       fused_max_dv = std::max(fused_max_dv, vn_classes[c].degree);
       int ops = (int)var_progs[c].n_ops;
-      int per = std::max(1, env_int("LUTLDPC_VN_TILE_OPS", 128) / std::max(1, ops));
+      int per = std::max(1, env_int("LUTLDPC_VN_TILE_OPS", 256) / std::max(1, ops));
       int nt = (vn_classes[c].n + per - 1) / per;
       for (int i = 0; i < nt; ++i)
         tiles.push_back({(i + 0.5) / nt, make_int4(j, i * per, std::min(per, vn_classes[c].n - i * per), 0)});
@@ -259,7 +260,9 @@ int lutldpc_decoder::init_device() {
     if (r.bytes + (size_t)r.n_slots * kNodeThreads * 4 > 200 * 1024)
       return fail(LUTLDPC_ERR_MODEL, "a node program (LUTs + value slots) exceeds the 200 KiB shared-memory budget");
   CK(d_prog_blob.upload(blob), "upload node programs");
-  CK(cudaMallocHost((void**)&h_active, 4 * sizeof(uint32_t)), "cudaMallocHost");
+  CK(cudaMallocHost((void**)&h_active, 8 * sizeof(uint32_t)), "cudaMallocHost");
+  CK(cudaEventCreateWithFlags(&ev_lag, cudaEventDisableTiming), "cudaEventCreate");
+  lag_poll = env_int("LUTLDPC_LAG_POLL", 1) != 0;
   CK(cudaEventCreate(&ev0), "cudaEventCreate");
   CK(cudaEventCreate(&ev1), "cudaEventCreate");
   return LUTLDPC_OK;
@@ -311,8 +314,8 @@ int lutldpc_decoder::max_batch_frames() const {
 
 int lutldpc_decoder::ensure_batch(int n_frames) {
   int W = ((n_frames + 255) / 256) * 32;
-  CK(buf_msgs.ensure((size_t)m.num_edges * W), "alloc msgs");
-  CK(buf_cha.ensure((size_t)m.nvar * W), "alloc cha");
+  CK(buf_msgs.ensure((size_t)m.num_edges * W + 4), "alloc msgs");  // + slack: the repack gather over-reads 2 words
+  CK(buf_cha.ensure((size_t)m.nvar * W + 4), "alloc cha");
   CK(buf_hard.ensure((size_t)m.nvar * W), "alloc hard");
   CK(buf_flags.ensure((size_t)4 * W + 32), "alloc flags");
   CK(buf_cols.ensure((size_t)W + W / 4), "alloc work lists");
@@ -343,8 +346,8 @@ int lutldpc_decoder::begin_batch(int n_frames) {
 int lutldpc_decoder::repack_into(BatchBuffers& cur, int slot, int n_live) {
   RepackCtx& c = rctx[slot];
   const int W = std::max(32, ((n_live + 255) / 256) * 32);
-  CK(c.msgs.ensure((size_t)m.num_edges * W), "alloc repack msgs");
-  CK(c.cha.ensure((size_t)m.nvar * W), "alloc repack cha");
+  CK(c.msgs.ensure((size_t)m.num_edges * W + 4), "alloc repack msgs");
+  CK(c.cha.ensure((size_t)m.nvar * W + 4), "alloc repack cha");
   CK(c.hard.ensure((size_t)m.nvar * W), "alloc repack hard");
   CK(c.flags.ensure((size_t)4 * W + 32), "alloc repack flags");
   CK(c.cols.ensure((size_t)W + W / 4), "alloc repack lists");
@@ -395,6 +398,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   const int n_frames = b.F;
   BatchBuffers cur = b;  // working layout: the batch itself until the first repack
   int rslot = 0;
+  int n_live_known = n_frames;  // unfinished frames at the last waiting poll
   const int nvc = (int)vn_classes.size(), ncc = (int)cn_classes.size();
   const uint8_t* blob = d_prog_blob.p;
   cudaStream_t st = stream;
@@ -430,6 +434,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     cur.host_grp4 = (int)h_active[3];
     // frame repacking: too many slots of the live words belong to frames that have already returned
     const int n_live = (int)h_active[0];
+    n_live_known = n_live;
     const int dense_cols = (n_live + 7) / 8;
     if (repack_on && !tr && n_live > 0 && (double)n_live < repack_alpha * 8.0 * cur.host_cols &&
         (std::max(32, ((n_live + 255) / 256) * 32) < cur.W || 2 * dense_cols <= cur.host_cols)) {
@@ -440,6 +445,7 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     return 0;
   };
   bool all_done = false;
+  bool lagging = lag_poll && !tr && poll_every == 1, lag_inflight = false;
   if (tr) tr->live = true;
   if (pisc) {  // :277
     CK(launch_syndrome(g, cur, st), "syndrome"); launched(KIND_SYNDROME);
@@ -479,8 +485,26 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
         }
       }
       if (poll_every > 0 && ++polled % poll_every == 0) {
-        if ((rc = poll(all_done))) return rc;
-        if (all_done) break;
+        // While no frame of the batch has returned yet there is nothing to decide: the counters are copied
+        // without waiting and looked at one iteration later, so the stream never drains.  The first copy that
+        // shows a returned frame switches to the waiting poll (exact counts for grids, repacking, termination).
+        bool wait = !lagging;
+        if (lagging) {
+          if (lag_inflight) {
+            CK(cudaEventSynchronize(ev_lag), "poll sync");
+            lag_inflight = false;
+            if (h_active[4] != (uint32_t)n_live_known) { lagging = false; wait = true; }
+          }
+          if (lagging) {
+            CK(cudaMemcpyAsync(h_active + 4, cur.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
+            CK(cudaEventRecord(ev_lag, st), "poll event");
+            lag_inflight = true;
+          }
+        }
+        if (wait) {
+          if ((rc = poll(all_done))) return rc;
+          if (all_done) break;
+        }
       }
     }
     if (ii != max_iters - 1) {  // variable-node pass (:320-325)

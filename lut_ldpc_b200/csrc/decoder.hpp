@@ -137,7 +137,9 @@ struct lutldpc_decoder {
   lutldpc::DevBuf<uint8_t> buf_cw;                 // transmitted codeword bits, [nvar][W] like hard
   lutldpc::DevBuf<uint32_t> buf_ferr;              // per-word frame-error flags (byte form)
   lutldpc::DevBuf<unsigned long long> buf_cnt;     // device image of lutldpc_sim_counters
-  uint32_t* h_active = nullptr;  // pinned
+  uint32_t* h_active = nullptr;  // pinned [8]: waiting poll | lagged poll
+  cudaEvent_t ev_lag = nullptr;
+  bool lag_poll = true;
   // frame repacking: when fewer than repack_alpha of the slots in the live words hold an unfinished frame, the
   // unfinished frames are gathered into a narrower layout (LUTLDPC_REPACK=0 switches it off)
   lutldpc::RepackCtx rctx[2];

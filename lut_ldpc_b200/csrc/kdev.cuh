@@ -47,7 +47,8 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 // Whole-CTA helper: thread 0 issues the copy (in <= 16 KiB pieces), everyone waits for the bytes.
 // `bytes` must be a multiple of 16.  The barrier is single-use (parity 0).
-__device__ __forceinline__ void stage_to_smem(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+// stage_issue + stage_wait: the wait can be placed after independent work (e.g. the first message loads)
+__device__ __forceinline__ void stage_issue(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   if (threadIdx.x == 0) {
     mbar_init(bar, 1);
     fence_barrier_init();
@@ -61,7 +62,11 @@ __device__ __forceinline__ void stage_to_smem(void* dst, const void* src, uint32
       bulk_g2s((char*)dst + off, (const char*)src + off, n, bar);
     }
   }
-  mbar_wait(bar, 0);
+}
+__device__ __forceinline__ void stage_wait(uint64_t* bar) { mbar_wait(bar, 0); }
+__device__ __forceinline__ void stage_to_smem(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  stage_issue(dst, src, bytes, bar);
+  stage_wait(bar);
 }
 
 // OR `f` into a per-word flag that thousands of threads of the same pass target: look first (L2) and
@@ -146,6 +151,82 @@ __device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int2* __
       uint8_t* hp = hard + offn;
       const uint32_t nb = nib_bits_to_byte(r0, so);
       *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
+    }
+  }
+}
+
+
+template <int DV, int II>
+struct FastStore2 {
+  static __device__ __forceinline__ void run(const uint32_t (&va)[DV + 1 + fastvn::Static<DV>::P.n_ops],
+                                             const uint32_t (&vb)[DV + 1 + fastvn::Static<DV>::P.n_ops],
+                                             uint32_t* __restrict__ msgs, uint32_t off0, uint32_t W, uint32_t ra0,
+                                             uint32_t rb0, uint32_t& Da, uint32_t& Db) {
+    if constexpr (II < DV) {
+      constexpr int kOut = fastvn::Static<DV>::P.out[II];
+      const uint32_t ra = va[kOut], rb = vb[kOut];
+      *reinterpret_cast<uint2*>(msgs + off0 + (uint32_t)II * W) = make_uint2(ra, rb);
+      if constexpr (II > 0) {
+        Da |= ra ^ ra0;
+        Db |= rb ^ rb0;
+      }
+      FastStore2<DV, II + 1>::run(va, vb, msgs, off0, W, ra0, rb0, Da, Db);
+    }
+  }
+};
+
+// Two word columns (16 frames) per thread: the per-node work that does not depend on the number of frames
+// (pair fetch, address arithmetic, loop control) is shared by twice the look-ups and the two independent
+// look-up chains give the scheduler more to overlap.  Used for the low degrees, where that fixed part is as
+// large as the look-ups themselves and the values still fit the register budget.  Columns w, w+1 (w even).
+template <int DV>
+__device__ __forceinline__ void vn_fast_body2(const uint8_t* tabs, const int2* __restrict__ nodes, int i0, int i1,
+                                              int W, int w, uint32_t* __restrict__ msgs,
+                                              const uint32_t* __restrict__ cha, uint8_t* __restrict__ hard,
+                                              uint32_t done_bytes, int want_flags, int q_out, uint32_t& fail0,
+                                              uint32_t& fail1) {
+  constexpr int NOPS = fastvn::Static<DV>::P.n_ops;
+  const int so = q_out - 1, root_shift = 4 - q_out;
+  const uint32_t uW = (uint32_t)W, uw = (uint32_t)w;
+  if (i0 >= i1) return;
+  uint2 nxt[DV + 1];
+  int2 cur = nodes[i0];
+  int2 ahead = nodes[min(i0 + 1, i1 - 1)];
+  {
+    const uint32_t off0 = (uint32_t)cur.y * uW + uw;
+#pragma unroll
+    for (int k = 0; k < DV; ++k) nxt[k] = *reinterpret_cast<const uint2*>(msgs + off0 + (uint32_t)k * uW);
+    nxt[DV] = *reinterpret_cast<const uint2*>(cha + (uint32_t)cur.x * uW + uw);
+  }
+  for (int i = i0; i < i1; ++i) {
+    const uint32_t off0 = (uint32_t)cur.y * uW + uw;
+    const uint32_t offn = (uint32_t)cur.x * uW + uw;
+    uint32_t va[DV + 1 + NOPS], vb[DV + 1 + NOPS];
+#pragma unroll
+    for (int k = 0; k <= DV; ++k) {
+      va[k] = nxt[k].x;
+      vb[k] = nxt[k].y;
+    }
+    cur = ahead;
+    if (i + 1 < i1) {
+      const uint32_t o1 = (uint32_t)cur.y * uW + uw;
+#pragma unroll
+      for (int k = 0; k < DV; ++k) nxt[k] = *reinterpret_cast<const uint2*>(msgs + o1 + (uint32_t)k * uW);
+      nxt[DV] = *reinterpret_cast<const uint2*>(cha + (uint32_t)cur.x * uW + uw);
+      ahead = nodes[min(i + 2, i1 - 1)];
+    }
+    fastvn::Exec<DV, 0>::run(va, tabs, root_shift);
+    fastvn::Exec<DV, 0>::run(vb, tabs, root_shift);
+    constexpr int kOut0 = fastvn::Static<DV>::P.out[0];
+    const uint32_t ra0 = va[kOut0], rb0 = vb[kOut0];
+    uint32_t Da = 0, Db = 0;
+    FastStore2<DV, 0>::run(va, vb, msgs, off0, uW, ra0, rb0, Da, Db);
+    if (want_flags) {
+      fail0 |= Da >> so;
+      fail1 |= Db >> so;
+      uint16_t* hp = reinterpret_cast<uint16_t*>(hard + offn);
+      const uint32_t nb = nib_bits_to_byte(ra0, so) | (nib_bits_to_byte(rb0, so) << 8);
+      *hp = (uint16_t)((*hp & done_bytes) | (nb & ~done_bytes));
     }
   }
 }

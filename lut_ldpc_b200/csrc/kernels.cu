@@ -26,26 +26,47 @@ __device__ __forceinline__ uint32_t lab2code(uint32_t m, int Nq, int q) {
 // Tile = 32 variable nodes x 256 frames through shared memory so that reads are 32-byte sectors of a
 // frame row and writes are 128-byte lines of an edge row.
 // ---------------------------------------------------------------------------------------------
+template <bool VEC4>
 __global__ void __launch_bounds__(256) k_pack(const uint8_t* __restrict__ cha_lab, const uint8_t* __restrict__ msg_lab,
                                               const int32_t* __restrict__ vn_edge0, int nvar, int F, int W,
                                               int Nq_cha, int q_cha, int Nq_msg, int q_msg,
                                               uint32_t* __restrict__ cha, uint32_t* __restrict__ msgs,
                                               uint8_t* __restrict__ hard) {
-  __shared__ uint8_t tc[256][33];
-  __shared__ uint8_t tm[256][33];
+  // one byte per (frame, node): channel code in the low nibble, message code in the high nibble
+  __shared__ uint8_t t[256][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int v0 = blockIdx.x * 32, w0 = blockIdx.y * 32, f0 = w0 * 8;
-  for (int i = 0; i < 32; ++i) {
-    int fl = ty + 8 * i, f = f0 + fl, v = v0 + tx;
-    uint8_t c = 0, m = 0;
-    bool in = f < F && v < nvar;
-    if (in) {
-      c = cha_lab[(size_t)f * nvar + v];
-      m = msg_lab[(size_t)f * nvar + v];
+  if (VEC4) {  // nvar % 4 == 0 and 4-byte aligned label arrays: four nodes per load
+    const int q4 = threadIdx.x & 7, fr = threadIdx.x >> 3;
+    const int v = v0 + 4 * q4;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int fl = fr + 32 * i, f = f0 + fl;
+      uint32_t c4 = 0, m4 = 0;
+      const bool in = f < F && v < nvar;
+      if (in) {
+        c4 = *reinterpret_cast<const uint32_t*>(cha_lab + (size_t)f * nvar + v);
+        m4 = *reinterpret_cast<const uint32_t*>(msg_lab + (size_t)f * nvar + v);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        // padded frames carry the weakest positive label (code 0)
+        const uint32_t c = in ? lab2code((c4 >> (8 * k)) & 0xFF, Nq_cha, q_cha) : 0u;
+        const uint32_t m = in ? lab2code((m4 >> (8 * k)) & 0xFF, Nq_msg, q_msg) : 0u;
+        t[fl][4 * q4 + k] = (uint8_t)(c | (m << 4));
+      }
     }
-    // padded frames carry the weakest positive label (code 0)
-    tc[fl][tx] = in ? (uint8_t)lab2code(c, Nq_cha, q_cha) : 0;
-    tm[fl][tx] = in ? (uint8_t)lab2code(m, Nq_msg, q_msg) : 0;
+  } else {
+    for (int i = 0; i < 32; ++i) {
+      int fl = ty + 8 * i, f = f0 + fl, v = v0 + tx;
+      uint8_t c = 0, m = 0;
+      bool in = f < F && v < nvar;
+      if (in) {
+        c = cha_lab[(size_t)f * nvar + v];
+        m = msg_lab[(size_t)f * nvar + v];
+      }
+      t[fl][tx] = in ? (uint8_t)(lab2code(c, Nq_cha, q_cha) | (lab2code(m, Nq_msg, q_msg) << 4)) : 0;
+    }
   }
   __syncthreads();
   const int w = w0 + tx;
@@ -55,8 +76,9 @@ __global__ void __launch_bounds__(256) k_pack(const uint8_t* __restrict__ cha_la
     uint32_t cw = 0, mw = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      cw |= (uint32_t)tc[8 * tx + j][vi] << (4 * j);
-      mw |= (uint32_t)tm[8 * tx + j][vi] << (4 * j);
+      const uint32_t x = t[8 * tx + j][vi];
+      cw |= (x & 0xFu) << (4 * j);
+      mw |= (x >> 4) << (4 * j);
     }
     cha[(size_t)v * W + w] = cw;
     hard[(size_t)v * W + w] = (uint8_t)nib_bits_to_byte(cw, q_cha - 1);
@@ -205,11 +227,13 @@ __global__ void __launch_bounds__(128) k_cn_exact(const int32_t* __restrict__ ro
                                                   uint32_t* __restrict__ msgs, const uint32_t* __restrict__ done,
                                                   uint32_t* __restrict__ cn_fail, int want_fail,
                                                   const uint32_t* __restrict__ grp4,
-                                                  const uint32_t* __restrict__ n_lists) {
+                                                  const uint32_t* __restrict__ n_lists, int n_checks, int tx_log2) {
   typedef typename WordVec<VEC>::T V;
-  // thread i of the pass owns VEC adjacent columns of live group grp4[i / (4 / VEC)]
-  const int i = blockIdx.y * blockDim.x + threadIdx.x;
-  if (i >= (int)n_lists[3] * (4 / VEC)) return;
+  // thread i of the pass owns VEC adjacent columns of live group grp4[i / (4 / VEC)]; a CTA covers
+  // 2^tx_log2 such threads of 128 >> tx_log2 checks (narrow layouts: several checks per CTA)
+  const int check = (blockIdx.x << (7 - tx_log2)) + (threadIdx.x >> tx_log2);
+  const int i = (blockIdx.y << tx_log2) + (threadIdx.x & ((1 << tx_log2) - 1));
+  if (check >= n_checks || i >= (int)n_lists[3] * (4 / VEC)) return;
   const int w = (int)grp4[i / (4 / VEC)] * 4 + (i % (4 / VEC)) * VEC;
   union U { V v; uint32_t u[VEC]; };
   U dn;
@@ -219,7 +243,7 @@ __global__ void __launch_bounds__(128) k_cn_exact(const int32_t* __restrict__ ro
   for (int j = 0; j < VEC; ++j) all_done &= dn.u[j] == kNibOnes;
   if (all_done) return;
   const QMask qm = make_qmask(q);
-  const int32_t* r = rows + (size_t)blockIdx.x * DC;
+  const int32_t* r = rows + (size_t)check * DC;
   uint32_t* p[DC];
 #pragma unroll
   for (int k = 0; k < DC; ++k) p[k] = msgs + (size_t)r[k] * W + w;
@@ -572,8 +596,55 @@ __global__ void __launch_bounds__(128) k_repack_rows(const int32_t* __restrict__
     sh[j] = 4u * ((uint32_t)s[j] & 7u);
     keep[j] = s[j] >= 0 ? 0xFu : 0u;
   }
-  constexpr int R = 4;  // rows in flight per thread: 32 independent (mostly L1-resident) loads
   const int r0 = blockIdx.x * rows_per_cta, r1 = min(n_rows, r0 + rows_per_cta);
+  // Dense case (every thread of the warp finds its 8 sources inside 4 consecutive old words, i.e. at least a
+  // quarter of the old slots is still in use): 4 loads per row and byte permutes.  The sources are the nibbles
+  // p_j = s[j] - 8 * b0 of the 16-byte string x0 x1 x2 x3; PRMT fetches the bytes p_j >> 1 of the even (odd) output
+  // nibbles into the four byte lanes, a masked shift moves each nibble to its half.  Old rows are read up to three
+  // words past their end (the next row, or the slack the buffers carry) and those bytes are never selected.
+  const uint32_t b0 = s[0] >= 0 ? (uint32_t)s[0] >> 3 : 0u;
+  bool span_ok = true;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) span_ok &= s[j] < 0 || ((uint32_t)s[j] >> 3) - b0 <= 3u;
+  if (__all_sync(0xFFFFFFFFu, span_ok)) {
+    uint32_t selA[2] = {0, 0}, selB[2] = {0, 0}, mB[2] = {0, 0}, mlo[2] = {0, 0}, mhi[2] = {0, 0};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (s[j] < 0) continue;
+      const uint32_t pj = (uint32_t)s[j] - 8u * b0, q = pj >> 1, lane = (uint32_t)j >> 1, h = j & 1;
+      if (q < 8) selA[h] |= q << (4 * lane);
+      else {
+        selB[h] |= (q - 8) << (4 * lane);
+        mB[h] |= 0xFFu << (8 * lane);
+      }
+      // even outputs end in the low half of their byte lane, odd outputs in the high half
+      const uint32_t want = h ? 0xF0u : 0x0Fu;
+      if ((pj & 1) == (uint32_t)h) mlo[h] |= want << (8 * lane);  // already in the right half
+      else mhi[h] |= want << (8 * lane);                           // needs the 4-bit shift
+    }
+    constexpr int R = 4;
+    for (int r = r0; r < r1; r += R) {
+      uint32_t x0[R], x1[R], x2[R], x3[R];
+#pragma unroll
+      for (int i = 0; i < R; ++i) {
+        const uint32_t* p = old_rows + (size_t)min(r + i, r1 - 1) * W_old + b0;
+        x0[i] = __ldg(p);
+        x1[i] = __ldg(p + 1);
+        x2[i] = __ldg(p + 2);
+        x3[i] = __ldg(p + 3);
+      }
+#pragma unroll
+      for (int i = 0; i < R; ++i) {
+        const uint32_t Ae = __byte_perm(x0[i], x1[i], selA[0]), Be = __byte_perm(x2[i], x3[i], selB[0]);
+        const uint32_t Ao = __byte_perm(x0[i], x1[i], selA[1]), Bo = __byte_perm(x2[i], x3[i], selB[1]);
+        const uint32_t E = (Ae & ~mB[0]) | (Be & mB[0]), O = (Ao & ~mB[1]) | (Bo & mB[1]);
+        const uint32_t out = (E & mlo[0]) | ((E >> 4) & mhi[0]) | (O & mlo[1]) | ((O << 4) & mhi[1]);
+        if (r + i < r1) __stcs(new_rows + (size_t)(r + i) * W_new + w, out);
+      }
+    }
+    return;
+  }
+  constexpr int R = 4;  // rows in flight per thread: 32 independent (mostly L1-resident) loads
   int r = r0;
   for (; r + R <= r1; r += R) {
     uint32_t x[R][8];
@@ -607,8 +678,7 @@ __global__ void __launch_bounds__(128) k_repack_rows(const int32_t* __restrict__
 __global__ void k_retire_plan(int W_c, const uint32_t* __restrict__ done_c, const int32_t* __restrict__ fid_c,
                               const int32_t* __restrict__ iters_c, int32_t* __restrict__ iters0,
                               int32_t* __restrict__ ow_first, uint8_t* __restrict__ ow_in,
-                              uint8_t* __restrict__ ow_ret, int32_t* __restrict__ ret_list,
-                              uint32_t* __restrict__ ret_count) {
+                              uint8_t* __restrict__ ow_ret) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   const int S = 8 * W_c;
   if (s >= S) return;
@@ -628,7 +698,36 @@ __global__ void k_retire_plan(int W_c, const uint32_t* __restrict__ done_c, cons
   ow_first[w0] = s;
   ow_in[w0] = (uint8_t)m_in;
   ow_ret[w0] = (uint8_t)m_ret;
-  if (m_ret) ret_list[atomicAdd(ret_count, 1u)] = w0;  // order is irrelevant
+}
+
+// ordered list of the original words that have retiring frames (single CTA): neighbouring threads of the next
+// kernel then touch neighbouring bytes of hard0
+__global__ void __launch_bounds__(1024) k_retire_list(int W0, const uint8_t* __restrict__ ow_ret,
+                                                      int32_t* __restrict__ ret_list, uint32_t* __restrict__ ret_count) {
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t base_s;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) base_s = 0;
+  __syncthreads();
+  for (int c0 = 0; c0 < W0; c0 += 1024) {
+    const int i = c0 + threadIdx.x;
+    const bool hit = i < W0 && ow_ret[i] != 0;
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, hit);
+    if (lane == 0) wsum[wid] = __popc(bal);
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+    for (int j = 0; j < 32; ++j) {
+      const uint32_t v = wsum[j];
+      before += j < wid ? v : 0;
+      total += v;
+    }
+    const uint32_t base = base_s;
+    if (hit) ret_list[base + before + __popc(bal & ((1u << lane) - 1u))] = i;
+    __syncthreads();
+    if (threadIdx.x == 0) base_s = base + total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *ret_count = base_s;
 }
 
 // retire, step 2 (thread = (rows, listed original word)): hard bits of the finished frames back to hard0[nvar][W0]
@@ -646,6 +745,23 @@ __global__ void __launch_bounds__(128) k_retire_hard(int nvar, int W0, int W_c, 
   const int s0 = ow_first[w0];
   const int byte0 = s0 >> 3, sh = s0 & 7;
   const int second = byte0 + 1 < W_c ? 1 : 0;
+  // bit k of the shifted source = k-th frame of this word present in the layout -> bit position of that frame:
+  // a bit-expand by m_in (Hacker's Delight 7-5), its three move masks are row-invariant
+  uint32_t mv[3];
+  {
+    uint32_t m = m_in, mk = ~m << 1;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      uint32_t mp = mk ^ (mk << 1);
+      mp ^= mp << 2;
+      mp ^= mp << 4;
+      mp ^= mp << 8;
+      mp ^= mp << 16;
+      mv[i] = mp & m;
+      m = (m ^ mv[i]) | (mv[i] >> (1 << i));
+      mk &= ~mp;
+    }
+  }
   const int v0 = blockIdx.x * rows_per_cta, v1 = min(nvar, v0 + rows_per_cta);
   constexpr int R = 8;
   for (int v = v0; v < v1; v += R) {
@@ -659,14 +775,13 @@ __global__ void __launch_bounds__(128) k_retire_hard(int nvar, int W0, int W_c, 
     }
 #pragma unroll
     for (int k = 0; k < R; ++k) {
-      uint32_t out = 0, xx = x[k];
+      uint32_t xx = x[k] & 0xFFu;
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if ((m_in >> j) & 1) {
-          out |= (xx & 1u) << j;
-          xx >>= 1;
-        }
-      if (v + k < v1) hard0[(size_t)(v + k) * W0 + w0] = (uint8_t)((o[k] & ~m_ret) | (out & m_ret));
+      for (int i = 2; i >= 0; --i) {
+        const uint32_t t = xx << (1 << i);
+        xx = (xx & ~mv[i]) | (t & mv[i]);
+      }
+      if (v + k < v1) hard0[(size_t)(v + k) * W0 + w0] = (uint8_t)((o[k] & ~m_ret) | (xx & m_ret));
     }
   }
 }
@@ -763,6 +878,18 @@ static const fastvn::Prog* fast_prog(int dv) {
 // All specialised degree classes of one VN pass in ONE launch.  A tile = a few nodes of one class; the
 // host interleaves the tiles of the classes (FusedVnPlan), so CTAs that are bound by HBM latency
 // (dv 2, 3) and CTAs that are bound by shared-memory look-ups (dv 8 ...) are resident on an SM together.
+// Degrees up to kVnWideMaxDv run two word columns per thread (vn_fast_body2): thread i owns the column pair
+// (i & 1) of live group grp4[i >> 1].
+constexpr int kVnWideMaxDv = 3;
+static int vn_wide_max_dv() {
+  static const int v = [] {
+    const char* e = getenv("LUTLDPC_VN_WIDE_MAXDV");
+    int x = e ? atoi(e) : kVnWideMaxDv;
+    return x < 0 ? 0 : (x > kVnWideMaxDv ? kVnWideMaxDv : x);
+  }();
+  return v;
+}
+
 template <int MAXDV>
 __global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fused(FusedVnParams P, const int4* __restrict__ tiles,
                                                             const int32_t* __restrict__ vn_edge0, int W,
@@ -770,16 +897,50 @@ __global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fuse
                                                             uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
                                                             uint32_t* __restrict__ vn_fail, int want_flags,
                                                             const uint32_t* __restrict__ cols,
-                                                            const uint32_t* __restrict__ n_lists) {
+                                                            const uint32_t* __restrict__ grp4,
+                                                            const uint32_t* __restrict__ n_lists, int wide_max_dv) {
   __shared__ __align__(128) uint8_t tabs[(MAXDV - 1) * 128];
   __shared__ uint64_t bar;
-  const int n_cols = (int)n_lists[2];
-  if ((int)(blockIdx.y * kNodeThreads) >= n_cols) return;  // whole CTA beyond the live columns
   const int4 tile = tiles[blockIdx.x];  // x = class, y = first node, z = node count
   const FusedVnClass cls = P.c[tile.x];
+  const bool wide = cls.dv <= wide_max_dv;
+  const int n_items = wide ? 2 * (int)n_lists[3] : (int)n_lists[2];
+  if ((int)(blockIdx.y * kNodeThreads) >= n_items) return;  // whole CTA beyond the live columns
   stage_to_smem(tabs, cls.tables, (uint32_t)(cls.dv - 1) * 128u, &bar);
-  const int i = blockIdx.y * kNodeThreads + threadIdx.x;
-  if (i >= n_cols) return;
+  int i = blockIdx.y * kNodeThreads + threadIdx.x;
+  int node0 = tile.y, node1 = tile.y + tile.z;
+  if (n_items <= 64) {  // narrow layout: the thread groups of the CTA share the nodes of the tile
+    const int tx_log2 = n_items <= 32 ? 5 : 6;
+    const int nsub = kNodeThreads >> tx_log2, sub = threadIdx.x >> tx_log2;
+    const int per = (tile.z + nsub - 1) / nsub;
+    i = threadIdx.x & ((1 << tx_log2) - 1);
+    node0 = tile.y + sub * per;
+    node1 = min(tile.y + tile.z, node0 + per);
+  }
+  if (i >= n_items) return;
+  if (wide) {
+    const int w = (int)grp4[i >> 1] * 4 + (i & 1) * 2;
+    const uint2 dn = *reinterpret_cast<const uint2*>(done + w);
+    if (dn.x == kNibOnes && dn.y == kNibOnes) return;
+    const uint32_t done_bytes = nib_bits_to_byte(dn.x, 0) | (nib_bits_to_byte(dn.y, 0) << 8);
+    uint32_t f0 = 0, f1 = 0;
+    switch (cls.dv) {
+      case 2:
+        vn_fast_body2<2>(tabs, cls.nodes, node0, node1, W, w, msgs, cha, hard, done_bytes, want_flags,
+                         cls.q_out, f0, f1);
+        break;
+      case 3:
+        if constexpr (MAXDV >= 3)
+          vn_fast_body2<3>(tabs, cls.nodes, node0, node1, W, w, msgs, cha, hard, done_bytes, want_flags,
+                           cls.q_out, f0, f1);
+        break;
+    }
+    if (want_flags) {
+      flag_or(&vn_fail[w], f0 & kNibOnes);
+      flag_or(&vn_fail[w + 1], f1 & kNibOnes);
+    }
+    return;
+  }
   const int w = (int)cols[i];
   const uint32_t dn = done[w];
   if (dn == kNibOnes) return;
@@ -789,8 +950,8 @@ __global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fuse
 #define X(D)                                                                                                     \
   case D:                                                                                                        \
     if constexpr (D <= MAXDV)                                                                                    \
-      vn_fast_body<D>(tabs, cls.nodes, tile.y, tile.y + tile.z, W, w, msgs, cha, hard, done_byte,               \
-                      want_flags, cls.q_out, failacc);                                                           \
+      vn_fast_body<D>(tabs, cls.nodes, node0, node1, W, w, msgs, cha, hard, done_byte,                          \
+                      want_flags, cls.q_out, failacc);                                                                 \
     break;
     LUTLDPC_FAST_DVS(X)
 #undef X
@@ -837,8 +998,13 @@ static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 cudaError_t launch_pack(const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, const GraphArrays& g,
                         const BatchBuffers& b, int Nq_cha, int Nq_msg, cudaStream_t st) {
   dim3 grid(cdiv(g.nvar, 32), cdiv(b.W, 32));
-  k_pack<<<grid, 256, 0, st>>>(d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha),
-                               Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard);
+  const bool vec4 = g.nvar % 4 == 0 && ((uintptr_t)d_cha_lab | (uintptr_t)d_msg_lab) % 4 == 0;
+  if (vec4)
+    k_pack<true><<<grid, 256, 0, st>>>(d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha),
+                                       Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard);
+  else
+    k_pack<false><<<grid, 256, 0, st>>>(d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha),
+                                        Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard);
   return cudaGetLastError();
 }
 
@@ -890,8 +1056,10 @@ cudaError_t launch_cn_exact(int dc, const int32_t* d_rows, int n_checks, const B
   if (n_checks == 0) return cudaSuccess;
   static const int vec = env_int("LUTLDPC_CN_VEC", 2) == 4 ? 4 : 2;
   if (b.host_grp4 <= 0) return cudaSuccess;
-  dim3 grid(n_checks, cdiv(b.host_grp4 * (4 / vec), 128));
-#define CN_X_ARGS d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail, b.grp4, b.n_active
+  const int items = b.host_grp4 * (4 / vec);
+  const int tx_log2 = items <= 32 ? 5 : (items <= 64 ? 6 : 7);
+  dim3 grid(cdiv(n_checks, 128 >> tx_log2), cdiv(items, 1 << tx_log2));
+#define CN_X_ARGS d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail, b.grp4, b.n_active, n_checks, tx_log2
   switch (dc) {
 #define X(D)                                                              \
   case D:                                                                 \
@@ -954,8 +1122,10 @@ cudaError_t launch_vn_fast(int dv, const uint8_t* d_tables, int q_out, const Nod
 cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_tiles, int n_tiles, const GraphArrays& g,
                             const BatchBuffers& b, int want_flags, cudaStream_t st) {
   if (n_tiles == 0 || b.host_cols <= 0) return cudaSuccess;
-  dim3 grid(n_tiles, cdiv(b.host_cols, kNodeThreads));
-#define FUSED_ARGS P, d_tiles, g.vn_edge0, b.W, b.msgs, b.cha, b.hard, b.done, b.vn_fail, want_flags, b.cols, b.n_active
+  const int wide = vn_wide_max_dv();
+  dim3 grid(n_tiles, cdiv(std::max(b.host_cols, wide >= 2 ? 2 * b.host_grp4 : 0), kNodeThreads));
+#define FUSED_ARGS P, d_tiles, g.vn_edge0, b.W, b.msgs, b.cha, b.hard, b.done, b.vn_fail, want_flags, b.cols, b.grp4, \
+                   b.n_active, wide
   if (max_dv <= 4) k_vn_fused<4><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
   else if (max_dv <= 8) k_vn_fused<8><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
   else if (max_dv <= 12) k_vn_fused<12><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
@@ -1006,10 +1176,9 @@ cudaError_t launch_retire(const GraphArrays& g, const BatchBuffers& from, const 
   uint8_t *d_ow_in = d_ow_mask, *d_ow_ret = d_ow_mask + orig.W;
   cudaError_t e = cudaMemsetAsync(d_ow_ret, 0, (size_t)orig.W, st);
   if (e != cudaSuccess) return e;
-  e = cudaMemsetAsync(d_count, 0, 4, st);
-  if (e != cudaSuccess) return e;
   k_retire_plan<<<cdiv(8 * from.W, 256), 256, 0, st>>>(from.W, from.done, from.fid, from.iters, orig.iters, d_ow_first,
-                                                      d_ow_in, d_ow_ret, d_list, d_count);
+                                                      d_ow_in, d_ow_ret);
+  k_retire_list<<<1, 1024, 0, st>>>(orig.W, d_ow_ret, d_list, d_count);
   const int rows_per = 64;
   const int max_words = std::min(orig.W, 8 * from.W);
   dim3 grid(cdiv(g.nvar, rows_per), cdiv(max_words, 128));
