@@ -263,6 +263,7 @@ int lutldpc_decoder::init_device() {
   CK(cudaMallocHost((void**)&h_active, 8 * sizeof(uint32_t)), "cudaMallocHost");
   CK(cudaEventCreateWithFlags(&ev_lag, cudaEventDisableTiming), "cudaEventCreate");
   lag_poll = env_int("LUTLDPC_LAG_POLL", 1) != 0;
+  tail_lag_frames = env_int("LUTLDPC_TAIL_LAG", 1024);
   CK(cudaEventCreate(&ev0), "cudaEventCreate");
   CK(cudaEventCreate(&ev1), "cudaEventCreate");
   return LUTLDPC_OK;
@@ -423,17 +424,14 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     done = (dw >> (4 * (tr->frame & 7))) & 1;
     return 0;
   };
-  auto poll = [&](bool& all_done) -> int {
-    all_done = false;
-    if (poll_every <= 0) return 0;
-    CK(cudaMemcpyAsync(h_active, cur.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
-    CK(cudaStreamSynchronize(st), "poll sync");
-    all_done = h_active[0] == 0;
-    // the work lists only shrink, so their lengths at this poll bound every later launch
-    cur.host_cols = (int)h_active[2];
-    cur.host_grp4 = (int)h_active[3];
+  // counters of one finalize, as they arrive on the host: [0] unfinished frames, [2] live words, [3] live groups.
+  // They only ever shrink, so a copy that is one iteration old still bounds every later launch.
+  auto process_counts = [&](const uint32_t* hc, bool& all_done) -> int {
+    all_done = hc[0] == 0;
+    cur.host_cols = (int)hc[2];
+    cur.host_grp4 = (int)hc[3];
     // frame repacking: too many slots of the live words belong to frames that have already returned
-    const int n_live = (int)h_active[0];
+    const int n_live = (int)hc[0];
     n_live_known = n_live;
     const int dense_cols = (n_live + 7) / 8;
     if (repack_on && !tr && n_live > 0 && (double)n_live < repack_alpha * 8.0 * cur.host_cols &&
@@ -444,8 +442,16 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
     }
     return 0;
   };
+  auto poll = [&](bool& all_done) -> int {  // waiting poll: exact counts, the stream drains
+    all_done = false;
+    if (poll_every <= 0) return 0;
+    CK(cudaMemcpyAsync(h_active, cur.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
+    CK(cudaStreamSynchronize(st), "poll sync");
+    return process_counts(h_active, all_done);
+  };
   bool all_done = false;
   bool lagging = lag_poll && !tr && poll_every == 1, lag_inflight = false;
+  const int tail_lag = lag_poll && !tr && poll_every == 1 ? tail_lag_frames : -1;
   if (tr) tr->live = true;
   if (pisc) {  // :277
     CK(launch_syndrome(g, cur, st), "syndrome"); launched(KIND_SYNDROME);
@@ -485,17 +491,26 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
         }
       }
       if (poll_every > 0 && ++polled % poll_every == 0) {
-        // While no frame of the batch has returned yet there is nothing to decide: the counters are copied
-        // without waiting and looked at one iteration later, so the stream never drains.  The first copy that
-        // shows a returned frame switches to the waiting poll (exact counts for grids, repacking, termination).
-        bool wait = !lagging;
-        if (lagging) {
+        // Lagged poll: the counters are copied without waiting and looked at one iteration later, so the stream
+        // never drains.  Used (a) while no frame of the batch has returned yet -- there is nothing to decide;
+        // the first copy that shows a returned frame switches to the waiting poll -- and (b) once few frames are
+        // left (tail_lag): those iterations are short, a drained stream would cost as much as the passes, and
+        // counts that are one iteration old still bound the grids and the repacked layout.
+        const bool tail = !lagging && n_live_known <= tail_lag;
+        bool wait = !lagging && !tail;
+        if (lagging || tail) {
           if (lag_inflight) {
             CK(cudaEventSynchronize(ev_lag), "poll sync");
             lag_inflight = false;
-            if (h_active[4] != (uint32_t)n_live_known) { lagging = false; wait = true; }
+            if (tail) {
+              if ((rc = process_counts(h_active + 4, all_done))) return rc;
+              if (all_done) break;
+            } else if (h_active[4] != (uint32_t)n_live_known) {
+              lagging = false;
+              wait = true;
+            }
           }
-          if (lagging) {
+          if (!wait) {
             CK(cudaMemcpyAsync(h_active + 4, cur.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
             CK(cudaEventRecord(ev_lag, st), "poll event");
             lag_inflight = true;

@@ -140,6 +140,7 @@ struct lutldpc_decoder {
   uint32_t* h_active = nullptr;  // pinned [8]: waiting poll | lagged poll
   cudaEvent_t ev_lag = nullptr;
   bool lag_poll = true;
+  int tail_lag_frames = 1024;  // lagged polls again once this few frames are unfinished
   // frame repacking: when fewer than repack_alpha of the slots in the live words hold an unfinished frame, the
   // unfinished frames are gathered into a narrower layout (LUTLDPC_REPACK=0 switches it off)
   lutldpc::RepackCtx rctx[2];
