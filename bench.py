@@ -141,24 +141,33 @@ def run_b200(args):
     def step_device():
         dec.decode_quantized_device(F, cha.data_ptr(), msg.data_ptr(), out.data_ptr(), its.data_ptr())
 
-    # ---- device-resident timing (value)
+    # ---- device-resident timing (value): K steps, no per-launch events
     for _ in range(args.warmup):
         step_device()
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
-    dec.set_profiling(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches = 0
     barrier()
     e0.record(stream)
     for _ in range(args.steps):
         step_device()
-        launches += dec.last_call_stats()["kernel_launches"] + 1  # + unpack
     e1.record(stream)
     barrier()
-    ms = max_over_ranks(e0.elapsed_time(e1))
     clocks = sampler.summary()
+    launches = (dec.last_call_stats()["kernel_launches"] + 1) * args.steps  # + unpack; every step decodes the same batch
+    # ---- the same K steps again with a CUDA event after every launch: per-kernel times for the roofline
+    # (the events cost ~1 % of the step, so they stay out of the region `value` is taken from)
+    dec.set_profiling(True)
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    p1.record(stream)
+    torch.cuda.synchronize()
+    profiled_ms = p0.elapsed_time(p1)
+    ms = max_over_ranks(e0.elapsed_time(e1))
     prof = dec.get_profile()
     dec.set_profiling(False)
     it_host = its.cpu().numpy()
@@ -197,6 +206,7 @@ def run_b200(args):
                 "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms_per_launch": round(dom_ms / max(1, prof[dom][1]), 4),
                 "whole_step_algorithmic_gbs": round(step_gbs, 1), "whole_step_frac": round(step_gbs / peak, 4),
+                "profiled_pass_ms_per_step": round(profiled_ms / args.steps, 3),
                 "profile_ms": {k: round(v[0], 3) for k, v in prof.items()},
                 "kernel_share_of_step": {k: round(v[0] / sum(x[0] for x in prof.values()), 4) for k, v in prof.items()}}
 

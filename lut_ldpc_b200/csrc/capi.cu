@@ -234,7 +234,7 @@ static int host_chunk_frames(lutldpc_decoder* h, int n_frames) {
 
 // Chunk sizes of one host-buffer call.  Only the first copy in and the last copy out are exposed, and the
 // decoder runs closer to its batch efficiency on large chunks: long calls therefore start with a small chunk,
-// grow by <= 2.5x per chunk (the copy of chunk c+1 must fit under the decode of chunk c: ~2.4 us per frame over
+// grow by 2x per chunk (the copy of chunk c+1 must fit under the decode of chunk c: ~2.4 us per frame over
 // PCIe against >= 6 us per frame of decoding for N=64800), run chunks of twice the nominal size in the middle
 // and shrink again at the end.  Short calls keep the uniform nominal chunks.
 static std::vector<int> host_chunk_plan(lutldpc_decoder* h, int n_frames, bool single) {
@@ -247,10 +247,10 @@ static std::vector<int> host_chunk_plan(lutldpc_decoder* h, int n_frames, bool s
     if (v >= 1024) C = std::min(maxb / 2, v / 256 * 256);
   }
   auto r256 = [](long long v) { return (int)std::max<long long>(256, (v + 128) / 256 * 256); };
-  const int up[3] = {r256(C / 4), r256((long long)C * 5 / 8), r256((long long)C * 3 / 2)};
-  const int down[2] = {r256((long long)C * 5 / 4), r256((long long)C * 3 / 8)};
-  const long long ramps = (long long)up[0] + up[1] + up[2] + down[0] + down[1];
-  const bool ramped = !getenv("LUTLDPC_HOST_CHUNK") && n_frames >= ramps && up[2] <= maxb && 2 * C <= maxb;
+  const int up[2] = {r256(C / 2), C};
+  const int down[2] = {C, r256(C / 2)};
+  const long long ramps = (long long)up[0] + up[1] + down[0] + down[1];
+  const bool ramped = !getenv("LUTLDPC_HOST_CHUNK") && n_frames >= ramps && 2 * C <= maxb;
   if (!ramped) {
     for (int f = 0; f < n_frames; f += C) plan.push_back(std::min(C, n_frames - f));
     return plan;

@@ -910,7 +910,7 @@ __global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fuse
   int i = blockIdx.y * kNodeThreads + threadIdx.x;
   int node0 = tile.y, node1 = tile.y + tile.z;
   if (n_items <= 64) {  // narrow layout: the thread groups of the CTA share the nodes of the tile
-    const int tx_log2 = n_items <= 32 ? 5 : 6;
+    const int tx_log2 = n_items <= 8 ? 3 : (n_items <= 16 ? 4 : (n_items <= 32 ? 5 : 6));
     const int nsub = kNodeThreads >> tx_log2, sub = threadIdx.x >> tx_log2;
     const int per = (tile.z + nsub - 1) / nsub;
     i = threadIdx.x & ((1 << tx_log2) - 1);
@@ -1057,7 +1057,7 @@ cudaError_t launch_cn_exact(int dc, const int32_t* d_rows, int n_checks, const B
   static const int vec = env_int("LUTLDPC_CN_VEC", 2) == 4 ? 4 : 2;
   if (b.host_grp4 <= 0) return cudaSuccess;
   const int items = b.host_grp4 * (4 / vec);
-  const int tx_log2 = items <= 32 ? 5 : (items <= 64 ? 6 : 7);
+  const int tx_log2 = items <= 8 ? 3 : (items <= 16 ? 4 : (items <= 32 ? 5 : (items <= 64 ? 6 : 7)));
   dim3 grid(cdiv(n_checks, 128 >> tx_log2), cdiv(items, 1 << tx_log2));
 #define CN_X_ARGS d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail, b.grp4, b.n_active, n_checks, tx_log2
   switch (dc) {

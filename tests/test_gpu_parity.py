@@ -274,7 +274,7 @@ def test_host_path_is_chunked_and_pipelined_bit_exact(L, monkeypatch):
     assert np.array_equal(it2, whole_it) and np.array_equal(out2, whole_out)
     monkeypatch.delenv("LUTLDPC_HOST_CHUNK")
     # long calls ramp their chunk sizes (small first and last chunk, large ones in between): nominal 1024
-    # -> chunks 256, 640, 1536, [middle], 1280, 384 over 6000 frames (ragged), same results as chunk by chunk
+    # -> chunks 512, 1024, [middle], 1024, 512 over 6000 frames (ragged), same results as chunk by chunk
     big = np.tile(np.arange(n), 6)[:6000 - 7]
     monkeypatch.setenv("LUTLDPC_HOST_RAMP_NOMINAL", "1024")
     out3, it3 = dec.decode_quantized(cha[big], msg[big])

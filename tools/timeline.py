@@ -17,6 +17,12 @@ out = torch.empty((F, dec.nvar), dtype=torch.uint8, device="cuda"); its = torch.
 for _ in range(2):
     dec.decode_quantized_device(F, cha.data_ptr(), msg.data_ptr(), out.data_ptr(), its.data_ptr())
 torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(st)
+for _ in range(3):
+    dec.decode_quantized_device(F, cha.data_ptr(), msg.data_ptr(), out.data_ptr(), its.data_ptr())
+e1.record(st); torch.cuda.synchronize()
+print("unprofiled_step_ms", e0.elapsed_time(e1) / 3, file=sys.stderr)
 dec.set_profiling(True)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record(st)
