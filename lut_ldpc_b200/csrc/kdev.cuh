@@ -69,6 +69,15 @@ __device__ __forceinline__ void stage_to_smem(void* dst, const void* src, uint32
   stage_wait(bar);
 }
 
+// Programmatic dependent launch (launch_pdl in kernels.cu): a kernel of the decode loop lets its successor's CTAs
+// become resident as soon as all of its own have started (pdl_launch_dependents, first statement), and waits for
+// its predecessor's memory (pdl_wait) after its index arithmetic and constant-data reads.  The launch latency and
+// CTA ramp-up of one pass then overlap the drain of the previous one.  (Moving more of the prologue -- LUT staging,
+// row tables -- in front of the wait cost more in registers than it gained.)  Both are no-ops in a kernel
+// that was launched without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // OR `f` into a per-word flag that thousands of threads of the same pass target: look first (L2) and
 // only issue the atomic when it would set a new bit.  Flags only ever gain bits within a pass, so a
 // stale read can cost an extra atomic but never lose one.  Without this, the 32400 checks of the
@@ -86,6 +95,16 @@ template <> struct WordVec<1> { typedef uint32_t T; };
 template <> struct WordVec<2> { typedef uint2 T; };
 template <> struct WordVec<4> { typedef uint4 T; };
 
+// message accesses of the specialised VN pass: streaming (evict-first) like the check pass -- every line is
+// touched once per pass and the batch is far larger than L2
+#ifndef LUTLDPC_VN_PLAIN_MEM
+#define VN_LD(p) __ldcs(p)
+#define VN_ST(p, v) __stcs(p, v)
+#else
+#define VN_LD(p) (*(p))
+#define VN_ST(p, v) (*(p) = (v))
+#endif
+
 #define LUTLDPC_EXACT_DCS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16)
 #define LUTLDPC_FAST_DVS(X) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16) X(17) X(18) X(19) X(20)
 
@@ -99,7 +118,7 @@ struct FastStore {
                                              uint32_t& D) {
     if constexpr (II < DV) {
       const uint32_t r = v[fastvn::Static<DV>::P.out[II]];
-      msgs[off0 + (uint32_t)II * W] = r;
+      VN_ST(msgs + off0 + (uint32_t)II * W, r);
       if constexpr (II > 0) D |= r ^ r0;  // bits where an outgoing message differs from the first one
       FastStore<DV, II + 1>::run(v, msgs, off0, W, r0, D);
     }
@@ -125,7 +144,7 @@ __device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int2* __
   {
     const uint32_t off0 = (uint32_t)cur.y * uW + uw;
 #pragma unroll
-    for (int k = 0; k < DV; ++k) nxt[k] = msgs[off0 + (uint32_t)k * uW];
+    for (int k = 0; k < DV; ++k) nxt[k] = VN_LD(msgs + off0 + (uint32_t)k * uW);
     nxt[DV] = cha[(uint32_t)cur.x * uW + uw];
   }
   for (int i = i0; i < i1; ++i) {
@@ -138,7 +157,7 @@ __device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int2* __
     if (i + 1 < i1) {  // node i+1: its pair arrived during the previous iteration
       const uint32_t o1 = (uint32_t)cur.y * uW + uw;
 #pragma unroll
-      for (int k = 0; k < DV; ++k) nxt[k] = msgs[o1 + (uint32_t)k * uW];
+      for (int k = 0; k < DV; ++k) nxt[k] = VN_LD(msgs + o1 + (uint32_t)k * uW);
       nxt[DV] = cha[(uint32_t)cur.x * uW + uw];
       ahead = nodes[min(i + 2, i1 - 1)];
     }
@@ -165,7 +184,7 @@ struct FastStore2 {
     if constexpr (II < DV) {
       constexpr int kOut = fastvn::Static<DV>::P.out[II];
       const uint32_t ra = va[kOut], rb = vb[kOut];
-      *reinterpret_cast<uint2*>(msgs + off0 + (uint32_t)II * W) = make_uint2(ra, rb);
+      VN_ST(reinterpret_cast<uint2*>(msgs + off0 + (uint32_t)II * W), make_uint2(ra, rb));
       if constexpr (II > 0) {
         Da |= ra ^ ra0;
         Db |= rb ^ rb0;
@@ -195,7 +214,7 @@ __device__ __forceinline__ void vn_fast_body2(const uint8_t* tabs, const int2* _
   {
     const uint32_t off0 = (uint32_t)cur.y * uW + uw;
 #pragma unroll
-    for (int k = 0; k < DV; ++k) nxt[k] = *reinterpret_cast<const uint2*>(msgs + off0 + (uint32_t)k * uW);
+    for (int k = 0; k < DV; ++k) nxt[k] = VN_LD(reinterpret_cast<const uint2*>(msgs + off0 + (uint32_t)k * uW));
     nxt[DV] = *reinterpret_cast<const uint2*>(cha + (uint32_t)cur.x * uW + uw);
   }
   for (int i = i0; i < i1; ++i) {
@@ -211,7 +230,7 @@ __device__ __forceinline__ void vn_fast_body2(const uint8_t* tabs, const int2* _
     if (i + 1 < i1) {
       const uint32_t o1 = (uint32_t)cur.y * uW + uw;
 #pragma unroll
-      for (int k = 0; k < DV; ++k) nxt[k] = *reinterpret_cast<const uint2*>(msgs + o1 + (uint32_t)k * uW);
+      for (int k = 0; k < DV; ++k) nxt[k] = VN_LD(reinterpret_cast<const uint2*>(msgs + o1 + (uint32_t)k * uW));
       nxt[DV] = *reinterpret_cast<const uint2*>(cha + (uint32_t)cur.x * uW + uw);
       ahead = nodes[min(i + 2, i1 - 1)];
     }

@@ -231,8 +231,10 @@ __global__ void __launch_bounds__(128) k_cn_exact(const int32_t* __restrict__ ro
   typedef typename WordVec<VEC>::T V;
   // thread i of the pass owns VEC adjacent columns of live group grp4[i / (4 / VEC)]; a CTA covers
   // 2^tx_log2 such threads of 128 >> tx_log2 checks (narrow layouts: several checks per CTA)
+  pdl_launch_dependents();
   const int check = (blockIdx.x << (7 - tx_log2)) + (threadIdx.x >> tx_log2);
   const int i = (blockIdx.y << tx_log2) + (threadIdx.x & ((1 << tx_log2) - 1));
+  pdl_wait();
   if (check >= n_checks || i >= (int)n_lists[3] * (4 / VEC)) return;
   const int w = (int)grp4[i / (4 / VEC)] * 4 + (i % (4 / VEC)) * VEC;
   union U { V v; uint32_t u[VEC]; };
@@ -461,6 +463,8 @@ __global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int w0, 
                                                    int32_t* iters, uint32_t* n_active, int W_lists, uint32_t* cols,
                                                    uint32_t* grp4, uint32_t* n_lists) {
   __shared__ uint32_t red[32];
+  pdl_launch_dependents();
+  pdl_wait();
   uint32_t cnt = 0;
   for (int w = w0 + threadIdx.x; w < w1; w += blockDim.x) {
     uint32_t d = done[w], conv;
@@ -901,9 +905,11 @@ __global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fuse
                                                             const uint32_t* __restrict__ n_lists, int wide_max_dv) {
   __shared__ __align__(128) uint8_t tabs[(MAXDV - 1) * 128];
   __shared__ uint64_t bar;
+  pdl_launch_dependents();
   const int4 tile = tiles[blockIdx.x];  // x = class, y = first node, z = node count
   const FusedVnClass cls = P.c[tile.x];
   const bool wide = cls.dv <= wide_max_dv;
+  pdl_wait();
   const int n_items = wide ? 2 * (int)n_lists[3] : (int)n_lists[2];
   if ((int)(blockIdx.y * kNodeThreads) >= n_items) return;  // whole CTA beyond the live columns
   stage_to_smem(tabs, cls.tables, (uint32_t)(cls.dv - 1) * 128u, &bar);
@@ -995,6 +1001,27 @@ cudaError_t configure_kernels() {
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
+// Launch with programmatic stream serialization (kdev.cuh: pdl_wait / pdl_launch_dependents).  LUTLDPC_PDL=0
+// falls back to ordinary stream order.
+template <class... KArgs, class... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args) {
+  static const bool on = [] {
+    const char* e = getenv("LUTLDPC_PDL");
+    return !(e && e[0] == '0');
+  }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = on ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 cudaError_t launch_pack(const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, const GraphArrays& g,
                         const BatchBuffers& b, int Nq_cha, int Nq_msg, cudaStream_t st) {
   dim3 grid(cdiv(g.nvar, 32), cdiv(b.W, 32));
@@ -1060,18 +1087,19 @@ cudaError_t launch_cn_exact(int dc, const int32_t* d_rows, int n_checks, const B
   const int tx_log2 = items <= 8 ? 3 : (items <= 16 ? 4 : (items <= 32 ? 5 : (items <= 64 ? 6 : 7)));
   dim3 grid(cdiv(n_checks, 128 >> tx_log2), cdiv(items, 1 << tx_log2));
 #define CN_X_ARGS d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail, b.grp4, b.n_active, n_checks, tx_log2
+  cudaError_t le = cudaSuccess;
   switch (dc) {
 #define X(D)                                                              \
   case D:                                                                 \
-    if (vec == 2) k_cn_exact<D, 2><<<grid, 128, 0, st>>>(CN_X_ARGS);      \
-    else k_cn_exact<D, 4><<<grid, 128, 0, st>>>(CN_X_ARGS);               \
+    if (vec == 2) le = launch_pdl(k_cn_exact<D, 2>, grid, dim3(128), st, CN_X_ARGS);      \
+    else le = launch_pdl(k_cn_exact<D, 4>, grid, dim3(128), st, CN_X_ARGS);               \
     break;
     LUTLDPC_EXACT_DCS(X)
 #undef X
     default:
       return cudaErrorInvalidValue;
   }
-  return cudaGetLastError();
+  return le != cudaSuccess ? le : cudaGetLastError();
 }
 
 cudaError_t launch_node(NodeMode mode, const NodeLaunch& nl, const GraphArrays& g, const BatchBuffers& b,
@@ -1126,13 +1154,14 @@ cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_ti
   dim3 grid(n_tiles, cdiv(std::max(b.host_cols, wide >= 2 ? 2 * b.host_grp4 : 0), kNodeThreads));
 #define FUSED_ARGS P, d_tiles, g.vn_edge0, b.W, b.msgs, b.cha, b.hard, b.done, b.vn_fail, want_flags, b.cols, b.grp4, \
                    b.n_active, wide
-  if (max_dv <= 4) k_vn_fused<4><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
-  else if (max_dv <= 8) k_vn_fused<8><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
-  else if (max_dv <= 12) k_vn_fused<12><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
-  else if (max_dv <= 20) k_vn_fused<20><<<grid, kNodeThreads, 0, st>>>(FUSED_ARGS);
+  cudaError_t le;
+  if (max_dv <= 4) le = launch_pdl(k_vn_fused<4>, grid, dim3(kNodeThreads), st, FUSED_ARGS);
+  else if (max_dv <= 8) le = launch_pdl(k_vn_fused<8>, grid, dim3(kNodeThreads), st, FUSED_ARGS);
+  else if (max_dv <= 12) le = launch_pdl(k_vn_fused<12>, grid, dim3(kNodeThreads), st, FUSED_ARGS);
+  else if (max_dv <= 20) le = launch_pdl(k_vn_fused<20>, grid, dim3(kNodeThreads), st, FUSED_ARGS);
   else return cudaErrorInvalidValue;
 #undef FUSED_ARGS
-  return cudaGetLastError();
+  return le != cudaSuccess ? le : cudaGetLastError();
 }
 
 cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st) {
@@ -1149,9 +1178,9 @@ cudaError_t launch_finalize(FinalizeMode mode, int value, const BatchBuffers& b,
 cudaError_t launch_finalize_range(FinalizeMode mode, int value, const BatchBuffers& b, int w0, int w1,
                                   uint32_t* n_active, cudaStream_t st) {
   const int full = w0 == 0 && w1 == b.W;
-  k_finalize<<<1, 1024, 0, st>>>((int)mode, value, w0, w1, b.done, b.vn_fail, b.cn_fail, b.syn_fail, b.iters,
-                                 n_active, full ? b.W : 0, b.cols, b.grp4, b.n_active);
-  return cudaGetLastError();
+  cudaError_t le = launch_pdl(k_finalize, dim3(1), dim3(1024), st, (int)mode, value, w0, w1, b.done, b.vn_fail,
+                              b.cn_fail, b.syn_fail, b.iters, n_active, full ? b.W : 0, b.cols, b.grp4, b.n_active);
+  return le != cudaSuccess ? le : cudaGetLastError();
 }
 
 cudaError_t launch_repack(const GraphArrays& g, const BatchBuffers& from, const BatchBuffers& to, int32_t* d_src,
