@@ -25,7 +25,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 WORKLOADS = {
     # name -> (golden cfg, default snr dB, default frames per step per GPU, description)
-    "c5_n64800": ("c5_n64800", 1.3, 16384,
+    "c5_n64800": ("c5_n64800", 1.3, 32768,
                   "rate0.50_dv02-08_dc07-08_lut_q4_N64800, LUT q=4/4, max_iter 50, psc=pisc=1"),
     "c3_irr_n10000": ("c3_irr_n10000", 1.3, 32768, "rate0.50_dv02-17_dc08-09_lut_q4_N10000, LUT q=4/4, max_iter 50"),
     "c1b_reg36_n1000": ("c1b_reg36_n1000", 2.0, 65536, "rate0.50_dv03_dc06_N1000 (3,6), LUT q=4/4, max_iter 50"),
@@ -200,7 +200,11 @@ def run_b200(args):
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(dom)
+        tj = json.load(open(tpath))
+        # measured per launch with every frame of the profiled batch live: scale to this run's batch
+        traffic = tj.get(dom)
+        if traffic is not None and tj.get("frames_per_step"):
+            traffic = int(traffic * F / tj["frames_per_step"])
     step_gbs = sum_iters * b_iter * args.steps / (e0.elapsed_time(e1) * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,

@@ -1,5 +1,7 @@
 // C ABI (include/lutldpc.h) over the decoder object.  No torch types, no exceptions across the ABI.
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -330,8 +332,13 @@ static int decode_host(lutldpc_decoder* h, int n_frames, const uint8_t* cha, con
       CKH(launch_quantize(hp.llr[slot].p, cnt, h->d_qb_cha.p, (int)h->m.qb_Cha.size(), h->d_qb_msg.p,
                           (int)h->m.qb_Msg.size(), h->d_cha2msg.p, h->init_mode == LUTLDPC_INIT_QCHA,
                           hp.lab_cha[slot].p, hp.lab_msg[slot].p, st), "quantize");
+    static const bool trace_host = getenv("LUTLDPC_HOST_TRACE") != nullptr;
+    const auto t_a = std::chrono::steady_clock::now();
     rc = h->run_batch(nf, hp.lab_cha[slot].p, hp.lab_msg[slot].p, tr);
     if (rc) return rc;
+    if (trace_host)
+      fprintf(stderr, "host chunk %d frames %d run_batch %.3f ms\n", c, nf,
+              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_a).count());
     CKH(cudaEventRecord(hp.ev_used[slot], st), "event");
     if (c >= 2) CKH(cudaStreamWaitEvent(st, hp.ev_out[slot], 0), "wait");  // results of chunk c-2 have left
     CKH(launch_unpack(h->g, h->b, hp.out[slot].p, st), "unpack");
