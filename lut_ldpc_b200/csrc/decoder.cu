@@ -264,7 +264,9 @@ int lutldpc_decoder::init_device() {
     if (r.bytes + (size_t)r.n_slots * kNodeThreads * 4 > 200 * 1024)
       return fail(LUTLDPC_ERR_MODEL, "a node program (LUTs + value slots) exceeds the 200 KiB shared-memory budget");
   CK(d_prog_blob.upload(blob), "upload node programs");
-  CK(cudaMallocHost((void**)&h_active, 8 * sizeof(uint32_t)), "cudaMallocHost");
+  CK(cudaHostAlloc((void**)&h_active, 8 * sizeof(uint32_t), cudaHostAllocMapped), "cudaHostAlloc");
+  memset(h_active, 0, 8 * sizeof(uint32_t));
+  CK(cudaHostGetDevicePointer((void**)&d_active_mirror, h_active, 0), "cudaHostGetDevicePointer");
   CK(cudaEventCreateWithFlags(&ev_lag, cudaEventDisableTiming), "cudaEventCreate");
   lag_poll = env_int("LUTLDPC_LAG_POLL", 1) != 0;
   tail_lag_frames = env_int("LUTLDPC_TAIL_LAG", 1024);
@@ -331,6 +333,7 @@ int lutldpc_decoder::ensure_batch(int n_frames) {
   b.iters = buf_iters.p;
   b.cols = buf_cols.p; b.grp4 = buf_cols.p + W;
   b.host_cols = W; b.host_grp4 = W / 4;  // upper bounds until the first poll
+  b.mirror = d_active_mirror;
   b.W = W; b.F = n_frames;
   return LUTLDPC_OK;
 }
@@ -363,7 +366,7 @@ int lutldpc_decoder::repack_into(BatchBuffers& cur, int slot, int n_live) {
   n.msgs = c.msgs.p; n.cha = c.cha.p; n.hard = c.hard.p;
   n.done = c.flags.p; n.vn_fail = c.flags.p + W; n.cn_fail = c.flags.p + 2 * W; n.syn_fail = c.flags.p + 3 * W;
   n.n_active = c.flags.p + 4 * W;
-  n.iters = c.iters.p; n.fid = c.fid.p;
+  n.iters = c.iters.p; n.fid = c.fid.p; n.mirror = d_active_mirror;
   n.cols = c.cols.p; n.grp4 = c.cols.p + W;
   n.host_cols = (n_live + 7) / 8; n.host_grp4 = (n.host_cols + 3) / 4;
   n.W = W; n.F = n_live;
@@ -449,12 +452,14 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   auto poll = [&](bool& all_done) -> int {  // waiting poll: exact counts, the stream drains
     all_done = false;
     if (poll_every <= 0) return 0;
-    CK(cudaMemcpyAsync(h_active, cur.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
+    // the finalize kernel wrote the counters into host-mapped memory: no copy (a D2H memcpy on this stream would
+    // queue behind the result transfer of the previous chunk on the copy engine and stall the whole schedule)
     CK(cudaStreamSynchronize(st), "poll sync");
     return process_counts(h_active, all_done);
   };
   bool all_done = false;
   bool lagging = lag_poll && !tr && poll_every == 1, lag_inflight = false;
+  bool lag_skip = false;
   const int tail_lag = lag_poll && !tr && poll_every == 1 ? tail_lag_frames : -1;
   if (tr) tr->live = true;
   if (pisc) {  // :277
@@ -507,16 +512,21 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
             CK(cudaEventSynchronize(ev_lag), "poll sync");
             lag_inflight = false;
             if (tail) {
-              if ((rc = process_counts(h_active + 4, all_done))) return rc;
-              if (all_done) break;
-            } else if (h_active[4] != (uint32_t)n_live_known) {
+              // the mirror may still hold the counts of the layout that was just left: skip one reading after a repack
+              if (lag_skip) lag_skip = false;
+              else {
+                const int64_t r0 = repacks;
+                if ((rc = process_counts(h_active, all_done))) return rc;
+                if (all_done) break;
+                lag_skip = repacks != r0;
+              }
+            } else if (h_active[0] != (uint32_t)n_live_known) {
               lagging = false;
               wait = true;
             }
           }
           if (!wait) {
-            CK(cudaMemcpyAsync(h_active + 4, cur.n_active, 16, cudaMemcpyDeviceToHost, st), "poll copy");
-            CK(cudaEventRecord(ev_lag, st), "poll event");
+            CK(cudaEventRecord(ev_lag, st), "poll event");  // the counters arrive through the mapped mirror
             lag_inflight = true;
           }
         }

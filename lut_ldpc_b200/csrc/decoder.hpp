@@ -137,7 +137,8 @@ struct lutldpc_decoder {
   lutldpc::DevBuf<uint8_t> buf_cw;                 // transmitted codeword bits, [nvar][W] like hard
   lutldpc::DevBuf<uint32_t> buf_ferr;              // per-word frame-error flags (byte form)
   lutldpc::DevBuf<unsigned long long> buf_cnt;     // device image of lutldpc_sim_counters
-  uint32_t* h_active = nullptr;  // pinned [8]: waiting poll | lagged poll
+  uint32_t* h_active = nullptr;  // host-mapped pinned [8]: counters written by the finalize kernel
+  uint32_t* d_active_mirror = nullptr;  // device view of h_active
   cudaEvent_t ev_lag = nullptr;
   bool lag_poll = true;
   int tail_lag_frames = 1024;  // lagged polls again once this few frames are unfinished

@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(1024) k_build_lists(int W, const uint32_t* don
 __global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int w0, int w1, uint32_t* done,
                                                    uint32_t* vn_fail, uint32_t* cn_fail, uint32_t* syn_fail,
                                                    int32_t* iters, uint32_t* n_active, int W_lists, uint32_t* cols,
-                                                   uint32_t* grp4, uint32_t* n_lists) {
+                                                   uint32_t* grp4, uint32_t* n_lists, uint32_t* mirror) {
   __shared__ uint32_t red[32];
   pdl_launch_dependents();
   pdl_wait();
@@ -499,6 +499,11 @@ __global__ void __launch_bounds__(1024) k_finalize(int mode, int value, int w0, 
   if (W_lists > 0) {
     __syncthreads();  // done[] of this CTA's writes is visible to the CTA
     build_lists(W_lists, done, cols, grp4, n_lists);
+    if (mirror && threadIdx.x == 0) {  // build_lists ends with a barrier after thread 0 wrote the counts
+      mirror[0] = n_lists[0];
+      mirror[2] = n_lists[2];
+      mirror[3] = n_lists[3];
+    }
   }
 }
 
@@ -1179,7 +1184,8 @@ cudaError_t launch_finalize_range(FinalizeMode mode, int value, const BatchBuffe
                                   uint32_t* n_active, cudaStream_t st) {
   const int full = w0 == 0 && w1 == b.W;
   cudaError_t le = launch_pdl(k_finalize, dim3(1), dim3(1024), st, (int)mode, value, w0, w1, b.done, b.vn_fail,
-                              b.cn_fail, b.syn_fail, b.iters, n_active, full ? b.W : 0, b.cols, b.grp4, b.n_active);
+                              b.cn_fail, b.syn_fail, b.iters, n_active, full ? b.W : 0, b.cols, b.grp4, b.n_active,
+                              full ? b.mirror : (uint32_t*)nullptr);
   return le != cudaSuccess ? le : cudaGetLastError();
 }
 

@@ -31,6 +31,8 @@ struct BatchBuffers {
   uint32_t* cols = nullptr;      // [W]
   uint32_t* grp4 = nullptr;      // [W/4]
   int host_cols = 0, host_grp4 = 0;  // host-side upper bounds of the list lengths (grid sizing)
+  uint32_t* mirror = nullptr;    // host-mapped copy of n_active[0..3], written by every whole-batch finalize (polls
+                                 // read it without a copy: a D2H memcpy would queue behind the result transfers)
   int32_t* fid = nullptr;        // repacked layouts: original frame index of every slot (-1 padding); nullptr = identity
   int W = 0;                     // words per row
   int F = 0;                     // real frames (<= 8W)
