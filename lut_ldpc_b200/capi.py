@@ -18,7 +18,8 @@ class LutLdpcError(RuntimeError):
 
 
 def library_path():
-    return os.path.join(HERE, "liblutldpc_b200.so")
+    # LUTLDPC_LIB: another build of the same library (kernel tuning experiments)
+    return os.environ.get("LUTLDPC_LIB") or os.path.join(HERE, "liblutldpc_b200.so")
 
 
 def build_library(verbose=False):

@@ -169,7 +169,9 @@ __device__ __forceinline__ void vn_fast_body(const uint8_t* tabs, const int2* __
       failacc |= D >> so;  // sign position of the outputs; the caller masks with kNibOnes
       uint8_t* hp = hard + offn;
       const uint32_t nb = nib_bits_to_byte(r0, so);
-      *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
+      // frozen bits of frames that have returned are kept; with none in the word (the common case) no read
+      if (done_byte) *hp = (uint8_t)((*hp & done_byte) | (nb & ~done_byte));
+      else *hp = (uint8_t)nb;
     }
   }
 }
@@ -245,7 +247,8 @@ __device__ __forceinline__ void vn_fast_body2(const uint8_t* tabs, const int2* _
       fail1 |= Db >> so;
       uint16_t* hp = reinterpret_cast<uint16_t*>(hard + offn);
       const uint32_t nb = nib_bits_to_byte(ra0, so) | (nib_bits_to_byte(rb0, so) << 8);
-      *hp = (uint16_t)((*hp & done_bytes) | (nb & ~done_bytes));
+      if (done_bytes) *hp = (uint16_t)((*hp & done_bytes) | (nb & ~done_bytes));
+      else *hp = (uint16_t)nb;
     }
   }
 }

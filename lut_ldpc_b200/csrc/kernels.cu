@@ -889,18 +889,27 @@ static const fastvn::Prog* fast_prog(int dv) {
 // (dv 2, 3) and CTAs that are bound by shared-memory look-ups (dv 8 ...) are resident on an SM together.
 // Degrees up to kVnWideMaxDv run two word columns per thread (vn_fast_body2): thread i owns the column pair
 // (i & 1) of live group grp4[i >> 1].
-constexpr int kVnWideMaxDv = 3;
+#ifndef VN_MIN_BLOCKS
+#define VN_MIN_BLOCKS 8  // resident CTAs per SM the fused VN kernel is compiled for: 64 registers.  Measured on
+                        // N=64800, 16384 frames per step: 12 (40 registers, 32 bytes of spills) 88.8 ms, 10 (48) 87.1,
+                        // 8 (64) 86.2, 6 (80) 86.4, 5 (94) 87.1
+#endif
+constexpr int kVnWideMaxDv = 3;       // default: degrees that run two columns per thread
+#ifndef VN_WIDE_COMPILED
+#define VN_WIDE_COMPILED 3
+#endif
+constexpr int kVnWideCompiled = VN_WIDE_COMPILED;  // degrees the two-column body is compiled for
 static int vn_wide_max_dv() {
   static const int v = [] {
     const char* e = getenv("LUTLDPC_VN_WIDE_MAXDV");
     int x = e ? atoi(e) : kVnWideMaxDv;
-    return x < 0 ? 0 : (x > kVnWideMaxDv ? kVnWideMaxDv : x);
+    return x < 0 ? 0 : (x > kVnWideCompiled ? kVnWideCompiled : x);
   }();
   return v;
 }
 
 template <int MAXDV>
-__global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fused(FusedVnParams P, const int4* __restrict__ tiles,
+__global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? VN_MIN_BLOCKS : 0)) k_vn_fused(FusedVnParams P, const int4* __restrict__ tiles,
                                                             const int32_t* __restrict__ vn_edge0, int W,
                                                             uint32_t* __restrict__ msgs, const uint32_t* __restrict__ cha,
                                                             uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
@@ -936,15 +945,14 @@ __global__ void __launch_bounds__(kNodeThreads, (MAXDV <= 8 ? 12 : 0)) k_vn_fuse
     const uint32_t done_bytes = nib_bits_to_byte(dn.x, 0) | (nib_bits_to_byte(dn.y, 0) << 8);
     uint32_t f0 = 0, f1 = 0;
     switch (cls.dv) {
-      case 2:
-        vn_fast_body2<2>(tabs, cls.nodes, node0, node1, W, w, msgs, cha, hard, done_bytes, want_flags,
-                         cls.q_out, f0, f1);
-        break;
-      case 3:
-        if constexpr (MAXDV >= 3)
-          vn_fast_body2<3>(tabs, cls.nodes, node0, node1, W, w, msgs, cha, hard, done_bytes, want_flags,
-                           cls.q_out, f0, f1);
-        break;
+#define X(D)                                                                                                     \
+  case D:                                                                                                        \
+    if constexpr (D <= MAXDV && D <= kVnWideCompiled)                                                            \
+      vn_fast_body2<D>(tabs, cls.nodes, node0, node1, W, w, msgs, cha, hard, done_bytes, want_flags, cls.q_out,  \
+                       f0, f1);                                                                                  \
+    break;
+      LUTLDPC_FAST_DVS(X)
+#undef X
     }
     if (want_flags) {
       flag_or(&vn_fail[w], f0 & kNibOnes);
