@@ -181,7 +181,7 @@ int lutldpc_last_call_stats(const lutldpc_decoder* h, double* device_ms, int64_t
 
 /* ---- frame repacking (no counterpart in the reference, which decodes one frame at a time).  A frame that
  * has returned keeps occupying its slot of the frame-interleaved batch; when fewer than `alpha` (0..1, default
- * 0.8) of the slots in the words that still hold an unfinished frame are in use, the unfinished frames are
+ * 0.7) of the slots in the words that still hold an unfinished frame are in use, the unfinished frames are
  * gathered into a narrower layout and the remaining iterations run there.  Results are identical with
  * repacking on or off (frames are independent); it needs the per-iteration poll (lutldpc_set_poll_interval
  * >= 1).  on = 0 switches it off.  lutldpc_get_repack_count: repacks done by the handle so far. */

@@ -166,7 +166,7 @@ class Decoder:
     def set_poll_interval(self, every):
         self._ck(self._L.lutldpc_set_poll_interval(self._h, int(every)))
 
-    def set_repack(self, on, alpha=0.8):
+    def set_repack(self, on, alpha=0.7):
         """Frame repacking (gather of the unfinished frames into a narrower layout); results do not depend on it."""
         self._ck(self._L.lutldpc_set_repack(self._h, int(bool(on)), float(alpha)))
 

@@ -148,7 +148,7 @@ struct lutldpc_decoder {
   lutldpc::DevBuf<int32_t> buf_rsrc, buf_ow_first;
   lutldpc::DevBuf<uint8_t> buf_ow_mask;
   bool repack_on = true;
-  double repack_alpha = 0.8;
+  double repack_alpha = 0.7;
   int64_t repacks = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool have_stats = false;

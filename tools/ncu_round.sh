@@ -7,6 +7,6 @@ $B > gpurun_out/ncu_plain.json 2> gpurun_out/ncu_plain.err && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches.csv $B > gpurun_out/launch_ncu.log 2>&1
 echo launches rc=$?
 $B > gpurun_out/ncu_plain2.json 2> gpurun_out/ncu_plain2.err && \
-ncu --set full --clock-control none --import-source on -k regex:"k_vn_fused|k_cn_exact<[78]" -s 60 -c 3 -o gpurun_out/prof_top $B > gpurun_out/full_ncu.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"k_vn_fused|k_cn_exact" -s 120 -c 4 -o gpurun_out/prof_top $B > gpurun_out/full_ncu.log 2>&1
 echo full rc=$?
 tail -2 gpurun_out/full_ncu.log
