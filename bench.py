@@ -378,6 +378,12 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--ref-seconds-per-step", type=float, default=6.0)
     args = ap.parse_args()
+    # ONE JSON line on stdout: libraries that write to file descriptor 1 themselves (NCCL prints its version banner
+    # there) are sent to stderr; the line goes to the saved descriptor.
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(saved, "w")
     if args.impl == "reference":
         run_reference(args)
     else:
