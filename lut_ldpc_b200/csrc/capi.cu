@@ -227,9 +227,9 @@ static int host_chunk_frames(lutldpc_decoder* h, int n_frames) {
     int v = atoi(e);
     if (v > 0) return std::min(maxb, std::max(256, (v + 255) / 256 * 256));
   }
-  // ~256 MB of labels per chunk: large enough for the kernels to run at batch efficiency (N=64800: 4096 frames),
+  // ~384 MB of labels per chunk: large enough for the kernels to run at batch efficiency (N=64800: 6144 frames),
   // small enough that the first copy in and the last copy out -- the only ones not hidden -- stay short
-  int c = (int)std::min<long long>(maxb, ((1LL << 28) / std::max(1, h->m.nvar) + 512) / 1024 * 1024);
+  int c = (int)std::min<long long>(maxb, ((3LL << 27) / std::max(1, h->m.nvar) + 512) / 1024 * 1024);
   (void)n_frames;
   return std::min(maxb, std::max(2048, c));
 }
