@@ -796,6 +796,7 @@ __global__ void __launch_bounds__(128) k_retire_hard(int nvar, int W0, int W_c, 
 }
 
 // hard[nvar][W] -> out_bits[F][nvar]
+template <bool VEC4>
 __global__ void __launch_bounds__(256) k_unpack(const uint8_t* __restrict__ hard, int nvar, int F, int W,
                                                 uint8_t* __restrict__ out) {
   __shared__ uint8_t t[32][36];
@@ -806,9 +807,24 @@ __global__ void __launch_bounds__(256) k_unpack(const uint8_t* __restrict__ hard
     t[vi][tx] = (v < nvar && w < W) ? hard[(size_t)v * W + w] : 0;
   }
   __syncthreads();
-  for (int i = 0; i < 32; ++i) {
-    int fl = ty + 8 * i, f = f0 + fl, v = v0 + tx;
-    if (f < F && v < nvar) out[(size_t)f * nvar + v] = (t[tx][fl >> 3] >> (fl & 7)) & 1;
+  if (VEC4) {  // nvar % 4 == 0 and a 4-byte aligned output: four nodes per store
+    const int q4 = threadIdx.x & 7, fr = threadIdx.x >> 3;
+    const int v = v0 + 4 * q4;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int fl = fr + 32 * i, f = f0 + fl;
+      if (f < F && v < nvar) {
+        uint32_t x = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) x |= (uint32_t)((t[4 * q4 + k][fl >> 3] >> (fl & 7)) & 1) << (8 * k);
+        *reinterpret_cast<uint32_t*>(out + (size_t)f * nvar + v) = x;
+      }
+    }
+  } else {
+    for (int i = 0; i < 32; ++i) {
+      int fl = ty + 8 * i, f = f0 + fl, v = v0 + tx;
+      if (f < F && v < nvar) out[(size_t)f * nvar + v] = (t[tx][fl >> 3] >> (fl & 7)) & 1;
+    }
   }
 }
 
@@ -1232,7 +1248,8 @@ cudaError_t launch_retire(const GraphArrays& g, const BatchBuffers& from, const 
 
 cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_bits, cudaStream_t st) {
   dim3 grid(cdiv(g.nvar, 32), cdiv(b.W, 32));
-  k_unpack<<<grid, 256, 0, st>>>(b.hard, g.nvar, b.F, b.W, d_out_bits);
+  if (g.nvar % 4 == 0 && (uintptr_t)d_out_bits % 4 == 0) k_unpack<true><<<grid, 256, 0, st>>>(b.hard, g.nvar, b.F, b.W, d_out_bits);
+  else k_unpack<false><<<grid, 256, 0, st>>>(b.hard, g.nvar, b.F, b.W, d_out_bits);
   return cudaGetLastError();
 }
 
