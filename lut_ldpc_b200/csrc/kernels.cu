@@ -406,6 +406,32 @@ __global__ void __launch_bounds__(128) k_syndrome(const int32_t* __restrict__ cn
   if (x) flag_or(&syn_fail[w], byte_to_nib_bits(x));
 }
 
+// four word columns per thread (one 4-byte read per variable node of the check): thread i owns live group grp4[i]
+__global__ void __launch_bounds__(128) k_syndrome4(const int32_t* __restrict__ cn_start,
+                                                   const int32_t* __restrict__ chk_equ_idx, int W,
+                                                   const uint8_t* __restrict__ hard, const uint32_t* __restrict__ done,
+                                                   uint32_t* __restrict__ syn_fail, const uint32_t* __restrict__ grp4,
+                                                   const uint32_t* __restrict__ n_lists, int nchk,
+                                                   int checks_per_cta) {
+  const int gi = blockIdx.y * blockDim.x + threadIdx.x;
+  if (gi >= (int)n_lists[3]) return;
+  const int w = (int)grp4[gi] * 4;
+  uint32_t acc = 0;  // OR over the checks of this CTA: a frame fails if any check fails
+  const int c1 = min(nchk, (int)(blockIdx.x + 1) * checks_per_cta);
+  for (int c = blockIdx.x * checks_per_cta; c < c1; ++c) {
+    const int s = cn_start[c], e = cn_start[c + 1];
+    uint32_t x = 0;
+    for (int k = s; k < e; ++k) x ^= *reinterpret_cast<const uint32_t*>(hard + (size_t)chk_equ_idx[k] * W + w);
+    acc |= x;
+  }
+  if (!acc) return;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t b = (acc >> (8 * j)) & 0xFFu;
+    if (b && done[w + j] != kNibOnes) flag_or(&syn_fail[w + j], byte_to_nib_bits(b));
+  }
+}
+
 // Single-CTA (1024 threads) order-preserving compaction of the live columns: cols = words with an
 // unfinished frame, grp4 = groups of 4 adjacent words with any such word; counts to n_active[2], [3].
 __device__ void build_lists(int W, const uint32_t* done, uint32_t* cols, uint32_t* grp4, uint32_t* n_active) {
@@ -1195,6 +1221,13 @@ cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_ti
 
 cudaError_t launch_syndrome(const GraphArrays& g, const BatchBuffers& b, cudaStream_t st) {
   if (b.host_cols <= 0) return cudaSuccess;
+  if (b.host_grp4 >= 32) {  // wide layouts: 4 columns per thread
+    const int per = 8;  // checks per CTA
+    dim3 grid4(cdiv(g.nchk, per), cdiv(b.host_grp4, 128));
+    k_syndrome4<<<grid4, 128, 0, st>>>(g.cn_start, g.chk_equ_idx, b.W, b.hard, b.done, b.syn_fail, b.grp4, b.n_active,
+                                       g.nchk, per);
+    return cudaGetLastError();
+  }
   dim3 grid(g.nchk, cdiv(b.host_cols, 128));
   k_syndrome<<<grid, 128, 0, st>>>(g.cn_start, g.chk_equ_idx, b.W, b.hard, b.done, b.syn_fail, b.cols, b.n_active);
   return cudaGetLastError();
