@@ -227,15 +227,17 @@ __global__ void __launch_bounds__(128) k_cn_exact(const int32_t* __restrict__ ro
                                                   uint32_t* __restrict__ msgs, const uint32_t* __restrict__ done,
                                                   uint32_t* __restrict__ cn_fail, int want_fail,
                                                   const uint32_t* __restrict__ grp4,
-                                                  const uint32_t* __restrict__ n_lists, int n_checks, int tx_log2) {
+                                                  const uint32_t* __restrict__ n_lists, int n_checks, int tx_log2,
+                                                  int per) {
   typedef typename WordVec<VEC>::T V;
   // thread i of the pass owns VEC adjacent columns of live group grp4[i / (4 / VEC)]; a CTA covers
   // 2^tx_log2 such threads of 128 >> tx_log2 checks (narrow layouts: several checks per CTA)
   pdl_launch_dependents();
-  const int check = (blockIdx.x << (7 - tx_log2)) + (threadIdx.x >> tx_log2);
+  // `per` checks in sequence per thread: fewer, longer-lived CTAs
+  const int check0 = ((blockIdx.x * per) << (7 - tx_log2)) + (threadIdx.x >> tx_log2);
   const int i = (blockIdx.y << tx_log2) + (threadIdx.x & ((1 << tx_log2) - 1));
   pdl_wait();
-  if (check >= n_checks || i >= (int)n_lists[3] * (4 / VEC)) return;
+  if (i >= (int)n_lists[3] * (4 / VEC)) return;
   const int w = (int)grp4[i / (4 / VEC)] * 4 + (i % (4 / VEC)) * VEC;
   union U { V v; uint32_t u[VEC]; };
   U dn;
@@ -245,6 +247,12 @@ __global__ void __launch_bounds__(128) k_cn_exact(const int32_t* __restrict__ ro
   for (int j = 0; j < VEC; ++j) all_done &= dn.u[j] == kNibOnes;
   if (all_done) return;
   const QMask qm = make_qmask(q);
+  uint32_t failacc[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) failacc[j] = 0;
+  for (int cc = 0; cc < per; ++cc) {
+  const int check = check0 + (cc << (7 - tx_log2));
+  if (check >= n_checks) break;
   const int32_t* r = rows + (size_t)check * DC;
   uint32_t* p[DC];
 #pragma unroll
@@ -267,9 +275,12 @@ __global__ void __launch_bounds__(128) k_cn_exact(const int32_t* __restrict__ ro
     for (int j = 0; j < VEC; ++j) o.u[j] = cng_emit(a[j], x[k].u[j], qm);
     __stcs(reinterpret_cast<V*>(p[k]), o.v);
   }
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) failacc[j] |= a[j].par;
+  }
   if (want_fail) {
 #pragma unroll
-    for (int j = 0; j < VEC; ++j) flag_or(&cn_fail[w + j], (a[j].par >> qm.s) & kNibOnes);
+    for (int j = 0; j < VEC; ++j) flag_or(&cn_fail[w + j], (failacc[j] >> qm.s) & kNibOnes);
   }
 }
 
@@ -1140,8 +1151,13 @@ cudaError_t launch_cn_exact(int dc, const int32_t* d_rows, int n_checks, const B
   if (b.host_grp4 <= 0) return cudaSuccess;
   const int items = b.host_grp4 * (4 / vec);
   const int tx_log2 = items <= 8 ? 3 : (items <= 16 ? 4 : (items <= 32 ? 5 : (items <= 64 ? 6 : 7)));
-  dim3 grid(cdiv(n_checks, 128 >> tx_log2), cdiv(items, 1 << tx_log2));
-#define CN_X_ARGS d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail, b.grp4, b.n_active, n_checks, tx_log2
+  // checks per thread in sequence.  One check per CTA column block means hundreds of thousands of CTAs that live
+  // for a few microseconds; measured on N=64800, 16384 frames: 1 -> 0.705 ms per check pass, 2 -> 0.658, 4 -> 0.642
+  // (0.94 of the measured HBM peak), 8 -> 0.640, 16 -> 0.650.  Narrow layouts keep 1 (their CTAs already share checks).
+  static const int per_env = env_int("LUTLDPC_CN_PER", 4);
+  const int per = items >= 128 ? (per_env < 1 ? 1 : per_env) : 1;
+  dim3 grid(cdiv(n_checks, (128 >> tx_log2) * per), cdiv(items, 1 << tx_log2));
+#define CN_X_ARGS d_rows, b.W, q, b.msgs, b.done, b.cn_fail, want_fail, b.grp4, b.n_active, n_checks, tx_log2, per
   cudaError_t le = cudaSuccess;
   switch (dc) {
 #define X(D)                                                              \
