@@ -189,12 +189,7 @@ def run_b200(args):
     # the fused launch runs every specialised class: all their nodes in one kernel
     per_frame_iter["vn_fused"] = sum(v for k, v in per_frame_iter.items() if k.startswith("vn_dv"))
     units = {"cn_minsum": sum_iters}
-    if dom == "stagger_step":
-        # one launch = check pass of one half of the batch + variable pass of the other half: over a step
-        # the launches carry every check pass (E bytes per frame-iteration) and every variable pass
-        alg = (float(E) * sum_iters + per_frame_iter["vn_fused"] * vn_passes) * args.steps
-    else:
-        alg = per_frame_iter.get(dom, 0.0) * units.get(dom, vn_passes) * args.steps
+    alg = per_frame_iter.get(dom, 0.0) * units.get(dom, vn_passes) * args.steps
     dom_ms = prof[dom][0]
     achieved = alg / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     traffic = None

@@ -67,8 +67,7 @@ typedef struct lutldpc_info {
   double rate;
   int32_t n_var_programs;       /* (iteration slot, degree class) programs of the VN pass */
   int32_t n_fast_var_programs;  /* ... of which run on the compile-time specialised kernel (vn_fast.cuh) */
-  int32_t staggered_schedule;   /* 1: batches of >= 2048 frames run as two halves half an iteration apart, the
-                                 * check pass of one half and the variable pass of the other in one launch */
+  int32_t reserved0_;           /* always 0 (was: staggered schedule, removed) */
   int32_t reserved_;
 } lutldpc_info;
 
@@ -166,8 +165,7 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
 /* ---- per-kernel device times.  With profiling on, an event is recorded after every kernel launch
  * of the handle; lutldpc_get_profile returns, per kind, the summed device milliseconds and launch
  * counts since profiling was switched on.  Kinds: 0 reset, 1 pack, 2 channel, 3 min-sum check pass,
- * 4 syndrome, 5 finalize, 6 unpack, 7 count, 8 encode, 9 staggered launch (check pass of one half of the
- * batch + variable pass of the other), 10 frame repack, 11 retire (results of repacked frames back), 16+c variable-node pass of degree class c,
+ * 4 syndrome, 5 finalize, 6 unpack, 7 count, 8 encode, 9 unused, 10 frame repack, 11 retire (results of repacked frames back), 16+c variable-node pass of degree class c,
  * 32+c decision pass, 48+c LUT check pass.  class_degree/class_nodes [16] describe the VN classes. */
 #define LUTLDPC_PROFILE_KINDS 64
 int lutldpc_set_profiling(lutldpc_decoder* h, int on);

@@ -2,7 +2,7 @@
 
 The product is the C-ABI library liblutldpc_b200.so (include/lutldpc.h, sources in csrc/); this
 package is the thin Python binding the tests and bench.py use, plus the host-side mirror of the
-reference's LDPC_Code_LUT / LDPC_BER_Sim_LUT interface (code_lut.py, ber_sim.py).  There is no CPU
+reference's LDPC_BER_Sim_LUT harness (ber_sim.py; the C++ mirror of LDPC_Code_LUT is host/ldpc_code_lut.hpp).  There is no CPU
 fallback: importing works anywhere, creating a decoder needs the built library and a CUDA device.
 """
 from .capi import (Decoder, LutLdpcError, SimCounters, INIT_CONT, INIT_QCHA, TRACE_INIT, TRACE_CN,  # noqa: F401

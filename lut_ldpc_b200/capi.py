@@ -33,7 +33,7 @@ class _Info(C.Structure):
                                          "min_lut", "has_gen", "n_degree_classes")] + \
                [("lookups_per_frame_iter", C.c_int64), ("lookups_per_frame_iter_naive", C.c_int64), ("rate", C.c_double),
                 ("n_var_programs", C.c_int32), ("n_fast_var_programs", C.c_int32),
-                ("staggered_schedule", C.c_int32), ("reserved_", C.c_int32)]
+                ("reserved0_", C.c_int32), ("reserved_", C.c_int32)]
 
 
 class _SimParams(C.Structure):
@@ -76,7 +76,7 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_set_repack", "lutldpc_get_repack_count"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
-                 7: "count", 8: "encode", 9: "stagger_step", 10: "repack", 11: "retire"}
+                 7: "count", 8: "encode", 10: "repack", 11: "retire"}
 
 
 def load_library():

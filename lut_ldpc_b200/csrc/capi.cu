@@ -129,7 +129,6 @@ int lutldpc_get_info(const lutldpc_decoder* h, lutldpc_info* info) {
       ++info->n_var_programs;
       info->n_fast_var_programs += h->var_progs[(size_t)t * nvc + c].fast_dv != 0;
     }
-  info->staggered_schedule = h->stagger_ok ? 1 : 0;
   return LUTLDPC_OK;
 }
 

@@ -22,11 +22,10 @@ static int env_int(const char* name, int dflt) {
 
 lutldpc_decoder::~lutldpc_decoder() {
   if (h_active) cudaFreeHost(h_active);
-  if (h_poll) cudaFreeHost(h_poll);
-  for (auto& e : ev_poll)
-    if (e) cudaEventDestroy(e);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
+  if (ev_sim0) cudaEventDestroy(ev_sim0);
+  if (ev_sim1) cudaEventDestroy(ev_sim1);
   if (ev_lag) cudaEventDestroy(ev_lag);
   for (cudaEvent_t e : evpool) cudaEventDestroy(e);
 }
@@ -151,9 +150,12 @@ int lutldpc_decoder::init_device() {
       if (!compile_program(tr, vn_classes[c].degree, dec ? PROG_DEC : PROG_VAR, m.Nq_Msg[ii], m.Nq_Cha, p, perr))
         return fail(LUTLDPC_ERR_MODEL, "var tree (slot " + std::to_string(t) + ", degree " +
                                            std::to_string(vn_classes[c].degree) + "): " + perr);
-      int want_out = dec ? 2 : m.Nq_Msg[std::min(ii + 1, m.max_iters - 1)];
-      if (!dec && tr.nodes[0].K != want_out)
-        return fail(LUTLDPC_ERR_MODEL, "var tree output alphabet does not match Nq_Msg of the next iteration");
+      // every iteration that uses this slot must be followed by the alphabet the slot's root emits: the next check
+      // pass reads the codes with code_bits(Nq_Msg[ii+1])
+      if (!dec)
+        for (int i2 = 0; i2 + 1 < m.max_iters; ++i2)
+          if (m.var_tree_idx_iter[i2] == t && tr.nodes[0].K != m.Nq_Msg[i2 + 1])
+            return fail(LUTLDPC_ERR_MODEL, "var tree output alphabet does not match Nq_Msg of the next iteration");
       if (dec && tr.nodes[0].K != 2) return fail(LUTLDPC_ERR_MODEL, "decision tree root must be binary");
       add_prog(p, var_progs[(size_t)t * nvc + c]);
       if (!dec && use_fast_vn && fast_vn_matches(p)) var_progs[(size_t)t * nvc + c].fast_dv = vn_classes[c].degree;
@@ -190,58 +192,6 @@ int lutldpc_decoder::init_device() {
       for (auto& t : tiles) flat.push_back(t.second);
       n_fused_tiles = (int)flat.size();
       CK(d_fused_tiles.upload(flat), "upload fused tiles");
-    }
-  }
-  {  // staggered schedule: needs every VN class on the specialised code and min-sum checks with row tables
-    // Opt-in (LUTLDPC_STAGGER=1): measured on B200 the combined launch is bound by the integer ALU pipe, which
-    // both passes load (N=64800: 0.82 ms per half-iteration pair of launches vs 0.84 ms back to back), so the
-    // sequential schedule stays the default.  DESIGN.md section 5 has the ncu numbers.
-    const char* e = getenv("LUTLDPC_STAGGER");
-    bool want = m.minLUT && use_cn_exact && cn_exact.size() <= 4 && n_iter_slots >= 2 && e && e[0] == '1';
-    std::vector<std::pair<double, int4>> items;
-    const int vn_ops = std::max(1, env_int("LUTLDPC_STAGGER_VN_OPS", 32));
-    const int cn_rows = std::max(1, env_int("LUTLDPC_STAGGER_CN_ROWS", 16));
-    stg_cn_warps = std::max(1, std::min(8, env_int("LUTLDPC_STAGGER_CN_WARPS", 2)));
-    for (int c = 0; c < nvc && want; ++c) {
-      if (!vn_classes[c].n) continue;
-      for (int t = 0; t + 1 < n_iter_slots; ++t) want &= var_progs[(size_t)t * nvc + c].fast_dv != 0;
-      want &= stg_classes.size() < 8;
-      if (!want) break;
-      const int j = (int)stg_classes.size();
-      stg_classes.push_back(c);
-      stg_max_dv = std::max(stg_max_dv, vn_classes[c].degree);
-      const int per = std::max(1, vn_ops / std::max(1, (int)var_progs[c].n_ops));
-      const int nt = (vn_classes[c].n + per - 1) / per;
-      for (int i = 0; i < nt; ++i)
-        items.push_back({(i + 0.5) / nt, make_int4(j, i * per, std::min(per, vn_classes[c].n - i * per), 0)});
-    }
-    for (auto& cl : cn_exact) stg_max_dc = std::max(stg_max_dc, cl.degree);
-    want = want && !stg_classes.empty() && stagger_supported(stg_max_dv, stg_max_dc);
-    if (want) {
-      // classes interleaved, so that the long tiles of the high degrees are spread over the whole launch
-      std::stable_sort(items.begin(), items.end(), [](const std::pair<double, int4>& a, const std::pair<double, int4>& b2) {
-        return a.first < b2.first;
-      });
-      std::vector<int4> flat;
-      for (auto& t : items) flat.push_back(t.second);
-      n_stg_vn_items = (int)flat.size();
-      CK(d_stg_vn_items.upload(flat), "upload stagger items");
-      flat.clear();
-      for (size_t k = 0; k < cn_exact.size(); ++k)
-        for (int i = 0; i < cn_exact[k].n; i += cn_rows)
-          flat.push_back(make_int4((int)k, i, std::min(cn_rows, cn_exact[k].n - i), 0));
-      n_stg_cn_items = (int)flat.size();
-      CK(d_stg_cn_items.upload(flat), "upload stagger items");
-      CK(d_stg_ctr.ensure((size_t)2 * (2 * m.max_iters + 4)), "alloc stagger counters");
-      int sms = 0;
-      CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device), "device attribute");
-      stg_ctas = 2 * sms;
-      CK(configure_stagger(), "configure stagger kernel");
-      CK(cudaMallocHost((void**)&h_poll, 8 * sizeof(uint32_t)), "cudaMallocHost");
-      for (auto& ev : ev_poll) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming), "cudaEventCreate");
-      stagger_ok = true;
-    } else {
-      stg_classes.clear();
     }
   }
   chk_progs.assign((size_t)n_iter_slots * ncc, ProgRef());
@@ -403,7 +353,6 @@ int lutldpc_decoder::run_batch(int n_frames, const uint8_t* d_cha_lab, const uin
 
 // Expects cha / msgs / hard of the current batch to be initialised (pack or the channel kernel).
 int lutldpc_decoder::run_passes(TraceSink* tr) {
-  if (stagger_ok && !tr && b.W >= 2 * kNodeThreads) return run_passes_staggered();
   int rc = 0;
   const int n_frames = b.F;
   BatchBuffers cur = b;  // working layout: the batch itself until the first repack
@@ -579,123 +528,6 @@ int lutldpc_decoder::run_passes(TraceSink* tr) {
   CK(cudaEventRecord(ev1, st), "event");
   have_stats = true;
   last_frames = n_frames;
-  stat_frame_iters = -1;
-  return LUTLDPC_OK;
-}
-
-// lut_decode with the two halves of the batch half an iteration apart (stagger.cu): launch s runs heavy
-// phase s of half 0 and heavy phase s-1 of half 1, where phase 2*ii is the check pass and phase 2*ii+1 the
-// variable pass of iteration ii (src/LDPC_Code_LUT.cpp:302-338).  Per frame the sequence of passes, flag
-// tests and returns is exactly that of run_passes(); frames are independent, so the interleaving of the
-// halves is not observable in the results.  The host looks at the counters of unfinished frames two
-// launches late (ring of pinned slots + events) so that the stream never drains.
-int lutldpc_decoder::run_passes_staggered() {
-  cudaStream_t st = stream;
-  const int nvc = (int)vn_classes.size();
-  const uint8_t* blob = d_prog_blob.p;
-  const int W = b.W;
-  const int Wa = std::min(W, ((W / 2 + kNodeThreads - 1) / kNodeThreads) * kNodeThreads);
-  const int w0[2] = {0, Wa}, w1[2] = {Wa, W};
-  CK(cudaMemsetAsync(d_stg_ctr.p, 0, d_stg_ctr.n * sizeof(unsigned int), st), "memset counters");
-  uint32_t* n_act = b.n_active;  // two device slots, one per half
-  bool alive[2] = {true, true};
-  if (pisc) {  // :277
-    CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
-    for (int h = 0; h < 2; ++h) {
-      CK(launch_finalize_range(FIN_INIT, 0, b, w0[h], w1[h], n_act + h, st), "finalize"); launched(KIND_FINALIZE);
-    }
-    if (poll_every > 0) {
-      CK(cudaMemcpyAsync(h_poll, n_act, 8, cudaMemcpyDeviceToHost, st), "poll copy");
-      CK(cudaStreamSynchronize(st), "poll sync");
-      alive[0] = h_poll[0] != 0;
-      alive[1] = h_poll[1] != 0;
-    }
-  }
-  const int n_phases = 2 * max_iters - 1;  // per half: CN(0) VN(0) ... CN(max-1)
-  int ring_head = 0, ring_n = 0, polled = 0;  // lagged polls in flight
-  int ring_mask[4] = {0, 0, 0, 0};            // which halves a slot reports on
-  for (int s = 0; s <= n_phases && (alive[0] || alive[1]); ++s) {
-    StaggerParams P;
-    memset(&P, 0, sizeof P);
-    P.W = W;
-    P.vn_items = d_stg_vn_items.p; P.n_vn_items = n_stg_vn_items;
-    P.cn_items = d_stg_cn_items.p; P.n_cn_items = n_stg_cn_items;
-    P.n_cn_warps = stg_cn_warps;
-    P.ring_rows = stagger_ring_rows(stg_max_dc);
-    P.ctr = d_stg_ctr.p + 2 * s;
-    int fin_half = -1, fin_ii = 0;
-    bool any = false;
-    for (int h = 0; h < 2; ++h) {
-      const int ph = s - h;
-      if (!alive[h] || ph < 0 || ph >= n_phases) continue;
-      const int ii = ph >> 1;
-      any = true;
-      if ((ph & 1) == 0) {
-        P.cn_w0 = w0[h]; P.cn_w1 = w1[h];
-        P.cn_q = code_bits(m.Nq_Msg[ii]);
-        P.cn_want = psc && ii > 0;
-        if (P.cn_want) { fin_half = h; fin_ii = ii; }
-      } else {
-        const int t = m.var_tree_idx_iter[ii];
-        P.vn_w0 = w0[h]; P.vn_w1 = w1[h];
-        P.vn_want = psc;
-        for (size_t j = 0; j < stg_classes.size(); ++j) {
-          const int c = stg_classes[j];
-          const ProgRef& r = var_progs[(size_t)t * nvc + c];
-          P.c[j] = FusedVnClass{blob + r.off + r.tables_off, vn_classes[c].pairs.p, r.fast_dv, r.q_out};
-          P.tab_off[j] = P.tab_bytes;
-          P.tab_bytes += (r.fast_dv - 1) * 128;
-        }
-      }
-    }
-    if (!any) continue;
-    for (size_t k = 0; k < cn_exact.size(); ++k) {
-      P.cn_rows[k] = cn_exact[k].list.p;
-      P.cn_dc[k] = cn_exact[k].degree;
-    }
-    CK(launch_stagger(P, stg_max_dv, stg_ctas, g, b, st), "stagger"); launched(KIND_STEP);
-    if (fin_half >= 0) {  // psc: VN pass ii-1 unanimous and syndrome zero -> return ii (:327)
-      CK(launch_finalize_range(FIN_ITER, fin_ii, b, w0[fin_half], w1[fin_half], n_act + fin_half, st), "finalize");
-      launched(KIND_FINALIZE);
-      if (poll_every > 0 && ++polled % poll_every == 0) {
-        if (ring_n == 4) return fail(LUTLDPC_ERR_STATE, "poll ring overflow");
-        const int slot = (ring_head + ring_n) & 3;
-        CK(cudaMemcpyAsync(h_poll + 2 * slot, n_act, 8, cudaMemcpyDeviceToHost, st), "poll copy");
-        CK(cudaEventRecord(ev_poll[slot], st), "poll event");
-        ring_mask[slot] = 1 << fin_half;
-        ++ring_n;
-      }
-    }
-    // consume polls that are at least two launches old (or everything that has already landed)
-    while (ring_n > 0) {
-      const int slot = ring_head;
-      if (ring_n <= 2) {
-        cudaError_t q = cudaEventQuery(ev_poll[slot]);
-        if (q == cudaErrorNotReady) break;
-        CK(q, "poll query");
-      } else {
-        CK(cudaEventSynchronize(ev_poll[slot]), "poll sync");
-      }
-      for (int h = 0; h < 2; ++h)
-        if ((ring_mask[slot] >> h & 1) && h_poll[2 * slot + h] == 0) alive[h] = false;
-      ring_head = (ring_head + 1) & 3;
-      --ring_n;
-    }
-  }
-  if (alive[0] || alive[1]) {  // decision + final syndrome (:340-349); finished words are skipped inside
-    const int t = m.var_tree_idx_iter[max_iters - 1];
-    for (int c = 0; c < nvc; ++c) {
-      if (!vn_classes[c].n) continue;
-      const ProgRef& r = var_progs[(size_t)t * nvc + c];
-      NodeLaunch nl{blob + r.off, r.bytes, r.n_slots, r.n_in, vn_classes[c].list.p, vn_classes[c].pairs.p, vn_classes[c].n};
-      CK(launch_node(NODE_DEC, nl, g, b, 0, st), "dec_lut"); launched(KIND_DEC0 + std::min(c, 15));
-    }
-    CK(launch_syndrome(g, b, st), "syndrome"); launched(KIND_SYNDROME);
-    CK(launch_finalize(FIN_LAST, max_iters, b, st), "finalize"); launched(KIND_FINALIZE);
-  }
-  CK(cudaEventRecord(ev1, st), "event");
-  have_stats = true;
-  last_frames = b.F;
   stat_frame_iters = -1;
   return LUTLDPC_OK;
 }

@@ -15,7 +15,6 @@ namespace lutldpc {
 enum ProfileKind {  // indices of lutldpc_get_profile
   KIND_RESET = 0, KIND_PACK = 1, KIND_CHANNEL = 2, KIND_CN = 3, KIND_SYNDROME = 4, KIND_FINALIZE = 5,
   KIND_UNPACK = 6, KIND_COUNT = 7, KIND_ENCODE = 8,
-  KIND_STEP = 9,  // staggered launch: check pass of one half of the batch + variable pass of the other
   KIND_REPACK = 10, KIND_RETIRE = 11,  // frame repacking: gather of the unfinished frames / results back
   KIND_VN0 = 16, KIND_DEC0 = 32, KIND_CHK0 = 48  // + degree-class index
 };
@@ -100,7 +99,8 @@ struct lutldpc_decoder {
   lutldpc::DecoderModel m;
   int device = 0;
   cudaStream_t stream = nullptr;
-  int max_iters = 0, psc = 1, pisc = 1, init_mode = LUTLDPC_INIT_CONT, poll_every = 1;
+  // psc/pisc: the reference constructs LDPC_Code_LUT with psc(true), pisc(false) (src/LDPC_Code_LUT.cpp:46-47)
+  int max_iters = 0, psc = 1, pisc = 0, init_mode = LUTLDPC_INIT_CONT, poll_every = 1;
   std::string err;
 
   lutldpc::DevBuf<int32_t> d_vn_edge0, d_dv, d_cn_start, d_cn_msg_idx, d_chk_equ_idx, d_cha2msg;
@@ -114,14 +114,6 @@ struct lutldpc_decoder {
   std::vector<int> fused_classes;
   lutldpc::DevBuf<int4> d_fused_tiles;
   int n_fused_tiles = 0, fused_max_dv = 0;
-  // staggered schedule (stagger.cu): every VN class specialised, min-sum checks with row tables
-  bool stagger_ok = false;
-  std::vector<int> stg_classes;  // VN class behind StaggerParams::c[j]
-  lutldpc::DevBuf<int4> d_stg_vn_items, d_stg_cn_items;
-  lutldpc::DevBuf<unsigned int> d_stg_ctr;  // two tile counters per launch of a batch
-  int n_stg_vn_items = 0, n_stg_cn_items = 0, stg_max_dv = 0, stg_max_dc = 0, stg_ctas = 0, stg_cn_warps = 2;
-  uint32_t* h_poll = nullptr;    // pinned [4][2]: unfinished frames per half, ring of lagged polls
-  cudaEvent_t ev_poll[4] = {nullptr, nullptr, nullptr, nullptr};
   std::vector<lutldpc::ProgRef> var_progs;  // [iter slot][vn class]; last slot = decision trees
   std::vector<lutldpc::ProgRef> chk_progs;  // [iter slot][cn class]
   int n_iter_slots = 0;
@@ -151,6 +143,7 @@ struct lutldpc_decoder {
   double repack_alpha = 0.7;
   int64_t repacks = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev_sim0 = nullptr, ev_sim1 = nullptr;  // lutldpc_simulate_snr: brackets of the whole call
   bool have_stats = false;
   int64_t launches = 0, last_frames = 0, stat_frame_iters = -1;
 
@@ -176,6 +169,5 @@ struct lutldpc_decoder {
   // gathers the unfinished frames of `cur` (n_live of them) into rctx[slot]; `cur` becomes the new layout
   int repack_into(lutldpc::BatchBuffers& cur, int slot, int n_live);
   int retire_from(const lutldpc::BatchBuffers& cur);  // results of a repacked layout back into b
-  int run_passes_staggered();               // same result, the two halves of the batch half an iteration apart
   int max_batch_frames() const;
 };

@@ -1,4 +1,4 @@
-// Device-side helpers shared by the kernel translation units (kernels.cu, stagger.cu).
+// Device-side helpers shared by the kernel translation units.
 #pragma once
 #include <cstdint>
 

@@ -23,8 +23,8 @@ struct BatchBuffers {
   uint32_t* cn_fail = nullptr;
   uint32_t* syn_fail = nullptr;
   int32_t* iters = nullptr;
-  uint32_t* n_active = nullptr;  // device counters written by finalize: [0] unfinished frames, [1] scratch of the
-                                 // staggered schedule, [2] entries of cols, [3] entries of grp4
+  uint32_t* n_active = nullptr;  // device counters written by finalize: [0] unfinished frames, [1] unused,
+                                 // [2] entries of cols, [3] entries of grp4
   // Work lists rebuilt by every finalize: word columns that still hold an unfinished frame, and groups of 4
   // adjacent columns (vector accesses) with any such word.  The hot kernels map thread i to cols[i] / grp4[i],
   // so the issue slots follow the number of live words instead of the number of live warps.
@@ -85,36 +85,6 @@ struct FusedVnParams {
 };
 cudaError_t launch_vn_fused(const FusedVnParams& P, int max_dv, const int4* d_tiles, int n_tiles, const GraphArrays& g,
                             const BatchBuffers& b, int want_flags, cudaStream_t st);
-// ---- staggered schedule.  The min-sum check pass is bound by HBM and leaves the issue slots idle; the
-// LUT variable pass is bound by shared-memory look-ups and integer issue and leaves HBM idle.  One
-// launch therefore runs the CHECK pass of one column range of the batch and the VARIABLE pass of
-// another (the two halves of a batch run half an iteration apart).  The kernel is persistent (2 CTAs per
-// SM) and warp-specialised: warps pull tiles from two global queues (stagger.cu).
-//   vn_items[i] = (slot j of c[], first node, node count, 0)   -- one tile = those nodes x 128 columns
-//   cn_items[i] = (check class k, first check, check count, 0)  -- one tile = those checks x 128 columns
-struct StaggerParams {
-  FusedVnClass c[8];          // dv == 0: unused slot
-  int tab_off[8];             // shared-memory offset of the class's LUTs
-  int tab_bytes;              // all classes
-  const int32_t* cn_rows[4];  // row tables [n][degree], as for launch_cn_exact
-  int cn_dc[4];
-  const int4* vn_items;
-  const int4* cn_items;
-  int n_vn_items, n_cn_items;
-  int W;                      // row stride of the batch (words)
-  int cn_w0, cn_w1;           // columns that get the check pass (empty range: none)
-  int cn_q, cn_want;          // code width of that pass; 1 = OR sign parities into cn_fail
-  int vn_w0, vn_w1;           // columns that get the variable pass
-  int vn_want;                // 1 = unanimity flags + hard decisions (psc)
-  int n_cn_warps;             // warps per CTA that start on the check queue
-  int ring_rows;              // check rows in flight per check warp (stagger_ring_rows)
-  unsigned int* ctr;          // [0] next variable tile, [1] next check tile; zero before the launch
-};
-bool stagger_supported(int max_dv, int max_dc);
-int stagger_ring_rows(int max_dc);
-cudaError_t configure_stagger();
-cudaError_t launch_stagger(const StaggerParams& P, int max_dv, int n_ctas, const GraphArrays& g, const BatchBuffers& b,
-                           cudaStream_t st);
 // finalize restricted to columns [w0, w1); *n_active receives the unfinished frames of that range
 cudaError_t launch_finalize_range(FinalizeMode mode, int value, const BatchBuffers& b, int w0, int w1,
                                   uint32_t* n_active, cudaStream_t st);

@@ -200,7 +200,7 @@ bool read_it_file(const char* path, ItFile& f, std::string& err) {
   while (off + 24 <= f.buf.size()) {
     uint64_t h[3];
     memcpy(h, f.buf.data() + off, 24);
-    if (h[2] < 24 || h[0] < 27 || h[0] + h[1] > h[2] || off + h[2] > f.buf.size()) { err = "codec file: corrupt block header"; return false; }
+    if (h[2] < 24 || h[0] < 27 || h[2] > f.buf.size() - off || h[0] > h[2] || h[1] > h[2] - h[0]) { err = "codec file: corrupt block header"; return false; }
     const char* s = reinterpret_cast<const char*>(f.buf.data() + off + 24);
     const char* end = reinterpret_cast<const char*>(f.buf.data() + off + h[0]);
     std::string str[3];

@@ -282,10 +282,10 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
   cp.Nq_cha = m.Nq_Cha; cp.q_cha = code_bits(m.Nq_Cha); cp.Nq_msg = m.Nq_Msg[0]; cp.q_msg = code_bits(m.Nq_Msg[0]);
   const uint32_t k0 = (uint32_t)p->seed, k1 = (uint32_t)(p->seed >> 32);
   int64_t total_launches = 0;
-  cudaEvent_t e_first = nullptr, e_last = nullptr;
-  CKH(cudaEventCreate(&e_first), "event");
-  CKH(cudaEventCreate(&e_last), "event");
-  CKH(cudaEventRecord(e_first, st), "event");
+  // whole-call events (all batches); owned by the handle, so no error path can leak them
+  if (!h->ev_sim0) CKH(cudaEventCreate(&h->ev_sim0), "event");
+  if (!h->ev_sim1) CKH(cudaEventCreate(&h->ev_sim1), "event");
+  CKH(cudaEventRecord(h->ev_sim0, st), "event");
   for (int64_t done = 0; done < p->n_frames; done += batch) {
     int nf = (int)std::min<int64_t>(batch, p->n_frames - done);
     int rc = h->begin_batch(nf);
@@ -319,15 +319,13 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
     h->launched(KIND_COUNT);
     total_launches += h->launches + 2;
   }
-  CKH(cudaEventRecord(e_last, st), "event");
+  CKH(cudaEventRecord(h->ev_sim1, st), "event");
   std::vector<unsigned long long> host(n_cnt);
   CKH(cudaMemcpyAsync(host.data(), h->buf_cnt.p, n_cnt * 8, cudaMemcpyDeviceToHost, st), "D2H counters");
   CKH(cudaStreamSynchronize(st), "sync");
   // report the whole call (all batches) through last_call_stats
-  std::swap(h->ev0, e_first);
-  std::swap(h->ev1, e_last);
-  cudaEventDestroy(e_first);
-  cudaEventDestroy(e_last);
+  std::swap(h->ev0, h->ev_sim0);
+  std::swap(h->ev1, h->ev_sim1);
   h->launches = total_launches;
   h->have_stats = p->n_frames > 0;
   h->stat_frame_iters = (int64_t)host[6];

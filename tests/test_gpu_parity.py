@@ -141,75 +141,6 @@ def test_generic_interpreter_still_bit_exact(L):
     assert np.array_equal(it, fx["ret"]) and np.array_equal(out, fx["out"])
 
 
-_stg = {}
-
-
-def _stagger_decoder(L, cfg):
-    """Decoder with the opt-in staggered schedule (LUTLDPC_STAGGER=1 at creation)."""
-    import os
-    if cfg not in _stg:
-        os.environ["LUTLDPC_STAGGER"] = "1"
-        try:
-            _stg[cfg] = L.Decoder(_golden.bundle_path(cfg))
-        finally:
-            del os.environ["LUTLDPC_STAGGER"]
-    return _stg[cfg]
-
-
-@pytest.mark.parametrize("cfg,tag", [(c, t) for c, t in _golden.all_fixtures()
-                                     if c in ("c1b_reg36_n1000", "c2_irr_n500", "c3_irr_n10000", "x_varq_reuse",
-                                              "x_qcha_irr_n1000")])
-def test_staggered_schedule_fixture_bit_exact(L, cfg, tag):
-    """Opt-in staggered schedule (stagger.cu): batches of >= 2048 frames run as two halves half an iteration
-    apart.  The reference's fixture frames, shuffled over a ragged batch that spans both halves, still decode
-    bit-exactly (the default sequential schedule sees the same large batches in the other tests)."""
-    fx = pyoracle.read_fixture(_golden.fixture_path(cfg, tag))
-    a = _golden.fixture_args(cfg, tag)
-    dec = _stagger_decoder(L, cfg)
-    # 4-bit balanced-tree decoders take the staggered schedule; the 3-bit ones stay sequential (same test)
-    assert bool(dec.staggered_schedule) == (cfg in ("c1b_reg36_n1000", "c2_irr_n500", "c3_irr_n10000"))
-    nfx = fx["cha"].shape[0]
-    for d in (dec, _dec(L, cfg)):
-        d.set_exit_conditions(d.max_iters, a["psc"], a["pisc"])
-        for n in (2048, 2309):
-            idx = np.random.default_rng(n).integers(0, nfx, n)
-            out, it = d.decode_quantized(fx["cha"][idx], fx["msg"][idx])
-            assert np.array_equal(it, fx["ret"][idx])
-            assert np.array_equal(out, fx["out"][idx])
-
-
-@pytest.mark.parametrize("cfg", ["c2_irr_n500", "c3_irr_n10000", "c5_n64800"])
-def test_staggered_equals_sequential_schedule(L, cfg):
-    """Same seeded noisy inputs through the staggered and the sequential pass schedule (and, for a few
-    frames of the small code, the oracle): identical decisions and lut_decode returns, incl. frames that
-    finish early, late and never."""
-    dec = _stagger_decoder(L, cfg)
-    ref = _dec(L, cfg)
-    assert dec.staggered_schedule and not ref.staggered_schedule
-    n = 2560 if cfg != "c5_n64800" else 2304
-    snr = {"c2_irr_n500": 1.5, "c3_irr_n10000": 1.1, "c5_n64800": 1.2}[cfg]
-    rng = np.random.default_rng(11)
-    sigma = np.sqrt(0.5 / (dec.rate * 10 ** (snr / 10)))
-    llr = (2.0 / sigma ** 2) * (1.0 + sigma * rng.standard_normal((n, dec.nvar)))
-    for psc, pisc in ((1, 1), (0, 0)):
-        dec.set_exit_conditions(dec.max_iters, psc, pisc)
-        ref.set_exit_conditions(ref.max_iters, psc, pisc)
-        o1, i1 = dec.decode_llr(llr)
-        o2, i2 = ref.decode_llr(llr)
-        assert np.array_equal(i1, i2) and np.array_equal(o1, o2)
-        if psc:
-            assert len(np.unique(np.abs(i1))) > 2  # a spread of return values is exercised
-    if cfg == "c2_irr_n500":
-        orc = pyoracle.Oracle(_golden.bundle_path(cfg))
-        orc.set_exit_conditions(dec.max_iters, 1, 1)
-        dec.set_exit_conditions(dec.max_iters, 1, 1)
-        cha, msg = dec.quantize(llr)
-        out, it = dec.decode_quantized(cha, msg)
-        sel = np.r_[0:40, n - 40:n]
-        want_out, want_it = orc.lut_decode_batch(cha[sel], msg[sel])
-        assert np.array_equal(want_it, it[sel]) and np.array_equal(want_out, out[sel])
-
-
 @pytest.mark.parametrize("cfg,snr,n", [("c2_irr_n500", 1.5, 3000), ("c1b_reg36_n1000", 1.8, 2100),
                                        ("c3_irr_n10000", 1.1, 1300), ("c5_n64800", 1.25, 1100)])
 def test_frame_repacking_is_not_observable(L, cfg, snr, n):
