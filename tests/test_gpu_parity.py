@@ -80,6 +80,23 @@ def test_random_inputs_vs_oracle(L, cfg, n_frames):
         assert np.array_equal(out, want_out), (psc, pisc)
 
 
+
+def test_fresh_handle_has_the_reference_constructor_defaults(L):
+    """LDPC_Code_LUT is constructed with psc(true), pisc(false) (src/LDPC_Code_LUT.cpp:46-47): a handle that never
+    saw lutldpc_set_exit_conditions must not take the initial syndrome exit.  The snr9 frames are codewords at the
+    channel output: pisc would return 0, the reference default runs iteration 0 and returns >= 1."""
+    cfg = "c1b_reg36_n1000"
+    fx = pyoracle.read_fixture(_golden.fixture_path(cfg, "snr9"))
+    assert (fx["ret"] == 0).any()  # the fixture itself was made with pisc=1
+    dec = L.Decoder(_golden.bundle_path(cfg))
+    out, it = dec.decode_quantized(fx["cha"], fx["msg"])
+    orc = pyoracle.Oracle(_golden.bundle_path(cfg))
+    orc.set_exit_conditions(orc.max_iters, 1, 0)
+    want_out, want_it = orc.lut_decode_batch(fx["cha"], fx["msg"])
+    assert (want_it >= 1).all()
+    assert np.array_equal(it, want_it) and np.array_equal(out, want_out)
+
+
 def test_empty_batch(L):
     dec = _dec(L, "c1b_reg36_n1000")
     out, it = dec.decode_quantized(np.zeros((0, dec.nvar), np.uint8), np.zeros((0, dec.nvar), np.uint8))
