@@ -33,6 +33,13 @@ WORKLOADS = {
 METRIC, UNIT = "decoded_info_gbit_per_s", "Gbit/s"
 
 
+def common_config(workload, desc, snr):
+    """`config` of the JSON line: identical in both arms (--impl b200 / reference) for the same command line."""
+    return {"workload": "%s: %s" % (workload, desc), "snr_db": snr, "codeword": "all-zero (LDPC.zero_codeword=true)",
+            "l2": "no flush needed: on the GPU arm the labels and message state of one step (frames x (2N + E/2) bytes, "
+                  "several GB) are far larger than the 126 MB L2; the CPU arm decodes one frame per core at a time"}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -185,7 +192,7 @@ def run_b200(args):
     dom = max(prof, key=lambda k: prof[k][0])
     per_frame_iter = {"cn_minsum": float(E)}
     for d, n in zip(dec.vn_class_degree, dec.vn_class_nodes):
-        per_frame_iter["vn_dv%d" % d] = n * (d + 0.5 + 0.125)   # dv nibbles in+out, channel nibble, hard-bit byte
+        per_frame_iter["vn_dv%d" % d] = n * (d + 0.5)   # dv nibbles in + out, channel nibble (E + N/2 per pass)
     # the fused launch runs every specialised class: all their nodes in one kernel
     per_frame_iter["vn_fused"] = sum(v for k, v in per_frame_iter.items() if k.startswith("vn_dv"))
     units = {"cn_minsum": sum_iters}
@@ -202,7 +209,12 @@ def run_b200(args):
             traffic = int(traffic * F / tj["frames_per_step"])
     step_gbs = sum_iters * b_iter * args.steps / (e0.elapsed_time(e1) * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                "frac": round(achieved / peak, 4), "traffic": traffic,
+                "traffic_source": "profiles/traffic.json (ncu --set full capture of one all-frames-live launch, static; "
+                                  "scaled to this run's frames per step)",
+                "algorithmic_bytes": "SURVEY 8(d): check pass E, variable pass E + N/2 bytes per frame-pass "
+                                     "(the N/8 hard-decision bytes a variable pass also writes are not counted)",
+                "peak_source": peak_src,
                 "kernel_ms_per_launch": round(dom_ms / max(1, prof[dom][1]), 4),
                 "whole_step_algorithmic_gbs": round(step_gbs, 1), "whole_step_frac": round(step_gbs / peak, 4),
                 "profiled_pass_ms_per_step": round(profiled_ms / args.steps, 3),
@@ -233,16 +245,56 @@ def run_b200(args):
     assert np.array_equal(i_np, it_host), "host-buffer path and device path disagree"
     e2e_value = sum_over_ranks(F) * e2e_steps * K / (e2e_ms * 1e-3) / 1e9
 
+    # ---- the fused Monte-Carlo step, i.e. what ber_sim runs per SNR point (LDPC_BER_Sim::sim_snr_point,
+    # src/LDPC_BER_Sim.cpp:246-311): Philox source/AWGN -> LLR -> quantise -> lut_decode -> BERC/BLERC counting, all on
+    # the device through lutldpc_simulate_snr, driven by the ber_sim.py harness: every step ends in the all-reduce of
+    # the 264 counters (NCCL for N > 1) and the global stop-rule test.  Same workload, SNR and frames per step.
+    from lut_ldpc_b200.ber_sim import LDPC_BER_Sim_LUT, SimParams
+    sp = SimParams(SNRdB=[snr], Nframes=F * world, Nfers=1 << 60, ber_min=0.0, fer_min=0.0, zero_codeword=True)
+    harness = LDPC_BER_Sim_LUT(sp, rand_seed=20261105, decoder=dec, chunk_frames=F, dist=dist if world > 1 else None,
+                               device="cuda" if world > 1 else None)
+    first = 0
+    for _ in range(max(1, min(args.warmup, 2))):
+        harness.sim_snr_point(snr, first)
+        first += F * world
+    harness.t_simulate = harness.t_allreduce = 0.0
+    sim_steps = max(1, min(args.steps, 3))
+    barrier()
+    t0 = time.perf_counter()
+    sim_acc = None
+    sim_dev_ms = 0.0
+    for _ in range(sim_steps):
+        acc, used, _stop = harness.sim_snr_point(snr, first)
+        first += used
+        sim_acc = acc if sim_acc is None else sim_acc + acc
+        sim_dev_ms += dec.last_call_stats()["device_ms"]
+    barrier()
+    sim_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+    dec.set_profiling(True)
+    harness.sim_snr_point(snr, first)
+    sim_prof = dec.get_profile()
+    dec.set_profiling(False)
+    sim = {"value": round(float(sim_acc[0]) * K / (sim_ms * 1e-3) / 1e9, 4), "unit": UNIT,
+           "frames_per_s": round(float(sim_acc[0]) / (sim_ms * 1e-3), 1), "ms_per_step": round(sim_ms / sim_steps, 3),
+           "device_ms_per_step_rank0": round(sim_dev_ms / sim_steps, 3), "steps": sim_steps,
+           "fer": float(sim_acc[1]) / float(sim_acc[0]), "ber": float(sim_acc[3]) / float(sim_acc[2]),
+           "mean_iterations": round(float(sim_acc[6]) / float(sim_acc[0]), 2),
+           "allreduce_ms_per_step": round(1e3 * harness.t_allreduce / sim_steps, 3),
+           "allreduce_share": round(1e3 * harness.t_allreduce / sim_ms, 5),
+           "profile_ms_one_step": {k: round(v[0], 3) for k, v in sim_prof.items()},
+           "call": "ber_sim.py LDPC_BER_Sim_LUT.sim_snr_point -> lutldpc_simulate_snr (Philox4x32-10 AWGN, quantiser, "
+                   "lut_decode, error counting on the device) + all_reduce(SUM) of 264 int64 counters per step"}
+
     line = {"metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u4 (8 codes per u32, SWAR)", "data": "synthetic",
-            "config": {"workload": "%s: %s" % (args.workload, desc), "snr_db": snr, "frames_per_step_per_gpu": F,
-                       "codeword": "all-zero (LDPC.zero_codeword=true)", "l2": "inputs+state larger than L2 "
-                       "(%.0f MB labels, %.0f MB messages per step)" % (2e-6 * F * N, 1e-6 * F * E / 2),
-                       "mean_iterations": round(sum_iters / F, 2), "decode_failures": int((it_host < 0).sum()),
-                       "frame_errors": int(wrong.sum()), "undetected_frame_errors": int((wrong & (it_host >= 0)).sum()),
-                       "edge_updates_per_s": round(2.0 * E * sum_iters_all * args.steps / (ms * 1e-3), 1)},
-            "roofline": roofline, "clocks": clocks, "gpu_launches": int(launches),
+            "config": common_config(args.workload, desc, snr),
+            "step": {"frames_per_step_per_gpu": F, "frames_per_step": F * world,
+                     "resident_bytes": "%.0f MB labels + %.0f MB messages per step and GPU" % (2e-6 * F * N, 1e-6 * F * E / 2),
+                     "mean_iterations": round(sum_iters / F, 2), "decode_failures": int((it_host < 0).sum()),
+                     "frame_errors": int(wrong.sum()), "undetected_frame_errors": int((wrong & (it_host >= 0)).sum()),
+                     "edge_updates_per_s": round(2.0 * E * sum_iters_all * args.steps / (ms * 1e-3), 1)},
+            "roofline": roofline, "sim": sim, "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": round(e2e_value, 4), "unit": UNIT, "h2d_bytes_per_step": int(2 * F * N) * world,
                     "d2h_bytes_per_step": int(F * N + 4 * F) * world, "steps": e2e_steps,
                     "call": "lutldpc_decode_quantized (pinned host u8 labels in, bits + iteration counts out; chunks pipelined over copy and decode streams)"}}
@@ -351,8 +403,8 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * wall / args.steps, 1),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32 (IT++ ivec)",
             "data": "synthetic",
-            "config": {"workload": "%s: %s" % (args.workload, desc), "snr_db": snr,
-                       "frames_per_step": per * procs, "codeword": "all-zero (LDPC.zero_codeword=true)"},
+            "config": common_config(args.workload, desc, snr),
+            "step": {"frames_per_step": per * procs},
             "cpu_baseline": {"value": round(value, 9), "unit": UNIT, "cores": procs, "kind": kind,
                              "sample": "%d frames per step (%d per process x %d processes, distinct seeds), "
                                        "frame-loop wall time only" % (per * procs, per, procs)},

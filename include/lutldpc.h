@@ -67,8 +67,8 @@ typedef struct lutldpc_info {
   double rate;
   int32_t n_var_programs;       /* (iteration slot, degree class) programs of the VN pass */
   int32_t n_fast_var_programs;  /* ... of which run on the compile-time specialised kernel (vn_fast.cuh) */
-  int32_t reserved0_;           /* always 0 (was: staggered schedule, removed) */
-  int32_t reserved_;
+  int32_t onchip;               /* 1: batches decode in the on-chip regime (lutldpc_set_onchip) */
+  int32_t onchip_smem_bytes;    /* shared memory per CTA of that regime (0: the decoder does not qualify) */
 } lutldpc_info;
 
 int lutldpc_abi_version(void);
@@ -165,7 +165,7 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
 /* ---- per-kernel device times.  With profiling on, an event is recorded after every kernel launch
  * of the handle; lutldpc_get_profile returns, per kind, the summed device milliseconds and launch
  * counts since profiling was switched on.  Kinds: 0 reset, 1 pack, 2 channel, 3 min-sum check pass,
- * 4 syndrome, 5 finalize, 6 unpack, 7 count, 8 encode, 9 unused, 10 frame repack, 11 retire (results of repacked frames back), 16+c variable-node pass of degree class c,
+ * 4 syndrome, 5 finalize, 6 unpack, 7 count, 8 encode, 9 unused, 10 frame repack, 11 retire (results of repacked frames back), 12 on-chip lut_decode (whole batch), 16+c variable-node pass of degree class c,
  * 32+c decision pass, 48+c LUT check pass.  class_degree/class_nodes [16] describe the VN classes. */
 #define LUTLDPC_PROFILE_KINDS 64
 int lutldpc_set_profiling(lutldpc_decoder* h, int on);
@@ -185,6 +185,15 @@ int lutldpc_last_call_stats(const lutldpc_decoder* h, double* device_ms, int64_t
  * >= 1).  on = 0 switches it off.  lutldpc_get_repack_count: repacks done by the handle so far. */
 int lutldpc_set_repack(lutldpc_decoder* h, int on, double alpha);
 int lutldpc_get_repack_count(const lutldpc_decoder* h, int64_t* repacks);
+
+/* ---- on-chip regime (no counterpart in the reference).  Decoders with min-sum checks whose per-column state
+ * (E message words, N channel words, N hard bytes for 8 frames) fits shared memory at least twice per SM -- the
+ * (3,6) N=1000, irregular N=500 and (6,32) N=2048 codes -- decode a batch in ONE persistent kernel: a CTA keeps the
+ * 8 frames of a word column in shared memory for all iterations, decides their early termination itself and then
+ * takes the next column.  Larger codes stream their messages through HBM once per half-iteration.  Results are
+ * identical in both regimes.  on = 0 forces the HBM regime; on = 1 on a decoder that does not qualify is
+ * LUTLDPC_ERR_STATE.  Traced decodes always take the HBM regime. */
+int lutldpc_set_onchip(lutldpc_decoder* h, int on);
 
 #ifdef __cplusplus
 }

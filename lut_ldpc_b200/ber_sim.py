@@ -17,6 +17,7 @@ designed decoder, i.e. the lut_codec.it a reference run saved (LDPC_Code_LUT::sa
 import configparser
 import math
 import os
+import time
 
 import numpy as np
 
@@ -89,6 +90,8 @@ class LDPC_BER_Sim_LUT:
         self.chunk, self.dist, self.device = int(chunk_frames), dist, device
         self._sim = simulate
         self.points = []
+        self.t_simulate = self.t_allreduce = 0.0  # host seconds spent in the per-rank GPU calls / the counter all-reduce
+        self.n_allreduce = 0
         self.rank = dist.get_rank() if dist is not None and dist.is_initialized() else 0
         self.world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
 
@@ -117,11 +120,15 @@ class LDPC_BER_Sim_LUT:
         if self.world == 1:
             return a
         import torch
+        t0 = time.perf_counter()
         t = torch.from_numpy(a.copy())
         if self.device is not None:
             t = t.to(self.device)
         self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
-        return t.cpu().numpy()
+        out = t.cpu().numpy()  # synchronises: the stop rules below need the sums on the host
+        self.t_allreduce += time.perf_counter() - t0
+        self.n_allreduce += 1
+        return out
 
     def sim_snr_point(self, snr, first_frame):
         """One SNR point; returns (counters, frames consumed, stop_sweep)."""
@@ -130,7 +137,10 @@ class LDPC_BER_Sim_LUT:
         while acc[0] < self.p.Nframes and acc[1] <= self.p.Nfers:
             todo = int(min(self.p.Nframes - acc[0], self.chunk * self.world))
             lo, n = split_frames(todo, first_frame + used, self.rank, self.world)
-            acc += self._allreduce(self._simulate(snr, n, lo))
+            t0 = time.perf_counter()
+            mine = self._simulate(snr, n, lo)
+            self.t_simulate += time.perf_counter() - t0
+            acc += self._allreduce(mine)
             used += todo
         ber = acc[3] / acc[2] if acc[2] else 0.0
         fer = acc[1] / acc[0] if acc[0] else 0.0

@@ -33,7 +33,7 @@ class _Info(C.Structure):
                                          "min_lut", "has_gen", "n_degree_classes")] + \
                [("lookups_per_frame_iter", C.c_int64), ("lookups_per_frame_iter_naive", C.c_int64), ("rate", C.c_double),
                 ("n_var_programs", C.c_int32), ("n_fast_var_programs", C.c_int32),
-                ("reserved0_", C.c_int32), ("reserved_", C.c_int32)]
+                ("onchip", C.c_int32), ("onchip_smem_bytes", C.c_int32)]
 
 
 class _SimParams(C.Structure):
@@ -73,10 +73,10 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_decode_quantized_device", "lutldpc_decode_llr", "lutldpc_decode_llr_device", "lutldpc_quantize",
            "lutldpc_decode_quantized_traced", "lutldpc_encode", "lutldpc_syndrome_check", "lutldpc_simulate_snr",
            "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device",
-           "lutldpc_set_repack", "lutldpc_get_repack_count"]
+           "lutldpc_set_repack", "lutldpc_get_repack_count", "lutldpc_set_onchip"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
-                 7: "count", 8: "encode", 10: "repack", 11: "retire"}
+                 7: "count", 8: "encode", 10: "repack", 11: "retire", 12: "onchip"}
 
 
 def load_library():
@@ -114,6 +114,7 @@ def load_library():
     L.lutldpc_last_call_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64)]
     L.lutldpc_quantize_device.argtypes = [vp, i32, vp, vp, vp]
     L.lutldpc_set_profiling.argtypes = [vp, i32]
+    L.lutldpc_set_onchip.argtypes = [vp, i32]
     L.lutldpc_get_profile.argtypes = [vp, vp, vp, vp, vp]
     _lib = L
     return L
@@ -169,6 +170,11 @@ class Decoder:
     def set_repack(self, on, alpha=0.7):
         """Frame repacking (gather of the unfinished frames into a narrower layout); results do not depend on it."""
         self._ck(self._L.lutldpc_set_repack(self._h, int(bool(on)), float(alpha)))
+
+    def set_onchip(self, on):
+        """On-chip regime (one persistent kernel per batch, state in shared memory) on/off; results do not depend on it."""
+        self._ck(self._L.lutldpc_set_onchip(self._h, int(bool(on))))
+        self.onchip = int(bool(on))
 
     @property
     def repack_count(self):

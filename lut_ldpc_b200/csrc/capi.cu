@@ -129,6 +129,17 @@ int lutldpc_get_info(const lutldpc_decoder* h, lutldpc_info* info) {
       ++info->n_var_programs;
       info->n_fast_var_programs += h->var_progs[(size_t)t * nvc + c].fast_dv != 0;
     }
+  info->onchip = h->onchip_ok ? 1 : 0;
+  info->onchip_smem_bytes = h->onchip_fits ? (int32_t)h->oc.smem_bytes : 0;
+  return LUTLDPC_OK;
+}
+
+int lutldpc_set_onchip(lutldpc_decoder* h, int on) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (on && !h->onchip_fits)
+    return h->fail(LUTLDPC_ERR_STATE, "the decoder does not qualify for the on-chip regime (LUT check nodes, or the state "
+                                      "of a word column does not fit shared memory twice per SM)");
+  h->onchip_ok = on != 0;
   return LUTLDPC_OK;
 }
 

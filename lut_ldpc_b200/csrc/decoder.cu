@@ -216,6 +216,10 @@ int lutldpc_decoder::init_device() {
     if (r.bytes + (size_t)r.n_slots * kNodeThreads * 4 > 200 * 1024)
       return fail(LUTLDPC_ERR_MODEL, "a node program (LUTs + value slots) exceeds the 200 KiB shared-memory budget");
   CK(d_prog_blob.upload(blob), "upload node programs");
+  {
+    int rc = init_onchip();
+    if (rc) return rc;
+  }
   CK(cudaHostAlloc((void**)&h_active, 8 * sizeof(uint32_t), cudaHostAllocMapped), "cudaHostAlloc");
   memset(h_active, 0, 8 * sizeof(uint32_t));
   CK(cudaHostGetDevicePointer((void**)&d_active_mirror, h_active, 0), "cudaHostGetDevicePointer");
@@ -271,15 +275,17 @@ int lutldpc_decoder::max_batch_frames() const {
   return (int)f;
 }
 
-int lutldpc_decoder::ensure_batch(int n_frames) {
+int lutldpc_decoder::ensure_batch(int n_frames, bool onchip) {
   int W = ((n_frames + 255) / 256) * 32;
-  CK(buf_msgs.ensure((size_t)m.num_edges * W + 4), "alloc msgs");  // + slack: the repack gather over-reads 2 words
+  if (onchip) CK(buf_msg0.ensure((size_t)m.nvar * W), "alloc msg0");  // the messages never leave shared memory
+  else CK(buf_msgs.ensure((size_t)m.num_edges * W + 4), "alloc msgs");  // + slack: the repack gather over-reads 2 words
   CK(buf_cha.ensure((size_t)m.nvar * W + 4), "alloc cha");
   CK(buf_hard.ensure((size_t)m.nvar * W), "alloc hard");
   CK(buf_flags.ensure((size_t)4 * W + 32), "alloc flags");
   CK(buf_cols.ensure((size_t)W + W / 4), "alloc work lists");
   CK(buf_iters.ensure((size_t)8 * W), "alloc iters");
-  b.msgs = buf_msgs.p; b.cha = buf_cha.p; b.hard = buf_hard.p;
+  b.msgs = onchip ? nullptr : buf_msgs.p; b.msg0 = onchip ? buf_msg0.p : nullptr;
+  b.cha = buf_cha.p; b.hard = buf_hard.p;
   b.done = buf_flags.p; b.vn_fail = buf_flags.p + W; b.cn_fail = buf_flags.p + 2 * W; b.syn_fail = buf_flags.p + 3 * W;
   b.n_active = buf_flags.p + 4 * W;
   b.iters = buf_iters.p;
@@ -291,8 +297,9 @@ int lutldpc_decoder::ensure_batch(int n_frames) {
 }
 
 // LDPC_Code_LUT::lut_decode for a whole batch (src/LDPC_Code_LUT.cpp:259-353; control flow: SURVEY A.6).
-int lutldpc_decoder::begin_batch(int n_frames) {
-  int rc = ensure_batch(n_frames);
+int lutldpc_decoder::begin_batch(int n_frames, bool traced) {
+  batch_onchip = onchip_ok && !traced;
+  int rc = ensure_batch(n_frames, batch_onchip);
   if (rc) return rc;
   launches = 0;
   if (profiling && (rc = flush_profile())) return rc;
@@ -345,10 +352,132 @@ int lutldpc_decoder::retire_from(const BatchBuffers& cur) {
 }
 
 int lutldpc_decoder::run_batch(int n_frames, const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, TraceSink* tr) {
-  int rc = begin_batch(n_frames);
+  int rc = begin_batch(n_frames, tr != nullptr);
   if (rc) return rc;
   CK(launch_pack(d_cha_lab, d_msg_lab, g, b, m.Nq_Cha, m.Nq_Msg[0], stream), "pack"); launched(KIND_PACK);
-  return run_passes(tr);
+  return run_decode(tr);
+}
+
+int lutldpc_decoder::run_decode(TraceSink* tr) { return batch_onchip ? run_onchip() : run_passes(tr); }
+
+// The whole lut_decode of the batch in one persistent kernel (onchip.cu): cha / msg0 / done in, hard / iters out.
+int lutldpc_decoder::run_onchip() {
+  OnchipParams P = oc;
+  P.W = b.W;
+  P.cha = b.cha; P.msg0 = b.msg0; P.hard = b.hard; P.iters = b.iters; P.done = b.done;
+  P.psc = psc; P.pisc = pisc;
+  CK(launch_onchip(P, oc_max_fast_dv, oc_threads, oc_ctas, stream), "onchip");
+  launched(KIND_ONCHIP);
+  CK(cudaEventRecord(ev1, stream), "event");
+  have_stats = true;
+  last_frames = b.F;
+  stat_frame_iters = -1;
+  return LUTLDPC_OK;
+}
+
+// Set-up of the on-chip regime.  A decoder qualifies when its checks are min-sum, and the state of one word column
+// (E message words with the bank skew, N channel words, N hard bytes), one slot of program images and the value
+// slots of the interpreted programs fit the shared memory of a CTA at least twice per SM.
+int lutldpc_decoder::init_onchip() {
+  onchip_ok = onchip_fits = false;
+  if (!m.minLUT) return LUTLDPC_OK;
+  const int nvc = (int)vn_classes.size();
+  std::vector<int> cls;
+  for (int c = 0; c < nvc; ++c)
+    if (vn_classes[c].n) cls.push_back(c);
+  if (cls.empty() || (int)cls.size() > kOnchipMaxClasses) return LUTLDPC_OK;
+  std::map<int, std::vector<int32_t>> rows;
+  for (int c = 0; c < m.nchk; ++c) {
+    std::vector<int32_t>& r = rows[m.dc[c]];
+    r.insert(r.end(), m.cn_msg_idx.begin() + m.cn_start[c], m.cn_msg_idx.begin() + m.cn_start[c + 1]);
+  }
+  if ((int)rows.size() > kOnchipMaxClasses) return LUTLDPC_OK;
+  auto al = [](size_t x, size_t a) { return (x + a - 1) / a * a; };
+  const size_t E = (size_t)m.num_edges, N = (size_t)m.nvar;
+  const size_t msgs_bytes = al((E + E / 32 + 1) * 4, 128), cha_bytes = al(N * 4, 128), hard_bytes = al(N, 128);
+  oc_state_bytes = msgs_bytes + cha_bytes + hard_bytes;
+  if (oc_state_bytes > (size_t)env_int("LUTLDPC_ONCHIP_MAX_STATE", 100 * 1024)) return LUTLDPC_OK;
+  const int dec_slot = n_iter_slots - 1;
+  // program images: class k of every iteration slot at the same offset, the decision slot laid out on its own
+  memset(&oc, 0, sizeof oc);
+  std::vector<uint32_t> it_sz(cls.size(), 0), dec_sz(cls.size(), 0);
+  int n_slots_max = 0;
+  oc_max_fast_dv = 0;
+  for (size_t k = 0; k < cls.size(); ++k) {
+    const int c = cls[k];
+    bool fast = n_iter_slots >= 2;
+    for (int t = 0; t < dec_slot; ++t) {
+      const ProgRef& r = var_progs[(size_t)t * nvc + c];
+      it_sz[k] = std::max(it_sz[k], r.bytes);
+      fast &= r.fast_dv != 0;
+    }
+    for (int t = 0; t < dec_slot && !fast; ++t) n_slots_max = std::max(n_slots_max, (int)var_progs[(size_t)t * nvc + c].n_slots);
+    const ProgRef& rd = var_progs[(size_t)dec_slot * nvc + c];
+    dec_sz[k] = rd.bytes;
+    n_slots_max = std::max(n_slots_max, (int)rd.n_slots);
+    oc.vc[k].pairs = vn_classes[c].pairs.p;
+    oc.vc[k].n = vn_classes[c].n;
+    oc.vc[k].dv = vn_classes[c].degree;
+    oc.vc[k].fast = fast ? 1 : 0;
+    if (fast) oc_max_fast_dv = std::max(oc_max_fast_dv, vn_classes[c].degree);
+  }
+  uint32_t off = 0, doff = 0;
+  for (size_t k = 0; k < cls.size(); ++k) {
+    oc.vc[k].img_off = off; off += (uint32_t)al(it_sz[k], 128);
+    oc.vc[k].dec_off = doff; doff += (uint32_t)al(dec_sz[k], 128);
+  }
+  oc.n_vc = (int)cls.size();
+  oc.slot_bytes = off; oc.dec_bytes = doff;
+  oc.slot_stride = std::max(off, doff);
+  oc_threads = m.nvar <= 1536 ? 128 : 256;
+  const size_t tab_bytes = oc.slot_stride, slots_bytes = al((size_t)n_slots_max * oc_threads * 4, 128);
+  oc.off_cha = (uint32_t)msgs_bytes;
+  oc.off_hard = (uint32_t)(msgs_bytes + cha_bytes);
+  oc.off_tab = (uint32_t)oc_state_bytes;
+  oc.off_slots = (uint32_t)(oc_state_bytes + tab_bytes);
+  oc.smem_bytes = (uint32_t)(oc_state_bytes + tab_bytes + slots_bytes);
+  if (oc.smem_bytes > (uint32_t)kOnchipMaxSmem) return LUTLDPC_OK;
+  CK(configure_onchip(), "configure onchip kernel");
+  oc_ctas_per_sm = onchip_ctas_per_sm(oc_max_fast_dv, oc_threads, oc.smem_bytes);
+  if (oc_ctas_per_sm < 2) return LUTLDPC_OK;
+  int sms = 0;
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device), "device attribute");
+  oc_ctas = sms * oc_ctas_per_sm;
+  // upload: slot images, iteration tables, check rows
+  std::vector<uint8_t> host_blob((size_t)d_prog_blob.n);
+  CK(cudaMemcpy(host_blob.data(), d_prog_blob.p, host_blob.size(), cudaMemcpyDeviceToHost), "read back programs");
+  std::vector<uint8_t> images((size_t)n_iter_slots * oc.slot_stride, 0);
+  for (int t = 0; t < n_iter_slots; ++t)
+    for (size_t k = 0; k < cls.size(); ++k) {
+      const ProgRef& r = var_progs[(size_t)t * nvc + cls[k]];
+      const uint32_t at = t == dec_slot ? oc.vc[k].dec_off : oc.vc[k].img_off;
+      memcpy(images.data() + (size_t)t * oc.slot_stride + at, host_blob.data() + r.off, r.bytes);
+    }
+  CK(d_oc_images.upload(images), "upload slot images");
+  std::vector<int32_t> q(m.max_iters);
+  for (int i = 0; i < m.max_iters; ++i) q[i] = code_bits(m.Nq_Msg[i]);
+  CK(d_oc_iter_slot.upload(m.var_tree_idx_iter), "upload iteration slots");
+  CK(d_oc_iter_q.upload(q), "upload iteration widths");
+  CK(d_oc_queue.ensure(4), "alloc queue");
+  oc_cn = std::vector<NodeClass>(rows.size());
+  int i = (int)rows.size() - 1;
+  for (auto& kv : rows) {  // descending degree
+    oc_cn[i].degree = kv.first;
+    oc_cn[i].n = (int)(kv.second.size() / kv.first);
+    CK(oc_cn[i].list.upload(kv.second), "upload cn rows");
+    --i;
+  }
+  for (size_t k = 0; k < oc_cn.size(); ++k) oc.cc[k] = OnchipCn{oc_cn[k].list.p, oc_cn[k].n, oc_cn[k].degree};
+  oc.n_cc = (int)oc_cn.size();
+  oc.slot_images = d_oc_images.p;
+  oc.iter_slot = d_oc_iter_slot.p; oc.iter_q = d_oc_iter_q.p;
+  oc.max_iters = m.max_iters; oc.dec_slot = dec_slot; oc.q_cha = code_bits(m.Nq_Cha);
+  oc.nvar = m.nvar; oc.nchk = m.nchk; oc.num_edges = m.num_edges;
+  oc.vn_edge0 = d_vn_edge0.p; oc.cn_start = d_cn_start.p; oc.chk_equ_idx = d_chk_equ_idx.p;
+  oc.queue = d_oc_queue.p;
+  onchip_fits = true;
+  onchip_ok = env_int("LUTLDPC_ONCHIP", 1) != 0;
+  return LUTLDPC_OK;
 }
 
 // Expects cha / msgs / hard of the current batch to be initialised (pack or the channel kernel).

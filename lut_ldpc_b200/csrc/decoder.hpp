@@ -8,6 +8,7 @@
 
 #include "../../include/lutldpc.h"
 #include "kernels.hpp"
+#include "onchip.hpp"
 #include "model.hpp"
 
 namespace lutldpc {
@@ -15,7 +16,8 @@ namespace lutldpc {
 enum ProfileKind {  // indices of lutldpc_get_profile
   KIND_RESET = 0, KIND_PACK = 1, KIND_CHANNEL = 2, KIND_CN = 3, KIND_SYNDROME = 4, KIND_FINALIZE = 5,
   KIND_UNPACK = 6, KIND_COUNT = 7, KIND_ENCODE = 8,
-  KIND_REPACK = 10, KIND_RETIRE = 11,  // frame repacking: gather of the unfinished frames / results back
+  KIND_REPACK = 10, KIND_RETIRE = 11,
+  KIND_ONCHIP = 12,  // the whole lut_decode of a batch in one persistent kernel (onchip.cu)  // frame repacking: gather of the unfinished frames / results back
   KIND_VN0 = 16, KIND_DEC0 = 32, KIND_CHK0 = 48  // + degree-class index
 };
 
@@ -119,6 +121,19 @@ struct lutldpc_decoder {
   int n_iter_slots = 0;
   bool use_fast_vn = true;  // LUTLDPC_GENERIC_VN=1 in the environment forces the interpreter (tests)
 
+  // on-chip regime (onchip.cu): codes whose per-column state fits shared memory decode in one persistent kernel
+  bool onchip_ok = false;      // batches take the regime (the decoder qualifies and it is switched on)
+  bool onchip_fits = false;    // the decoder qualifies
+  bool batch_onchip = false;   // the current batch takes it (traced decodes never do)
+  lutldpc::OnchipParams oc;    // static part; the per-batch pointers are filled at launch
+  lutldpc::DevBuf<uint8_t> d_oc_images;
+  lutldpc::DevBuf<int32_t> d_oc_iter_slot, d_oc_iter_q;
+  lutldpc::DevBuf<unsigned int> d_oc_queue;
+  std::vector<lutldpc::NodeClass> oc_cn;  // checks by degree, list = edge rows [n][degree] (any degree)
+  lutldpc::DevBuf<uint32_t> buf_msg0;
+  int oc_threads = 0, oc_ctas = 0, oc_ctas_per_sm = 0, oc_max_fast_dv = 0;
+  size_t oc_state_bytes = 0;
+
   // batch state
   lutldpc::BatchBuffers b;
   lutldpc::DevBuf<uint32_t> buf_msgs, buf_cha, buf_flags, buf_cols;
@@ -161,11 +176,14 @@ struct lutldpc_decoder {
   int fail(int code, const std::string& msg) { err = msg; return code; }
   int cuda_fail(cudaError_t e, const char* where);
   int init_device();          // uploads + program compilation
-  int ensure_batch(int n_frames);
+  int init_onchip();          // on-chip regime set-up (part of init_device)
+  int ensure_batch(int n_frames, bool onchip = false);
   // one batch, labels already on the device (frame-major); results left in b.hard / b.iters
   int run_batch(int n_frames, const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, lutldpc::TraceSink* tr);
-  int begin_batch(int n_frames);            // buffers + flag reset + start event
-  int run_passes(lutldpc::TraceSink* tr);   // all iterations + decision on the initialised batch
+  int begin_batch(int n_frames, bool traced = false);  // buffers + flag reset + start event; picks the regime
+  int run_decode(lutldpc::TraceSink* tr);   // lut_decode of the initialised batch in the regime begin_batch picked
+  int run_onchip();                         // ... one persistent kernel, state in shared memory
+  int run_passes(lutldpc::TraceSink* tr);   // ... all iterations + decision as separate passes over HBM
   // gathers the unfinished frames of `cur` (n_live of them) into rctx[slot]; `cur` becomes the new layout
   int repack_into(lutldpc::BatchBuffers& cur, int slot, int n_live);
   int retire_from(const lutldpc::BatchBuffers& cur);  // results of a repacked layout back into b

@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(256) k_pack(const uint8_t* __restrict__ cha_la
                                               const int32_t* __restrict__ vn_edge0, int nvar, int F, int W,
                                               int Nq_cha, int q_cha, int Nq_msg, int q_msg,
                                               uint32_t* __restrict__ cha, uint32_t* __restrict__ msgs,
-                                              uint8_t* __restrict__ hard) {
+                                              uint8_t* __restrict__ hard, uint32_t* __restrict__ msg0) {
   // one byte per (frame, node): channel code in the low nibble, message code in the high nibble
   __shared__ uint8_t t[256][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -82,6 +82,10 @@ __global__ void __launch_bounds__(256) k_pack(const uint8_t* __restrict__ cha_la
     }
     cha[(size_t)v * W + w] = cw;
     hard[(size_t)v * W + w] = (uint8_t)nib_bits_to_byte(cw, q_cha - 1);
+    if (msg0) {  // on-chip regime: the decode kernel broadcasts the word to the node's edges in shared memory
+      msg0[(size_t)v * W + w] = mw;
+      continue;
+    }
     int e0 = vn_edge0[v], e1 = vn_edge0[v + 1];
     for (int e = e0; e < e1; ++e) msgs[(size_t)e * W + w] = mw;
   }
@@ -1094,10 +1098,10 @@ cudaError_t launch_pack(const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, cons
   const bool vec4 = g.nvar % 4 == 0 && ((uintptr_t)d_cha_lab | (uintptr_t)d_msg_lab) % 4 == 0;
   if (vec4)
     k_pack<true><<<grid, 256, 0, st>>>(d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha),
-                                       Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard);
+                                       Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard, b.msg0);
   else
     k_pack<false><<<grid, 256, 0, st>>>(d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha),
-                                        Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard);
+                                        Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard, b.msg0);
   return cudaGetLastError();
 }
 

@@ -17,6 +17,7 @@ constexpr int kNodeThreads = 128;  // word columns per CTA of the node kernels
 struct BatchBuffers {
   uint32_t* msgs = nullptr;
   uint32_t* cha = nullptr;
+  uint32_t* msg0 = nullptr;      // on-chip regime only: [nvar][W] initial message code per node instead of msgs
   uint8_t* hard = nullptr;
   uint32_t* done = nullptr;
   uint32_t* vn_fail = nullptr;

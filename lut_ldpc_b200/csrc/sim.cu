@@ -38,16 +38,26 @@ __device__ __forceinline__ void philox4x32_10(uint32_t (&c)[4], uint32_t k0, uin
 }
 enum { STREAM_NOISE = 0, STREAM_INFO = 1 };
 
-// one standard normal for (frame, symbol): Box-Muller on two 52/32-bit uniforms of one Philox block
-__device__ __forceinline__ double normal_for(uint64_t frame, uint32_t sym, uint32_t k0, uint32_t k1) {
-  uint32_t c[4] = {(uint32_t)frame, (uint32_t)(frame >> 32), sym, STREAM_NOISE};
+// Four standard normals for (frame, node quad q) = the noise of symbols 4q .. 4q+3 of that frame: one Philox block,
+// two Box-Muller pairs (both outputs of each pair are used), all arithmetic in FP64.  The uniforms carry 32 bits:
+// u = (c + 0.5) / 2^32 in (0,1), i.e. radii up to sqrt(-2 ln 2^-33) = 6.76 sigma on a grid far finer than the
+// reference's own (IT++'s ziggurat spends 24 bits on the abscissa, itpp/itpp/base/random.cpp:690-720).
+// A sample depends only on (seed, frame, symbol): results do not depend on batch size or on how frames are
+// split over GPUs.
+__device__ __forceinline__ void normals4_for(uint64_t frame, uint32_t quad, uint32_t k0, uint32_t k1, double (&n)[4]) {
+  uint32_t c[4] = {(uint32_t)frame, (uint32_t)(frame >> 32), quad, STREAM_NOISE};
   philox4x32_10(c, k0, k1);
-  uint64_t a = ((uint64_t)c[0] << 32) | c[1];
-  double u1 = ((double)(a >> 11) + 0.5) * (1.0 / 9007199254740992.0);  // (0,1)
-  double u2 = ((double)c[2] + 0.5) * (1.0 / 4294967296.0);
-  double s, co;
-  sincospi(2.0 * u2, &s, &co);
-  return sqrt(-2.0 * log(u1)) * co;
+  const double k2m32 = 1.0 / 4294967296.0;
+#pragma unroll
+  for (int p = 0; p < 2; ++p) {
+    const double u1 = ((double)c[2 * p] + 0.5) * k2m32;
+    const double u2 = ((double)c[2 * p + 1] + 0.5) * k2m32;
+    const double r = sqrt(-2.0 * log(u1));
+    double sn, cs;
+    sincospi(2.0 * u2, &sn, &cs);
+    n[2 * p] = r * cs;
+    n[2 * p + 1] = r * sn;
+  }
 }
 
 __device__ __forceinline__ int quant_nonlin_s(double x, const double* b, int nb) {  // src/common.cpp:120-138
@@ -56,6 +66,16 @@ __device__ __forceinline__ int quant_nonlin_s(double x, const double* b, int nb)
     if (x > b[i]) ++idx;
     else break;
   }
+  return idx;
+}
+// Same value for ascending thresholds (the designed quantisers are: src/LDPC_DE.cpp:561-601): the number of leading
+// thresholds with x > b[i] is then the number of ALL thresholds below x -- a branch-free upper-bound search over the
+// 16 padded entries (+inf beyond nb), 4 compares instead of up to 15.
+__device__ __forceinline__ int quant_sorted16(double x, const double* b) {
+  int idx = (x > b[7]) ? 8 : 0;
+  idx += (x > b[idx + 3]) ? 4 : 0;
+  idx += (x > b[idx + 1]) ? 2 : 0;
+  idx += (x > b[idx]) ? 1 : 0;
   return idx;
 }
 __device__ __forceinline__ uint32_t lab2code_s(uint32_t m, int Nq, int q) {
@@ -97,47 +117,65 @@ __global__ void __launch_bounds__(128) k_encode(const uint8_t* __restrict__ P, i
 struct ChanParams {
   double sigma, four_over_N0;
   int n_qb_cha, n_qb_msg, use_map, Nq_cha, q_cha, Nq_msg, q_msg;
+  int sorted;  // both threshold vectors ascend: binary search gives quant_nonlin's value
 };
 
 // BPSK + AWGN + LLR + both quantisers -> channel labels, initial messages, channel hard decision,
-// and the uncoded (slicer) error count.  Thread = (variable node, word).
+// and the uncoded (slicer) error count.  Thread = (node quad 4q..4q+3, word): one Philox block per frame gives the
+// four normals of the quad, so a thread draws 8 blocks for its 32 symbols.
 __global__ void __launch_bounds__(128) k_channel(const uint8_t* __restrict__ cw, int zero_cw,
                                                  const int32_t* __restrict__ vn_edge0, int nvar, int W, int F,
                                                  uint64_t first_frame, uint32_t k0, uint32_t k1, ChanParams cp,
                                                  const double* __restrict__ qb_cha, const double* __restrict__ qb_msg,
                                                  const int32_t* __restrict__ cha2msg, uint32_t* __restrict__ cha,
                                                  uint32_t* __restrict__ msgs, uint8_t* __restrict__ hard,
+                                                 uint32_t* __restrict__ msg0,
                                                  unsigned long long* __restrict__ cnt_uncoded_err) {
   __shared__ double s_qc[16], s_qm[16];
   __shared__ int s_map[16];
   if (threadIdx.x < 16) {
-    s_qc[threadIdx.x] = threadIdx.x < cp.n_qb_cha ? qb_cha[threadIdx.x] : 0.0;
-    s_qm[threadIdx.x] = threadIdx.x < cp.n_qb_msg ? qb_msg[threadIdx.x] : 0.0;
+    const double inf = __longlong_as_double(0x7FF0000000000000LL);
+    s_qc[threadIdx.x] = threadIdx.x < cp.n_qb_cha ? qb_cha[threadIdx.x] : inf;
+    s_qm[threadIdx.x] = threadIdx.x < cp.n_qb_msg ? qb_msg[threadIdx.x] : inf;
     s_map[threadIdx.x] = (cp.use_map && threadIdx.x < cp.Nq_cha) ? cha2msg[threadIdx.x] : 0;
   }
   __syncthreads();
   const int w = blockIdx.y * blockDim.x + threadIdx.x;
-  const int v = blockIdx.x;
+  const int q = blockIdx.x, v0 = 4 * q;
   uint32_t nerr = 0;
   if (w < W) {
-    uint32_t bits = zero_cw ? 0u : cw[(size_t)v * W + w];
-    uint32_t cword = 0, mword = 0, slicer = 0;
+    uint32_t bits[4], cword[4] = {0, 0, 0, 0}, mword[4] = {0, 0, 0, 0}, slicer[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) bits[i] = (zero_cw || v0 + i >= nvar) ? 0u : cw[(size_t)(v0 + i) * W + w];
     for (int j = 0; j < 8; ++j) {
-      int f = 8 * w + j;
+      const int f = 8 * w + j;
       if (f >= F) break;
-      double s = ((bits >> j) & 1u) ? -1.0 : 1.0;
-      double x = s + cp.sigma * normal_for(first_frame + f, (uint32_t)v, k0, k1);
-      double llr = cp.four_over_N0 * x;
-      int c = quant_nonlin_s(llr, s_qc, cp.n_qb_cha);
-      int mm = cp.use_map ? s_map[c] : quant_nonlin_s(llr, s_qm, cp.n_qb_msg);
-      cword |= lab2code_s((uint32_t)c, cp.Nq_cha, cp.q_cha) << (4 * j);
-      mword |= lab2code_s((uint32_t)mm, cp.Nq_msg, cp.q_msg) << (4 * j);
-      slicer |= (x > 0.0 ? 0u : 1u) << j;
+      double nrm[4];
+      normals4_for(first_frame + f, (uint32_t)q, k0, k1, nrm);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const double sgn = ((bits[i] >> j) & 1u) ? -1.0 : 1.0;
+        const double x = sgn + cp.sigma * nrm[i];
+        const double llr = cp.four_over_N0 * x;
+        const int c = cp.sorted ? quant_sorted16(llr, s_qc) : quant_nonlin_s(llr, s_qc, cp.n_qb_cha);
+        const int mm = cp.use_map ? s_map[c]
+                                  : (cp.sorted ? quant_sorted16(llr, s_qm) : quant_nonlin_s(llr, s_qm, cp.n_qb_msg));
+        cword[i] |= lab2code_s((uint32_t)c, cp.Nq_cha, cp.q_cha) << (4 * j);
+        mword[i] |= lab2code_s((uint32_t)mm, cp.Nq_msg, cp.q_msg) << (4 * j);
+        slicer[i] |= (x > 0.0 ? 0u : 1u) << j;
+      }
     }
-    cha[(size_t)v * W + w] = cword;
-    hard[(size_t)v * W + w] = (uint8_t)nib_bits_to_byte(cword, cp.q_cha - 1);
-    for (int e = vn_edge0[v]; e < vn_edge0[v + 1]; ++e) msgs[(size_t)e * W + w] = mword;
-    nerr = __popc(slicer ^ bits);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int v = v0 + i;
+      if (v >= nvar) break;
+      cha[(size_t)v * W + w] = cword[i];
+      hard[(size_t)v * W + w] = (uint8_t)nib_bits_to_byte(cword[i], cp.q_cha - 1);
+      if (msg0) msg0[(size_t)v * W + w] = mword[i];  // on-chip regime
+      else
+        for (int e = vn_edge0[v]; e < vn_edge0[v + 1]; ++e) msgs[(size_t)e * W + w] = mword[i];
+      nerr += __popc(slicer[i] ^ bits[i]);
+    }
   }
   for (int o = 16; o; o >>= 1) nerr += __shfl_xor_sync(0xFFFFFFFFu, nerr, o);
   if ((threadIdx.x & 31) == 0 && nerr) atomicAdd(cnt_uncoded_err, (unsigned long long)nerr);
@@ -266,7 +304,9 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
   const int N = m.nvar, K = m.ninfo();
   if (!p->zero_codeword && (m.gen_cols != K || m.gen_rows != N - K))
     return h->fail(LUTLDPC_ERR_MODEL, "generator shape does not match the code");
-  int batch = p->batch_frames > 0 ? p->batch_frames : 8192;
+  // frames in flight: large batches run the decoder at its efficient point (N=64800: 32768 frames per batch decode
+  // 5 % faster per frame than 8192: fewer repacks and tail iterations per frame)
+  int batch = p->batch_frames > 0 ? p->batch_frames : 32768;
   batch = std::min(batch, h->max_batch_frames());
   batch = std::max(256, batch / 256 * 256);
   const size_t n_cnt = 8 + LUTLDPC_ITER_HIST_MAX;
@@ -280,6 +320,9 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
   cp.n_qb_cha = (int)m.qb_Cha.size(); cp.n_qb_msg = (int)m.qb_Msg.size();
   cp.use_map = h->init_mode == LUTLDPC_INIT_QCHA;
   cp.Nq_cha = m.Nq_Cha; cp.q_cha = code_bits(m.Nq_Cha); cp.Nq_msg = m.Nq_Msg[0]; cp.q_msg = code_bits(m.Nq_Msg[0]);
+  cp.sorted = 1;
+  for (size_t i = 1; i < m.qb_Cha.size(); ++i) cp.sorted &= m.qb_Cha[i - 1] < m.qb_Cha[i];
+  for (size_t i = 1; i < m.qb_Msg.size(); ++i) cp.sorted &= m.qb_Msg[i - 1] < m.qb_Msg[i];
   const uint32_t k0 = (uint32_t)p->seed, k1 = (uint32_t)(p->seed >> 32);
   int64_t total_launches = 0;
   // whole-call events (all batches); owned by the handle, so no error path can leak them
@@ -303,12 +346,12 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
       CKL("encode");
       h->launched(KIND_ENCODE);
     }
-    k_channel<<<dim3(N, gw.x), 128, 0, st>>>(h->buf_cw.p, p->zero_codeword != 0, h->g.vn_edge0, N, W, nf, first, k0, k1,
+    k_channel<<<dim3((N + 3) / 4, gw.x), 128, 0, st>>>(h->buf_cw.p, p->zero_codeword != 0, h->g.vn_edge0, N, W, nf, first, k0, k1,
                                              cp, h->d_qb_cha.p, h->d_qb_msg.p, h->d_cha2msg.p, h->b.cha, h->b.msgs,
-                                             h->b.hard, h->buf_cnt.p + 5);
+                                             h->b.hard, h->b.msg0, h->buf_cnt.p + 5);
     CKL("channel");
     h->launched(KIND_CHANNEL);
-    rc = h->run_passes(nullptr);
+    rc = h->run_decode(nullptr);
     if (rc) return rc;
     int rows_per = 64;
     k_count_data<<<dim3((K + rows_per - 1) / rows_per, gw.x), 128, 0, st>>>(h->b.hard, h->buf_cw.p, p->zero_codeword != 0,

@@ -244,6 +244,22 @@ static int cmd_fixture(const Args& a) {
   RNG_reset((unsigned)a.num("seed", 0));
   double N0 = itpp::pow10(-snr / 10.0) / C->get_rate();
   AWGN_Channel chan(N0 / 2); BPSK Mod;
+  // --llr-from <file>: channel LLRs (f64 [n][nvar], all-zero codeword) chosen elsewhere -- e.g. frames the GPU search
+  // tools/find_frames.py found to end in a rare return value -- instead of IT++'s own noise.  Quantisation, decoding
+  // and every recorded output below are still the reference's.
+  std::vector<double> llr_file;
+  if (a.has("llr-from")) {
+    std::ifstream is(a.get("llr-from").c_str(), std::ios::binary);
+    is.seekg(0, std::ios::end);
+    size_t bytes = (size_t)is.tellg();
+    is.seekg(0);
+    llr_file.resize(bytes / 8);
+    is.read((char*)llr_file.data(), (std::streamsize)(llr_file.size() * 8));
+    int avail = (int)(llr_file.size() / N), first = (int)a.num("llr-first", 0);
+    if (!is || first + (a.has("frames") ? n_frames : 0) > avail) { fprintf(stderr, "--llr-from: short file\n"); return 2; }
+    if (!a.has("frames")) n_frames = avail - first;
+    zero_cw = true;
+  }
   std::ofstream os(a.pos[1].c_str(), std::ios::binary);
   os.write("LUTFIX01", 8);
   put_i32(os, N); put_i32(os, E); put_i32(os, n_frames); put_i32(os, n_trace);
@@ -252,8 +268,15 @@ static int cmd_fixture(const Args& a) {
   for (int ff = 0; ff < n_frames; ff++) {
     bvec bitsin = zero_cw ? zeros_b(K) : randb(K);
     bvec cw = zero_cw ? zeros_b(N) : C->encode(bitsin);
-    vec x = chan(Mod.modulate_bits(cw));
-    vec llr = Mod.demodulate_soft_bits(x, N0);
+    vec llr;
+    if (!llr_file.empty()) {
+      llr.set_size(N);
+      const double* src = llr_file.data() + (size_t)((int)a.num("llr-first", 0) + ff) * N;
+      for (int i = 0; i < N; i++) llr(i) = src[i];
+    } else {
+      vec x = chan(Mod.modulate_bits(cw));
+      llr = Mod.demodulate_soft_bits(x, N0);
+    }
     ivec cha, msg; Peek::quantise(*C, llr, cha, msg);
     bvec out; int ret;
     if (ff < n_trace) {

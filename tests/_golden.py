@@ -47,3 +47,11 @@ def fixture_args(cfg, tag):
 
 def all_fixtures(skip=()):
     return [(c, t) for c in sorted(MANIFEST) for t in sorted(MANIFEST[c]["fixtures"]) if c not in skip]
+
+
+def sel_llr(cfg):
+    """Channel LLRs (float64 [frames][nvar]) of the `sel` fixture of cfg: the committed input the reference decoded
+    (tests/golden/<cfg>.sel.llr_i16.xz, cell centres of the 0.01 threshold grid; see make_sel_inputs.py)."""
+    import numpy as np
+    k = np.frombuffer(lzma.open(os.path.join(GOLD, cfg + ".sel.llr_i16.xz"), "rb").read(), "<i2")
+    return ((k.astype(np.float64) + 0.5) * 0.01).reshape(-1, MANIFEST[cfg]["design_report"]["nvar"])

@@ -52,6 +52,9 @@ CONFIGS = {
     # configs[2]: irregular N=10000
     "c3_irr_n10000": (IRR + "_N10000", "--design-thr 0.88 --max-iter 50 --qcha 4 --qmsg 4", [
         ("snr1.3", "--frames 4 --trace 0 --snr 1.3 --seed 1 --with-llr 0"),
+        # 16 frames picked on the GPU for their outcome (2 x -50, 2 x +50, late, early at two SNRs), decoded by the
+        # reference from the committed LLR input; per-iteration dumps of one failing and one converging frame
+        ("sel", "--trace 2 --with-llr 0 --llr-from c3_irr_n10000.sel.llr_i16"),
     ]),
     # configs[3]: (6,32) N=2048 with trees/6_32_high.ini (single 6-input root LUT); q_msg 2 is the
     # largest resolution the reference's own design step can build
@@ -62,6 +65,10 @@ CONFIGS = {
     # configs[4]: LUT-optimised N=64800 code
     "c5_n64800": ("rate0.50_dv02-08_dc07-08_lut_q4_N64800", "--design-thr 0.88 --max-iter 50 --qcha 4 --qmsg 4", [
         ("snr1.3", "--frames 2 --trace 0 --snr 1.3 --seed 1 --with-llr 0"),
+        # 20 frames picked on the GPU for their outcome (4 x -50, 4 x +50, late, early, typical at 1.15 and 1.3 dB),
+        # decoded by the reference from the committed LLR input; the per-iteration dumps of one failing and one
+        # converging frame (100 + ~70 records of 239023 messages) are stored as SHA-256 digests (LUTFIX02)
+        ("sel", "--trace 2 --with-llr 0 --llr-from c5_n64800.sel.llr_i16 --hash-traces"),
     ]),
     # per-iteration message resolution (LUT.qbits_messages) + LUT reuse schedule (LUT.reuse_lut)
     "x_varq_reuse": ("rate0.50_dv03_dc06_N1000",
@@ -96,6 +103,33 @@ def xz(src, dst):
         g.write(f.read())
 
 
+def expand_llr_input(name, dst):
+    """tests/golden/<name>.xz (int16 cell indices, see make_sel_inputs.py) -> float64 LLR file for --llr-from."""
+    import numpy as np
+    k = np.frombuffer(lzma.open(os.path.join(HERE, name + ".xz"), "rb").read(), "<i2")
+    ((k.astype(np.float64) + 0.5) * 0.01).astype("<f8").tofile(dst)
+
+
+def hash_traces(path):
+    """LUTFIX01 -> LUTFIX02: every trace record's message array is replaced by its SHA-256 digest (32 bytes)."""
+    import struct
+    b = open(path, "rb").read()
+    assert b[:8] == b"LUTFIX01"
+    n, e, nf, nt, with_llr, zero_cw = struct.unpack("<6i", b[8:32])
+    off = 40 + nf * ((8 * n if with_llr else 0) + 4 * n + 4)
+    out = [b"LUTFIX02", b[8:off]]
+    for _ in range(nt):
+        (nr,) = struct.unpack_from("<i", b, off)
+        out.append(b[off:off + 4])
+        off += 4
+        for _ in range(nr):
+            out.append(b[off:off + 8])
+            out.append(hashlib.sha256(b[off + 8:off + 8 + e]).digest())
+            off += 8 + e
+    assert off == len(b)
+    open(path, "wb").write(b"".join(out))
+
+
 def run(cmd):
     print("+", " ".join(cmd), flush=True)
     return subprocess.run(cmd, check=True, capture_output=True, text=True).stdout
@@ -114,6 +148,33 @@ def main():
             # LUTLDPC_PREDESIGNED=<prefix>: reuse <prefix>.it/.bundle/.log written earlier by the same
             # `design` command (the N=64800 design spends 8 min in the reference's dense rank)
             predesigned = os.environ.get("LUTLDPC_PREDESIGNED")
+            only = os.environ.get("LUTLDPC_FIXTURES_ONLY")
+            if only and name in CODEC_FOR and name in manifest:
+                # new fixtures for a config whose committed codec file stays: LUTLDPC_FIXTURES_ONLY=tag[,tag]
+                codec = os.path.join(tmp, name + ".it")
+                with open(codec, "wb") as f:
+                    f.write(lzma.open(os.path.join(HERE, name + ".codec.it.xz"), "rb").read())
+                assert sha(codec) == manifest[name]["codec_sha256"]
+                for tag, fargs in fixtures:
+                    if tag not in only.split(","):
+                        continue
+                    fx = "%s.%s.fix" % (pre, tag)
+                    fl = fargs.split()
+                    hashed = "--hash-traces" in fl
+                    if hashed:
+                        fl.remove("--hash-traces")
+                    if "--llr-from" in fl:
+                        i = fl.index("--llr-from")
+                        tmp_llr = os.path.join(tmp, "llr_in.f64")
+                        expand_llr_input(fl[i + 1], tmp_llr)
+                        fl[i + 1] = tmp_llr
+                    run([REF_BIN, "fixture", codec, fx] + fl)
+                    if hashed:
+                        hash_traces(fx)
+                    manifest[name]["fixtures"][tag] = {"args": fargs, "sha256": sha(fx), "bytes": os.path.getsize(fx)}
+                    xz(fx, os.path.join(HERE, "%s.%s.fix.xz" % (name, tag)))
+                json.dump(manifest, open(mpath, "w"), indent=1, sort_keys=True)
+                continue
             if predesigned and len(names) == 1:
                 pre = predesigned
                 info = open(pre + ".log").read().split("\n")[0]
@@ -132,8 +193,19 @@ def main():
             src = [apath] + dargs.split() if "--gen" in dargs else [pre + ".it"]
             for tag, fargs in fixtures:
                 fx = "%s.%s.fix" % (pre, tag)
-                run([REF_BIN, "fixture", src[0], fx] + src[1:] + fargs.split() +
+                fl = fargs.split()
+                hashed = "--hash-traces" in fl
+                if hashed:
+                    fl.remove("--hash-traces")
+                if "--llr-from" in fl:
+                    i = fl.index("--llr-from")
+                    tmp_llr = os.path.join(tmp, "llr_in.f64")
+                    expand_llr_input(fl[i + 1], tmp_llr)
+                    fl[i + 1] = tmp_llr
+                run([REF_BIN, "fixture", src[0], fx] + src[1:] + fl +
                     (["--init-mode", "qcha"] if qcha and "--gen" not in dargs else []))
+                if hashed:
+                    hash_traces(fx)
                 entry["fixtures"][tag] = {"args": fargs, "sha256": sha(fx), "bytes": os.path.getsize(fx)}
                 xz(fx, os.path.join(HERE, "%s.%s.fix.xz" % (name, tag)))
             manifest[name] = entry
