@@ -139,6 +139,20 @@ int lutldpc_encode(lutldpc_decoder* h, int n_frames, const uint8_t* info, uint8_
 /* syndrome_check(const bvec&), src/LDPC_Code_LUT.cpp:455-469: ok[f] = 1 iff H*bits_f == 0 */
 int lutldpc_syndrome_check(lutldpc_decoder* h, int n_frames, const uint8_t* bits, uint8_t* ok);
 
+/* Allocation-free variant of lutldpc_syndrome_check with DEVICE pointers.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The call allocates nothing (no cudaMalloc / cudaFree / allocating library
+ * routine): its scratch (bit rows, flag words, work lists) lives in a static __device__ array of
+ * LUTLDPC_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  Calls needing more fail
+ * with LUTLDPC_ERR_ARG (lutldpc_noalloc_max_frames gives the limit for the handle's code: 4096 frames at
+ * nvar = 64800, 127744 at nvar = 2048).  d_bits [n_frames][nvar] 0/1, d_ok [n_frames] = 1 iff H*bits_f == 0;
+ * asynchronous on the handle's stream.  All calls on a device share the array: calls that overlap on the GPU
+ * (different streams or handles) race; the array keeps the last call's contents and each call clears what it
+ * needs. */
+#define LUTLDPC_NOALLOC_SCRATCH_BYTES (32u << 20)
+int lutldpc_syndrome_check_device_noalloc(lutldpc_decoder* h, int n_frames, const uint8_t* d_bits, uint8_t* d_ok);
+int lutldpc_noalloc_max_frames(const lutldpc_decoder* h);
+
 /* ---- fused Monte-Carlo step == the frame loop of LDPC_BER_Sim::sim_snr_point
  * (src/LDPC_BER_Sim.cpp:246-311): source -> encode -> BPSK -> AWGN -> LLR = 4x/N0 -> quantise ->
  * lut_decode -> BERC/BLERC counting, all on the device; only the counters cross to the host. */

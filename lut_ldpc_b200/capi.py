@@ -73,7 +73,8 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_decode_quantized_device", "lutldpc_decode_llr", "lutldpc_decode_llr_device", "lutldpc_quantize",
            "lutldpc_decode_quantized_traced", "lutldpc_encode", "lutldpc_syndrome_check", "lutldpc_simulate_snr",
            "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device",
-           "lutldpc_set_repack", "lutldpc_get_repack_count", "lutldpc_set_onchip"]
+           "lutldpc_set_repack", "lutldpc_get_repack_count", "lutldpc_set_onchip", "lutldpc_syndrome_check_device_noalloc",
+           "lutldpc_noalloc_max_frames"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
                  7: "count", 8: "encode", 10: "repack", 11: "retire", 12: "onchip"}
@@ -115,6 +116,8 @@ def load_library():
     L.lutldpc_quantize_device.argtypes = [vp, i32, vp, vp, vp]
     L.lutldpc_set_profiling.argtypes = [vp, i32]
     L.lutldpc_set_onchip.argtypes = [vp, i32]
+    L.lutldpc_syndrome_check_device_noalloc.argtypes = [vp, i32, vp, vp]
+    L.lutldpc_noalloc_max_frames.argtypes = [vp]
     L.lutldpc_get_profile.argtypes = [vp, vp, vp, vp, vp]
     _lib = L
     return L
@@ -235,6 +238,15 @@ class Decoder:
         ok = np.empty(bits.shape[0], np.uint8)
         self._ck(self._L.lutldpc_syndrome_check(self._h, bits.shape[0], _p(bits), _p(ok)))
         return ok.astype(bool)
+
+    def syndrome_check_device_noalloc(self, n_frames, d_bits, d_ok):
+        """Allocation-free syndrome check on device pointers (static __device__ scratch; asynchronous on the stream)."""
+        self._ck(self._L.lutldpc_syndrome_check_device_noalloc(self._h, int(n_frames), C.c_void_p(d_bits),
+                                                               C.c_void_p(d_ok)))
+
+    @property
+    def noalloc_max_frames(self):
+        return int(self._L.lutldpc_noalloc_max_frames(self._h))
 
     # ---- decode (device pointers, e.g. torch tensors' data_ptr())
     def decode_quantized_device(self, n_frames, d_cha, d_msg, d_out, d_iters=0):
