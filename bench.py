@@ -29,7 +29,11 @@ WORKLOADS = {
                   "rate0.50_dv02-08_dc07-08_lut_q4_N64800, LUT q=4/4, max_iter 50, psc=pisc=1"),
     "c3_irr_n10000": ("c3_irr_n10000", 1.3, 32768, "rate0.50_dv02-17_dc08-09_lut_q4_N10000, LUT q=4/4, max_iter 50"),
     "c1b_reg36_n1000": ("c1b_reg36_n1000", 2.0, 65536, "rate0.50_dv03_dc06_N1000 (3,6), LUT q=4/4, max_iter 50"),
+    "c2_irr_n500": ("c2_irr_n500", 2.0, 65536, "rate0.50_dv02-17_dc08-09_lut_q4_N500, LUT q=4/4, max_iter 50 (params/ber.ini.irregular.example)"),
+    "c4_reg632_high": ("c4_reg632_high", 4.5, 65536, "rate0.84_reg_v6c32_N2048 with trees/6_32_high.ini, LUT q=4/2, max_iter 8"),
+    "c1a_reg632_wide": ("c1a_reg632_wide", 4.5, 65536, "rate0.84_reg_v6c32_N2048 with trees/6_32_wide.ini, LUT q=4/3, QCHA, max_iter 8 (params/ber.ini.regular.example)"),
 }
+SEC_PER_FRAME_EXTRA = {"c2_irr_n500": 0.013, "c4_reg632_high": 0.0064, "c1a_reg632_wide": 0.0115}
 METRIC, UNIT = "decoded_info_gbit_per_s", "Gbit/s"
 
 
@@ -115,6 +119,8 @@ def run_b200(args):
     F = args.frames or frames_def
     dec = L.Decoder(_golden.bundle_path(cfg))
     dec.set_exit_conditions(dec.max_iters, True, True)
+    if _golden.MANIFEST[cfg]["init_mode"] == "qcha":
+        dec.set_initial_message_mode(L.INIT_QCHA)
     if os.environ.get("LUTLDPC_POLL"):
         dec.set_poll_interval(int(os.environ["LUTLDPC_POLL"]))
     stream = torch.cuda.Stream()
@@ -208,18 +214,35 @@ def run_b200(args):
         if traffic is not None and tj.get("frames_per_step"):
             traffic = int(traffic * F / tj["frames_per_step"])
     step_gbs = sum_iters * b_iter * args.steps / (e0.elapsed_time(e1) * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": traffic,
-                "traffic_source": "profiles/traffic.json (ncu --set full capture of one all-frames-live launch, static; "
-                                  "scaled to this run's frames per step)",
-                "algorithmic_bytes": "SURVEY 8(d): check pass E, variable pass E + N/2 bytes per frame-pass "
-                                     "(the N/8 hard-decision bytes a variable pass also writes are not counted)",
-                "peak_source": peak_src,
-                "kernel_ms_per_launch": round(dom_ms / max(1, prof[dom][1]), 4),
-                "whole_step_algorithmic_gbs": round(step_gbs, 1), "whole_step_frac": round(step_gbs / peak, 4),
-                "profiled_pass_ms_per_step": round(profiled_ms / args.steps, 3),
-                "profile_ms": {k: round(v[0], 3) for k, v in prof.items()},
-                "kernel_share_of_step": {k: round(v[0] / sum(x[0] for x in prof.values()), 4) for k, v in prof.items()}}
+    if dom == "onchip":
+        # on-chip regime (second bound): the same algorithmic message bytes, 2E + N/2 per frame-iteration,
+        # move through shared memory instead of HBM; peak = 128 B per clock and SM at the maximum SM clock
+        smem_peak = 148 * 128 * (clocks["sm_max_mhz"] or 1965.0) * 1e6 / 1e9
+        alg = b_iter * sum_iters * args.steps
+        achieved = alg / (dom_ms * 1e-3) / 1e9
+        roofline = {"bound": "smem", "kernel": "k_onchip (whole lut_decode of a batch, state in shared memory)",
+                    "achieved": round(achieved, 1), "peak": round(smem_peak, 1), "unit": "GB/s",
+                    "frac": round(achieved / smem_peak, 4), "traffic": None,
+                    "peak_source": "148 SMs x 128 B/clk shared-memory bandwidth x max SM clock (B200_PROFILING.md)",
+                    "algorithmic_bytes": "SURVEY 8(d): 2E + N/2 message bytes per frame-iteration, through shared memory; "
+                                         "LUT look-ups (one LDS.U8 per frame-look-up) come on top and are the actual limit: "
+                                         "see profiles/ for lsu wavefronts and issue utilisation",
+                    "hbm_bytes_per_frame": 3 * N + 4, "kernel_ms_per_launch": round(dom_ms / max(1, prof[dom][1]), 4),
+                    "profile_ms": {k: round(v[0], 3) for k, v in prof.items()},
+                    "kernel_share_of_step": {k: round(v[0] / sum(x[0] for x in prof.values()), 4) for k, v in prof.items()}}
+    else:
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                  "frac": round(achieved / peak, 4), "traffic": traffic,
+                  "traffic_source": "profiles/traffic.json (ncu --set full capture of one all-frames-live launch, static; "
+                                    "scaled to this run's frames per step)",
+                  "algorithmic_bytes": "SURVEY 8(d): check pass E, variable pass E + N/2 bytes per frame-pass "
+                                       "(the N/8 hard-decision bytes a variable pass also writes are not counted)",
+                  "peak_source": peak_src,
+                  "kernel_ms_per_launch": round(dom_ms / max(1, prof[dom][1]), 4),
+                  "whole_step_algorithmic_gbs": round(step_gbs, 1), "whole_step_frac": round(step_gbs / peak, 4),
+                  "profiled_pass_ms_per_step": round(profiled_ms / args.steps, 3),
+                  "profile_ms": {k: round(v[0], 3) for k, v in prof.items()},
+                  "kernel_share_of_step": {k: round(v[0] / sum(x[0] for x in prof.values()), 4) for k, v in prof.items()}}
 
     # ---- end to end through the host-buffer C-ABI call (pinned host memory)
     cha_h = torch.empty((F, N), dtype=torch.uint8, pin_memory=True)
@@ -285,6 +308,29 @@ def run_b200(args):
            "call": "ber_sim.py LDPC_BER_Sim_LUT.sim_snr_point -> lutldpc_simulate_snr (Philox4x32-10 AWGN, quantiser, "
                    "lut_decode, error counting on the device) + all_reduce(SUM) of 264 int64 counters per step"}
 
+    # ---- the same batch through the packed host entry point (one byte per symbol in, one bit per decision out)
+    both_h = torch.empty((F, N), dtype=torch.uint8, pin_memory=True)
+    both_h.copy_(cha_h | (msg_h << 4))
+    NB = (N + 7) // 8
+    pk_h = torch.empty((F, NB), dtype=torch.uint8, pin_memory=True)
+    both_np, pk_np = both_h.numpy(), pk_h.numpy()
+    dec.decode_packed(both_np, out=pk_np, iters=i_np)  # warm-up
+    barrier()
+    t0 = time.perf_counter()
+    e0.record(stream)
+    for _ in range(e2e_steps):
+        dec.decode_packed(both_np, out=pk_np, iters=i_np)
+    e1.record(stream)
+    barrier()
+    pk_ms = max_over_ranks(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3))
+    assert np.array_equal(i_np, it_host), "packed host path and device path disagree"
+    assert np.array_equal(np.packbits(o_np[:64], axis=1, bitorder="little"), pk_np[:64])
+    e2e_packed = {"value": round(sum_over_ranks(F) * e2e_steps * K / (pk_ms * 1e-3) / 1e9, 4), "unit": UNIT,
+                  "h2d_bytes_per_step": int(F * N) * world, "d2h_bytes_per_step": int(F * NB + 4 * F) * world,
+                  "steps": e2e_steps,
+                  "call": "lutldpc_decode_packed (pinned host: cha | msg << 4 per symbol in, bit-packed decisions + "
+                          "iteration counts out): the same decode with 2.65x fewer bytes across PCIe"}
+
     line = {"metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u4 (8 codes per u32, SWAR)", "data": "synthetic",
@@ -294,7 +340,7 @@ def run_b200(args):
                      "mean_iterations": round(sum_iters / F, 2), "decode_failures": int((it_host < 0).sum()),
                      "frame_errors": int(wrong.sum()), "undetected_frame_errors": int((wrong & (it_host >= 0)).sum()),
                      "edge_updates_per_s": round(2.0 * E * sum_iters_all * args.steps / (ms * 1e-3), 1)},
-            "roofline": roofline, "sim": sim, "clocks": clocks, "gpu_launches": int(launches),
+            "roofline": roofline, "sim": sim, "e2e_packed": e2e_packed, "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": round(e2e_value, 4), "unit": UNIT, "h2d_bytes_per_step": int(2 * F * N) * world,
                     "d2h_bytes_per_step": int(F * N + 4 * F) * world, "steps": e2e_steps,
                     "call": "lutldpc_decode_quantized (pinned host u8 labels in, bits + iteration counts out; chunks pipelined over copy and decode streams)"}}
@@ -313,7 +359,7 @@ def run_b200(args):
 # there, the plain-C port in oracle/ is timed instead ("kind": "port").
 # ------------------------------------------------------------------------------------------------
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "lutldpc_ref")
-SEC_PER_FRAME = {"c5_n64800": 1.9, "c3_irr_n10000": 0.7, "c1b_reg36_n1000": 0.025}  # SURVEY.md 6.2, one core
+SEC_PER_FRAME = {"c5_n64800": 1.9, "c3_irr_n10000": 0.7, "c1b_reg36_n1000": 0.025, **SEC_PER_FRAME_EXTRA}  # SURVEY.md 6.2, one core
 
 
 def _ref_sample(workload, snr, frames_per_proc, procs, seed0=0):
@@ -338,14 +384,14 @@ def _port_worker(a):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import numpy as np
     import pyoracle
-    bundle, snr, frames, seed = a
+    bundle, snr, frames, seed, qcha = a
     orc = pyoracle.Oracle(bundle)
     orc.set_exit_conditions(orc.max_iters, True, True)
     rate = orc.ninfo / orc.nvar
     N0 = 10.0 ** (-snr / 10.0) / rate
     rng = np.random.default_rng(seed)
     llr = (1.0 + (N0 / 2) ** 0.5 * rng.standard_normal((frames, orc.nvar))) * 4.0 / N0
-    cha, msg = orc.quantise(llr)
+    cha, msg = orc.quantise(llr, pyoracle.INIT_QCHA if qcha else pyoracle.INIT_CONT)
     t0 = time.perf_counter()
     orc.lut_decode_batch(cha, msg)
     return time.perf_counter() - t0
@@ -355,14 +401,16 @@ def _port_sample(workload, snr, frames_per_proc, procs, seed0=0):
     import multiprocessing as mp
     import _golden
     bundle = _golden.bundle_path(WORKLOADS[workload][0])
+    qcha = _golden.MANIFEST[WORKLOADS[workload][0]]["init_mode"] == "qcha"
     with mp.get_context("spawn").Pool(procs) as pool:
-        walls = pool.map(_port_worker, [(bundle, snr, frames_per_proc, seed0 + i) for i in range(procs)])
+        walls = pool.map(_port_worker, [(bundle, snr, frames_per_proc, seed0 + i, qcha) for i in range(procs)])
     return frames_per_proc * procs, max(walls), []
 
 
-def _cpu_kind():
+def _cpu_kind(workload):
+    """The compiled reference when it and the workload's reference-written codec file are there, else the C port."""
     import _golden
-    have = os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)
+    have = os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK) and "codec_sha256" in _golden.MANIFEST[WORKLOADS[workload][0]]
     return ("reference", _ref_sample) if have else ("port", _port_sample)
 
 
@@ -372,7 +420,7 @@ def _ninfo(workload):
 
 
 def cpu_baseline(workload, snr, seconds=15.0):
-    kind, fn = _cpu_kind()
+    kind, fn = _cpu_kind(workload)
     procs = os.cpu_count() or 1
     per = max(1, int(seconds / SEC_PER_FRAME.get(workload, 1.0)))
     frames, wall, _ = fn(workload, snr, per, procs)
@@ -388,7 +436,7 @@ def run_reference(args):
         return
     cfg, snr_def, frames_def, desc = WORKLOADS[args.workload]
     snr = args.snr if args.snr is not None else snr_def
-    kind, fn = _cpu_kind()
+    kind, fn = _cpu_kind(args.workload)
     procs = os.cpu_count() or 1
     per = max(1, int(args.ref_seconds_per_step / SEC_PER_FRAME.get(args.workload, 1.0)))
     for i in range(args.warmup):

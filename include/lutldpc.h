@@ -114,6 +114,16 @@ int lutldpc_decode_quantized(lutldpc_decoder* h, int n_frames, const uint8_t* ll
  * poll_every == 0: all max_iters iterations are enqueued, finished frames idle). */
 int lutldpc_decode_quantized_device(lutldpc_decoder* h, int n_frames, const uint8_t* d_llr_cha,
                                     const uint8_t* d_llr_msg, uint8_t* d_out_bits, int32_t* d_out_iters);
+/* Packed form of lutldpc_decode_quantized (same decoder, same results; no counterpart in the reference, whose
+ * containers spend an int per label and a byte per bit): 73 KB instead of 194 KB per N=64800 frame across PCIe.
+ *   cha_msg          [n_frames][nvar]  one byte per symbol: LLRin_cha label in the low nibble, LLRin_msg label in the high
+ *   out_bits_packed  [n_frames][ceil(nvar/8)]  LLRout, bit (v & 7) of byte v >> 3 = decision of variable node v
+ *   out_iters        [n_frames] lut_decode's return (may be NULL for the _device form)
+ * Host pointers (pinned memory makes the copies asynchronous) / device pointers as for lutldpc_decode_quantized. */
+int lutldpc_decode_packed(lutldpc_decoder* h, int n_frames, const uint8_t* cha_msg, uint8_t* out_bits_packed,
+                          int32_t* out_iters);
+int lutldpc_decode_packed_device(lutldpc_decoder* h, int n_frames, const uint8_t* d_cha_msg, uint8_t* d_out_bits_packed,
+                                 int32_t* d_out_iters);
 /* lutldpc_decode_llr == LDPC_Code_LUT::decode(const vec& llr_in, bvec& syst_bits)
  * (src/LDPC_Code_LUT.cpp:204-239): quant_nonlin front end (src/common.cpp:120-138) + lut_decode.
  *   llr [n_frames][nvar] doubles;  out_bits [n_frames][nvar];  out_iters may be NULL. */

@@ -73,8 +73,8 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_decode_quantized_device", "lutldpc_decode_llr", "lutldpc_decode_llr_device", "lutldpc_quantize",
            "lutldpc_decode_quantized_traced", "lutldpc_encode", "lutldpc_syndrome_check", "lutldpc_simulate_snr",
            "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device",
-           "lutldpc_set_repack", "lutldpc_get_repack_count", "lutldpc_set_onchip", "lutldpc_syndrome_check_device_noalloc",
-           "lutldpc_noalloc_max_frames"]
+           "lutldpc_set_repack", "lutldpc_get_repack_count", "lutldpc_syndrome_check_device_noalloc",
+           "lutldpc_noalloc_max_frames", "lutldpc_set_onchip", "lutldpc_decode_packed", "lutldpc_decode_packed_device"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
                  7: "count", 8: "encode", 10: "repack", 11: "retire", 12: "onchip"}
@@ -115,9 +115,11 @@ def load_library():
     L.lutldpc_last_call_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64)]
     L.lutldpc_quantize_device.argtypes = [vp, i32, vp, vp, vp]
     L.lutldpc_set_profiling.argtypes = [vp, i32]
-    L.lutldpc_set_onchip.argtypes = [vp, i32]
     L.lutldpc_syndrome_check_device_noalloc.argtypes = [vp, i32, vp, vp]
     L.lutldpc_noalloc_max_frames.argtypes = [vp]
+    L.lutldpc_set_onchip.argtypes = [vp, i32]
+    L.lutldpc_decode_packed.argtypes = [vp, i32, vp, vp, vp]
+    L.lutldpc_decode_packed_device.argtypes = [vp, i32, vp, vp, vp]
     L.lutldpc_get_profile.argtypes = [vp, vp, vp, vp, vp]
     _lib = L
     return L
@@ -198,6 +200,22 @@ class Decoder:
         assert it.dtype == np.int32 and it.shape == (cha.shape[0],) and it.flags.c_contiguous
         self._ck(self._L.lutldpc_decode_quantized(self._h, cha.shape[0], _p(cha), _p(msg), _p(out), _p(it)))
         return out, it
+
+    def decode_packed(self, cha_msg, out=None, iters=None):
+        """lut_decode on packed host buffers: cha_msg [F, nvar] u8 = cha label | msg label << 4; returns the bit-packed
+        decisions [F, ceil(nvar/8)] (numpy.unpackbits(..., bitorder="little") gives LLRout) and the returns."""
+        cha_msg = np.ascontiguousarray(cha_msg, np.uint8).reshape(-1, self.nvar)
+        nb = (self.nvar + 7) // 8
+        out = np.empty((cha_msg.shape[0], nb), np.uint8) if out is None else out
+        it = np.empty(cha_msg.shape[0], np.int32) if iters is None else iters
+        assert out.dtype == np.uint8 and out.shape == (cha_msg.shape[0], nb) and out.flags.c_contiguous
+        assert it.dtype == np.int32 and it.shape == (cha_msg.shape[0],) and it.flags.c_contiguous
+        self._ck(self._L.lutldpc_decode_packed(self._h, cha_msg.shape[0], _p(cha_msg), _p(out), _p(it)))
+        return out, it
+
+    def decode_packed_device(self, n_frames, d_cha_msg, d_out, d_iters=0):
+        self._ck(self._L.lutldpc_decode_packed_device(self._h, int(n_frames), C.c_void_p(d_cha_msg), C.c_void_p(d_out),
+                                                      C.c_void_p(d_iters or None)))
 
     def decode_quantized_traced(self, cha, msg, trace_frame, max_rec):
         cha = np.ascontiguousarray(cha, np.uint8).reshape(-1, self.nvar)

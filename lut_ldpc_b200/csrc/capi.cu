@@ -282,11 +282,13 @@ static std::vector<int> host_chunk_plan(lutldpc_decoder* h, int n_frames, bool s
   return plan;
 }
 
+// packed: `cha` holds both labels of a symbol in one byte (msg == nullptr) and out_bits is bit-packed, NB bytes per frame
 static int decode_host(lutldpc_decoder* h, int n_frames, const uint8_t* cha, const uint8_t* msg, const double* llr,
-                       uint8_t* out_bits, int32_t* out_iters, TraceSink* tr) {
+                       uint8_t* out_bits, int32_t* out_iters, TraceSink* tr, bool packed = false) {
   CKH(cudaSetDevice(h->device), "cudaSetDevice");
   if (n_frames == 0) return LUTLDPC_OK;
   const int N = h->m.nvar;
+  const size_t out_per_frame = packed ? (size_t)(N + 7) / 8 : (size_t)N;
   const std::vector<int> plan = host_chunk_plan(h, n_frames, tr != nullptr);
   const int n_chunks = (int)plan.size();
   std::vector<int> first(n_chunks + 1, 0);
@@ -310,7 +312,7 @@ static int decode_host(lutldpc_decoder* h, int n_frames, const uint8_t* cha, con
   const size_t cap = (size_t)std::min(chunk, n_frames) * N;
   for (int i = 0; i < (n_chunks > 1 ? 2 : 1); ++i) {
     CKH(hp.lab_cha[i].ensure(cap), "alloc labels");
-    CKH(hp.lab_msg[i].ensure(cap), "alloc labels");
+    if (!packed) CKH(hp.lab_msg[i].ensure(cap), "alloc labels");
     CKH(hp.out[i].ensure(cap), "alloc out");
     CKH(hp.its[i].ensure((size_t)std::min(chunk, n_frames)), "alloc iters");
     if (llr) CKH(hp.llr[i].ensure(cap), "alloc llr");
@@ -326,7 +328,8 @@ static int decode_host(lutldpc_decoder* h, int n_frames, const uint8_t* cha, con
       CKH(cudaMemcpyAsync(hp.llr[slot].p, llr + (size_t)f0 * N, cnt * 8, cudaMemcpyHostToDevice, hp.s_in), "H2D llr");
     } else {
       CKH(cudaMemcpyAsync(hp.lab_cha[slot].p, cha + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, hp.s_in), "H2D cha");
-      CKH(cudaMemcpyAsync(hp.lab_msg[slot].p, msg + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, hp.s_in), "H2D msg");
+      if (!packed)
+        CKH(cudaMemcpyAsync(hp.lab_msg[slot].p, msg + (size_t)f0 * N, cnt, cudaMemcpyHostToDevice, hp.s_in), "H2D msg");
     }
     CKH(cudaEventRecord(hp.ev_in[slot], hp.s_in), "event");
     return LUTLDPC_OK;
@@ -344,19 +347,21 @@ static int decode_host(lutldpc_decoder* h, int n_frames, const uint8_t* cha, con
                           hp.lab_cha[slot].p, hp.lab_msg[slot].p, st), "quantize");
     static const bool trace_host = getenv("LUTLDPC_HOST_TRACE") != nullptr;
     const auto t_a = std::chrono::steady_clock::now();
-    rc = h->run_batch(nf, hp.lab_cha[slot].p, hp.lab_msg[slot].p, tr);
+    rc = h->run_batch(nf, hp.lab_cha[slot].p, packed ? nullptr : hp.lab_msg[slot].p, tr);
     if (rc) return rc;
     if (trace_host)
       fprintf(stderr, "host chunk %d frames %d run_batch %.3f ms\n", c, nf,
               std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_a).count());
     CKH(cudaEventRecord(hp.ev_used[slot], st), "event");
     if (c >= 2) CKH(cudaStreamWaitEvent(st, hp.ev_out[slot], 0), "wait");  // results of chunk c-2 have left
-    CKH(launch_unpack(h->g, h->b, hp.out[slot].p, st), "unpack");
+    if (packed) CKH(launch_unpack_bits(h->g, h->b, hp.out[slot].p, st), "unpack_bits");
+    else CKH(launch_unpack(h->g, h->b, hp.out[slot].p, st), "unpack");
     h->launched(KIND_UNPACK);
     CKH(cudaMemcpyAsync(hp.its[slot].p, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToDevice, st), "iters copy");
     CKH(cudaEventRecord(hp.ev_dec[slot], st), "event");
     CKH(cudaStreamWaitEvent(hp.s_out, hp.ev_dec[slot], 0), "wait");
-    CKH(cudaMemcpyAsync(out_bits + (size_t)f0 * N, hp.out[slot].p, cnt, cudaMemcpyDeviceToHost, hp.s_out), "D2H bits");
+    CKH(cudaMemcpyAsync(out_bits + (size_t)f0 * out_per_frame, hp.out[slot].p, (size_t)nf * out_per_frame,
+                        cudaMemcpyDeviceToHost, hp.s_out), "D2H bits");
     if (out_iters)
       CKH(cudaMemcpyAsync(out_iters + f0, hp.its[slot].p, (size_t)nf * 4, cudaMemcpyDeviceToHost, hp.s_out), "D2H iters");
     CKH(cudaEventRecord(hp.ev_out[slot], hp.s_out), "event");
@@ -371,6 +376,31 @@ int lutldpc_decode_quantized(lutldpc_decoder* h, int n_frames, const uint8_t* ch
   int rc = check_decode_args(h, n_frames, cha, msg, out_bits);
   if (rc) return rc;
   return decode_host(h, n_frames, cha, msg, nullptr, out_bits, out_iters, nullptr);
+}
+
+int lutldpc_decode_packed(lutldpc_decoder* h, int n_frames, const uint8_t* cha_msg, uint8_t* out_bits_packed,
+                          int32_t* out_iters) {
+  int rc = check_decode_args(h, n_frames, cha_msg, cha_msg, out_bits_packed);
+  if (rc) return rc;
+  return decode_host(h, n_frames, cha_msg, nullptr, nullptr, out_bits_packed, out_iters, nullptr, true);
+}
+
+int lutldpc_decode_packed_device(lutldpc_decoder* h, int n_frames, const uint8_t* d_cha_msg, uint8_t* d_out_bits_packed,
+                                 int32_t* d_out_iters) {
+  int rc = check_decode_args(h, n_frames, d_cha_msg, d_cha_msg, d_out_bits_packed);
+  if (rc) return rc;
+  CKH(cudaSetDevice(h->device), "cudaSetDevice");
+  const int N = h->m.nvar, NB = (N + 7) / 8, maxb = h->max_batch_frames();
+  for (int f0 = 0; f0 < n_frames; f0 += maxb) {
+    int nf = std::min(maxb, n_frames - f0);
+    rc = h->run_batch(nf, d_cha_msg + (size_t)f0 * N, nullptr, nullptr);
+    if (rc) return rc;
+    CKH(launch_unpack_bits(h->g, h->b, d_out_bits_packed + (size_t)f0 * NB, h->stream), "unpack_bits");
+    h->launched(KIND_UNPACK);
+    if (d_out_iters)
+      CKH(cudaMemcpyAsync(d_out_iters + f0, h->b.iters, (size_t)nf * 4, cudaMemcpyDeviceToDevice, h->stream), "iters copy");
+  }
+  return LUTLDPC_OK;
 }
 
 int lutldpc_decode_quantized_traced(lutldpc_decoder* h, int n_frames, const uint8_t* cha, const uint8_t* msg,

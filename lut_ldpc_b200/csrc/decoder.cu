@@ -366,7 +366,7 @@ int lutldpc_decoder::run_onchip() {
   P.W = b.W;
   P.cha = b.cha; P.msg0 = b.msg0; P.hard = b.hard; P.iters = b.iters; P.done = b.done;
   P.psc = psc; P.pisc = pisc;
-  CK(launch_onchip(P, oc_max_fast_dv, oc_threads, oc_ctas, stream), "onchip");
+  CK(launch_onchip(P, oc_max_fast_dv, oc_ctas, stream), "onchip");
   launched(KIND_ONCHIP);
   CK(cudaEventRecord(ev1, stream), "event");
   have_stats = true;
@@ -375,9 +375,9 @@ int lutldpc_decoder::run_onchip() {
   return LUTLDPC_OK;
 }
 
-// Set-up of the on-chip regime.  A decoder qualifies when its checks are min-sum, and the state of one word column
-// (E message words with the bank skew, N channel words, N hard bytes), one slot of program images and the value
-// slots of the interpreted programs fit the shared memory of a CTA at least twice per SM.
+// Set-up of the on-chip regime.  A decoder qualifies when its checks are min-sum and the state of one word column
+// (E message words with the bank skew, N channel words, N hard bytes) is small enough that a CTA holding a few columns,
+// one slot of program images and the interpreter's value slots fits shared memory at least twice per SM.
 int lutldpc_decoder::init_onchip() {
   onchip_ok = onchip_fits = false;
   if (!m.minLUT) return LUTLDPC_OK;
@@ -402,6 +402,7 @@ int lutldpc_decoder::init_onchip() {
   memset(&oc, 0, sizeof oc);
   std::vector<uint32_t> it_sz(cls.size(), 0), dec_sz(cls.size(), 0);
   int n_slots_max = 0;
+  bool any_interp_vn = false;
   oc_max_fast_dv = 0;
   for (size_t k = 0; k < cls.size(); ++k) {
     const int c = cls[k];
@@ -412,6 +413,7 @@ int lutldpc_decoder::init_onchip() {
       fast &= r.fast_dv != 0;
     }
     for (int t = 0; t < dec_slot && !fast; ++t) n_slots_max = std::max(n_slots_max, (int)var_progs[(size_t)t * nvc + c].n_slots);
+    any_interp_vn |= !fast;
     const ProgRef& rd = var_progs[(size_t)dec_slot * nvc + c];
     dec_sz[k] = rd.bytes;
     n_slots_max = std::max(n_slots_max, (int)rd.n_slots);
@@ -429,21 +431,32 @@ int lutldpc_decoder::init_onchip() {
   oc.n_vc = (int)cls.size();
   oc.slot_bytes = off; oc.dec_bytes = doff;
   oc.slot_stride = std::max(off, doff);
-  oc_threads = m.nvar <= 1536 ? 128 : 256;
-  const size_t tab_bytes = oc.slot_stride, slots_bytes = al((size_t)n_slots_max * oc_threads * 4, 128);
+  // interpreted variable passes need value slots for every thread; the (rare) decision pass runs on two warps' worth
+  oc.slot_threads = any_interp_vn ? kOnchipThreads : 64;
+  const size_t tab_bytes = oc.slot_stride, slots_bytes = al((size_t)n_slots_max * oc.slot_threads * 4, 128);
+  // columns per CTA: as many as leave room for about four CTAs per SM (LUTLDPC_ONCHIP_COLS overrides)
+  const size_t fixed = tab_bytes + slots_bytes;
+  CK(configure_onchip(), "configure onchip kernel");
+  const int by_regs = std::max(1, onchip_ctas_per_sm(oc_max_fast_dv, 0));  // CTAs per SM the register file allows
+  const size_t target = (size_t)kOnchipMaxSmem / std::max(1, std::min(by_regs, env_int("LUTLDPC_ONCHIP_CTAS", 4)));
+  int C = target > fixed ? (int)((target - fixed) / oc_state_bytes) : 0;
+  C = std::max(1, std::min(kOnchipMaxCols, C));
+  if (int v = env_int("LUTLDPC_ONCHIP_COLS", 0)) C = std::max(1, std::min(kOnchipMaxCols, v));
+  while (C > 1 && fixed + (size_t)C * oc_state_bytes > (size_t)kOnchipMaxSmem) --C;
+  oc.C = C;
+  oc.col_bytes = (uint32_t)oc_state_bytes;
   oc.off_cha = (uint32_t)msgs_bytes;
   oc.off_hard = (uint32_t)(msgs_bytes + cha_bytes);
-  oc.off_tab = (uint32_t)oc_state_bytes;
-  oc.off_slots = (uint32_t)(oc_state_bytes + tab_bytes);
-  oc.smem_bytes = (uint32_t)(oc_state_bytes + tab_bytes + slots_bytes);
+  oc.off_tab = (uint32_t)((size_t)C * oc_state_bytes);
+  oc.off_slots = (uint32_t)(oc.off_tab + tab_bytes);
+  oc.smem_bytes = (uint32_t)(oc.off_slots + slots_bytes);
   if (oc.smem_bytes > (uint32_t)kOnchipMaxSmem) return LUTLDPC_OK;
-  CK(configure_onchip(), "configure onchip kernel");
-  oc_ctas_per_sm = onchip_ctas_per_sm(oc_max_fast_dv, oc_threads, oc.smem_bytes);
-  if (oc_ctas_per_sm < 2) return LUTLDPC_OK;
+  oc_ctas_per_sm = onchip_ctas_per_sm(oc_max_fast_dv, oc.smem_bytes);
+  if (oc_ctas_per_sm < 1 || oc_ctas_per_sm * C < 2) return LUTLDPC_OK;
   int sms = 0;
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device), "device attribute");
   oc_ctas = sms * oc_ctas_per_sm;
-  // upload: slot images, iteration tables, check rows
+  // upload: slot images, iteration tables, check rows, work items
   std::vector<uint8_t> host_blob((size_t)d_prog_blob.n);
   CK(cudaMemcpy(host_blob.data(), d_prog_blob.p, host_blob.size(), cudaMemcpyDeviceToHost), "read back programs");
   std::vector<uint8_t> images((size_t)n_iter_slots * oc.slot_stride, 0);
@@ -469,6 +482,26 @@ int lutldpc_decoder::init_onchip() {
   }
   for (size_t k = 0; k < oc_cn.size(); ++k) oc.cc[k] = OnchipCn{oc_cn[k].list.p, oc_cn[k].n, oc_cn[k].degree};
   oc.n_cc = (int)oc_cn.size();
+  // work items: 32 nodes of a class, the most expensive class first (its units are handed out first)
+  std::vector<std::pair<int64_t, int4>> vi, ci;
+  for (size_t k = 0; k < cls.size(); ++k) {
+    const int64_t cost = std::max<int64_t>(1, var_progs[cls[k]].n_ops);
+    for (int f = 0; f < oc.vc[k].n; f += 32) vi.push_back({cost, make_int4((int)k, f, std::min(32, oc.vc[k].n - f), 0)});
+  }
+  for (size_t k = 0; k < oc_cn.size(); ++k)
+    for (int f = 0; f < oc_cn[k].n; f += 32) ci.push_back({oc_cn[k].degree, make_int4((int)k, f, std::min(32, oc_cn[k].n - f), 0)});
+  auto by_cost = [](const std::pair<int64_t, int4>& a, const std::pair<int64_t, int4>& b2) { return a.first > b2.first; };
+  std::stable_sort(vi.begin(), vi.end(), by_cost);
+  std::stable_sort(ci.begin(), ci.end(), by_cost);
+  std::vector<int4> flat;
+  for (auto& x : vi) flat.push_back(x.second);
+  oc.n_vn_items = (int)flat.size();
+  CK(d_oc_vn_items.upload(flat), "upload vn items");
+  flat.clear();
+  for (auto& x : ci) flat.push_back(x.second);
+  oc.n_cn_items = (int)flat.size();
+  CK(d_oc_cn_items.upload(flat), "upload cn items");
+  oc.vn_items = d_oc_vn_items.p; oc.cn_items = d_oc_cn_items.p;
   oc.slot_images = d_oc_images.p;
   oc.iter_slot = d_oc_iter_slot.p; oc.iter_q = d_oc_iter_q.p;
   oc.max_iters = m.max_iters; oc.dec_slot = dec_slot; oc.q_cha = code_bits(m.Nq_Cha);
@@ -476,7 +509,12 @@ int lutldpc_decoder::init_onchip() {
   oc.vn_edge0 = d_vn_edge0.p; oc.cn_start = d_cn_start.p; oc.chk_equ_idx = d_chk_equ_idx.p;
   oc.queue = d_oc_queue.p;
   onchip_fits = true;
-  onchip_ok = env_int("LUTLDPC_ONCHIP", 1) != 0;
+  // Default: on chip only where it was measured faster than the HBM regime -- compile-time variable programs of degree
+  // <= 8 for every class (the (3,6) N=1000 decoder: 4.9 against 4.45 Gbit/s).  Interpreted trees (file templates,
+  // 2- and 3-bit messages) and high degrees (113-233 registers per thread: one CTA per SM) run 0.4-0.6x as fast on
+  // chip as through HBM; they take the regime only on request (lutldpc_set_onchip, LUTLDPC_ONCHIP=2).
+  const int mode = env_int("LUTLDPC_ONCHIP", 1);
+  onchip_ok = mode == 2 || (mode == 1 && !any_interp_vn && oc_max_fast_dv <= 8);
   return LUTLDPC_OK;
 }
 

@@ -129,9 +129,10 @@ struct lutldpc_decoder {
   lutldpc::DevBuf<uint8_t> d_oc_images;
   lutldpc::DevBuf<int32_t> d_oc_iter_slot, d_oc_iter_q;
   lutldpc::DevBuf<unsigned int> d_oc_queue;
+  lutldpc::DevBuf<int4> d_oc_vn_items, d_oc_cn_items;
   std::vector<lutldpc::NodeClass> oc_cn;  // checks by degree, list = edge rows [n][degree] (any degree)
   lutldpc::DevBuf<uint32_t> buf_msg0;
-  int oc_threads = 0, oc_ctas = 0, oc_ctas_per_sm = 0, oc_max_fast_dv = 0;
+  int oc_ctas = 0, oc_ctas_per_sm = 0, oc_max_fast_dv = 0;
   size_t oc_state_bytes = 0;
 
   // batch state

@@ -26,7 +26,9 @@ __device__ __forceinline__ uint32_t lab2code(uint32_t m, int Nq, int q) {
 // Tile = 32 variable nodes x 256 frames through shared memory so that reads are 32-byte sectors of a
 // frame row and writes are 128-byte lines of an edge row.
 // ---------------------------------------------------------------------------------------------
-template <bool VEC4>
+// PACKED: one byte per (frame, node) with the channel label in the low and the message label in the high nibble
+// (cha_lab; msg_lab unused) instead of one byte per label: half the bytes across PCIe (lutldpc_decode_packed).
+template <bool VEC4, bool PACKED>
 __global__ void __launch_bounds__(256) k_pack(const uint8_t* __restrict__ cha_lab, const uint8_t* __restrict__ msg_lab,
                                               const int32_t* __restrict__ vn_edge0, int nvar, int F, int W,
                                               int Nq_cha, int q_cha, int Nq_msg, int q_msg,
@@ -46,7 +48,12 @@ __global__ void __launch_bounds__(256) k_pack(const uint8_t* __restrict__ cha_la
       const bool in = f < F && v < nvar;
       if (in) {
         c4 = *reinterpret_cast<const uint32_t*>(cha_lab + (size_t)f * nvar + v);
-        m4 = *reinterpret_cast<const uint32_t*>(msg_lab + (size_t)f * nvar + v);
+        if (PACKED) {
+          m4 = (c4 >> 4) & 0x0F0F0F0Fu;
+          c4 &= 0x0F0F0F0Fu;
+        } else {
+          m4 = *reinterpret_cast<const uint32_t*>(msg_lab + (size_t)f * nvar + v);
+        }
       }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -63,7 +70,12 @@ __global__ void __launch_bounds__(256) k_pack(const uint8_t* __restrict__ cha_la
       bool in = f < F && v < nvar;
       if (in) {
         c = cha_lab[(size_t)f * nvar + v];
-        m = msg_lab[(size_t)f * nvar + v];
+        if (PACKED) {
+          m = c >> 4;
+          c &= 0xF;
+        } else {
+          m = msg_lab[(size_t)f * nvar + v];
+        }
       }
       t[fl][tx] = in ? (uint8_t)(lab2code(c, Nq_cha, q_cha) | (lab2code(m, Nq_msg, q_msg) << 4)) : 0;
     }
@@ -869,6 +881,45 @@ __global__ void __launch_bounds__(256) k_unpack(const uint8_t* __restrict__ hard
   }
 }
 
+// hard[nvar][W] -> out[F][NB] bit-packed rows, NB = ceil(nvar / 8), bit (v & 7) of byte v >> 3 = decision of node v
+// (lutldpc_decode_packed: an eighth of the bytes of the one-byte-per-bit form).  Tile = 256 nodes x 32 words (256
+// frames) through shared memory: reads are 32-byte sectors of a node row, writes 32-byte pieces of a frame row; in
+// between every thread transposes 8 x 8 bit blocks (8 nodes x 8 frames).
+__global__ void __launch_bounds__(256) k_unpack_bits(const uint8_t* __restrict__ hard, int nvar, int F, int W, int NB,
+                                                     uint8_t* __restrict__ out) {
+  __shared__ uint8_t t[256][33];  // [node of the tile][word of the tile]
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int v0 = blockIdx.x * 256, w0 = blockIdx.y * 32;
+  for (int vi = ty; vi < 256; vi += 8) {
+    const int v = v0 + vi, w = w0 + tx;
+    t[vi][tx] = (v < nvar && w < W) ? hard[(size_t)v * W + w] : 0;
+  }
+  __syncthreads();
+  // thread = (node group g of 8 nodes, word wl): 8 bytes in (one per node, bit j = frame j), 8 bytes out (one per frame)
+  for (int item = threadIdx.x; item < 32 * 32; item += 256) {
+    const int g = item & 31, wl = item >> 5;
+    uint32_t lo = 0, hi = 0;  // nodes 0..3 and 4..7 of the group, one byte each
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      lo |= (uint32_t)t[8 * g + k][wl] << (8 * k);
+      hi |= (uint32_t)t[8 * g + 4 + k][wl] << (8 * k);
+    }
+    // 8 x 8 bit transpose of the block m (bit 8r + c = node r, frame c): three masked swaps of ever larger sub-blocks
+    unsigned long long m = (unsigned long long)lo | ((unsigned long long)hi << 32), tt;
+    tt = 0x0F0F0F0F00000000ull & (m ^ (m << 28)); m ^= tt ^ (tt >> 28);
+    tt = 0x3333000033330000ull & (m ^ (m << 14)); m ^= tt ^ (tt >> 14);
+    tt = 0x5500550055005500ull & (m ^ (m << 7));  m ^= tt ^ (tt >> 7);
+    // now byte j of m = frame j of the word: bit k = node k of the group
+    const int gb = (v0 >> 3) + g;
+    if (gb >= NB) continue;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int f = 8 * (w0 + wl) + j;
+      if (f < F) out[(size_t)f * NB + gb] = (uint8_t)(m >> (8 * j));
+    }
+  }
+}
+
 // all edge messages of one frame as reference labels (the verbosity>=2 dumps, :291-337)
 __global__ void k_extract_frame(const uint32_t* __restrict__ msgs, int num_edges, int W, int frame, int Nq, int q,
                                 uint8_t* __restrict__ out) {
@@ -1095,13 +1146,15 @@ static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cud
 cudaError_t launch_pack(const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, const GraphArrays& g,
                         const BatchBuffers& b, int Nq_cha, int Nq_msg, cudaStream_t st) {
   dim3 grid(cdiv(g.nvar, 32), cdiv(b.W, 32));
+  const bool packed = d_msg_lab == nullptr;  // both labels of a symbol in one byte of d_cha_lab
   const bool vec4 = g.nvar % 4 == 0 && ((uintptr_t)d_cha_lab | (uintptr_t)d_msg_lab) % 4 == 0;
-  if (vec4)
-    k_pack<true><<<grid, 256, 0, st>>>(d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha),
-                                       Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard, b.msg0);
-  else
-    k_pack<false><<<grid, 256, 0, st>>>(d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha),
-                                        Nq_msg, code_bits(Nq_msg), b.cha, b.msgs, b.hard, b.msg0);
+#define PACK_ARGS d_cha_lab, d_msg_lab, g.vn_edge0, g.nvar, b.F, b.W, Nq_cha, code_bits(Nq_cha), Nq_msg, code_bits(Nq_msg), \
+                  b.cha, b.msgs, b.hard, b.msg0
+  if (vec4 && packed) k_pack<true, true><<<grid, 256, 0, st>>>(PACK_ARGS);
+  else if (vec4) k_pack<true, false><<<grid, 256, 0, st>>>(PACK_ARGS);
+  else if (packed) k_pack<false, true><<<grid, 256, 0, st>>>(PACK_ARGS);
+  else k_pack<false, false><<<grid, 256, 0, st>>>(PACK_ARGS);
+#undef PACK_ARGS
   return cudaGetLastError();
 }
 
@@ -1303,6 +1356,12 @@ cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* 
   dim3 grid(cdiv(g.nvar, 32), cdiv(b.W, 32));
   if (g.nvar % 4 == 0 && (uintptr_t)d_out_bits % 4 == 0) k_unpack<true><<<grid, 256, 0, st>>>(b.hard, g.nvar, b.F, b.W, d_out_bits);
   else k_unpack<false><<<grid, 256, 0, st>>>(b.hard, g.nvar, b.F, b.W, d_out_bits);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_unpack_bits(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_packed, cudaStream_t st) {
+  dim3 grid(cdiv(g.nvar, 256), cdiv(b.W, 32));
+  k_unpack_bits<<<grid, 256, 0, st>>>(b.hard, g.nvar, b.F, b.W, (g.nvar + 7) / 8, d_out_packed);
   return cudaGetLastError();
 }
 

@@ -59,7 +59,8 @@ struct NodeLaunch {       // one degree class of one pass
 enum NodeMode { NODE_VAR = 0, NODE_DEC = 1, NODE_CHK = 2 };
 enum FinalizeMode { FIN_INIT = 0, FIN_ITER = 1, FIN_LAST = 2 };
 
-// pack: frame-major labels -> cha/msgs/hard; q_cha/q_msg = code widths; Nq_* = alphabets
+// pack: frame-major labels -> cha/msgs/hard; q_cha/q_msg = code widths; Nq_* = alphabets.  d_msg_lab == nullptr:
+// d_cha_lab holds both labels of a symbol in one byte (low nibble channel, high nibble message)
 cudaError_t launch_pack(const uint8_t* d_cha_lab, const uint8_t* d_msg_lab, const GraphArrays& g,
                         const BatchBuffers& b, int Nq_cha, int Nq_msg, cudaStream_t st);
 cudaError_t launch_reset_flags(const BatchBuffers& b, cudaStream_t st);
@@ -100,6 +101,8 @@ cudaError_t launch_repack(const GraphArrays& g, const BatchBuffers& from, const 
 cudaError_t launch_retire(const GraphArrays& g, const BatchBuffers& from, const BatchBuffers& orig, int32_t* d_ow_first,
                           uint8_t* d_ow_mask, cudaStream_t st);
 cudaError_t launch_unpack(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_bits, cudaStream_t st);
+// hard -> bit-packed frame rows [F][ceil(nvar/8)], bit (v & 7) of byte v >> 3 = decision of node v
+cudaError_t launch_unpack_bits(const GraphArrays& g, const BatchBuffers& b, uint8_t* d_out_packed, cudaStream_t st);
 cudaError_t launch_extract_frame(const BatchBuffers& b, int num_edges, int frame, int Nq, uint8_t* d_out,
                                  cudaStream_t st);
 // quant_nonlin front end: llr [F][nvar] f64 -> labels

@@ -179,7 +179,9 @@ def test_python_harness_single_gpu(L):
     assert r["sim_Nframes"] == [6000, 6000]
     ref = REF["c2_irr_n500"]
     for i, s in enumerate(("1.00", "2.00")):
-        assert _agree(r["sim_frame_errors"][i], 6000, ref[s]["frame_errors"], ref[s]["frames"])
+        # 99.9 % bound: a fixed-seed check of the harness plumbing, not a second statistical study (that is
+        # test_ber_fer_within_confidence_interval)
+        assert _agree(r["sim_frame_errors"][i], 6000, ref[s]["frame_errors"], ref[s]["frames"], z=3.29)
 
 
 def test_multi_gpu_harness_is_split_invariant(L):

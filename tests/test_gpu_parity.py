@@ -273,28 +273,35 @@ def test_decoder_from_reference_codec_file(L, cfg):
         assert np.array_equal(it, fx["ret"]) and np.array_equal(out, fx["out"])
 
 
-ONCHIP = {"c1b_reg36_n1000": True, "c2_irr_n500": True, "c1a_reg632_wide": True, "c4_reg632_high": True,
-          "x_varq_reuse": True, "x_qcha_irr_n1000": True, "x_lutcn_irr_n500": False, "c3_irr_n10000": False,
-          "c5_n64800": False}
+# decoder qualifies for the on-chip regime (min-sum checks, state of a few columns fits shared memory) / takes it by default
+ONCHIP = {"c1b_reg36_n1000": (True, True), "c2_irr_n500": (True, False), "c1a_reg632_wide": (True, False),
+          "c4_reg632_high": (True, False), "x_varq_reuse": (True, False), "x_qcha_irr_n1000": (True, False),
+          "x_lutcn_irr_n500": (False, False), "c3_irr_n10000": (False, False), "c5_n64800": (False, False)}
 
 
-def test_onchip_regime_is_taken_by_the_small_codes(L):
-    """min-sum decoders whose per-column state fits shared memory decode on chip; LUT check nodes and the large codes
-    stream through HBM.  Asking for the regime on a decoder that does not qualify is an error."""
-    for cfg, want in ONCHIP.items():
-        d = _dec(L, cfg)
-        assert bool(d.onchip) == want, (cfg, d.onchip, d.onchip_smem_bytes)
-        assert (d.onchip_smem_bytes > 0) == want
-    with pytest.raises(L.LutLdpcError):
-        _dec(L, "c5_n64800").set_onchip(True)
+def test_onchip_regime_qualification(L):
+    """min-sum decoders whose per-column state fits shared memory can decode on chip; by default only those for which
+    it was measured faster than the HBM regime do (compile-time variable programs, degree <= 8).  LUT check nodes and
+    the large codes stream through HBM; asking for the regime on a decoder that does not qualify is an error."""
+    for cfg, (fits, default) in ONCHIP.items():
+        d = L.Decoder(_golden.bundle_path(cfg))
+        assert bool(d.onchip) == default, (cfg, d.onchip, d.onchip_smem_bytes)
+        assert (d.onchip_smem_bytes > 0) == fits
+        if fits:
+            d.set_onchip(True)
+            d.set_onchip(False)
+        else:
+            with pytest.raises(L.LutLdpcError):
+                d.set_onchip(True)
 
 
-@pytest.mark.parametrize("cfg", [c for c, v in ONCHIP.items() if v])
+@pytest.mark.parametrize("cfg", [c for c, v in ONCHIP.items() if v[0]])
 def test_onchip_regime_equals_hbm_regime_and_oracle(L, cfg):
     """Same seeded noisy frames through the persistent shared-memory kernel and through the per-pass HBM kernels: same
     decisions and lut_decode returns (returns at the initial check, early, late, never; ragged batch over several
     columns per CTA), and both equal the oracle on a sample; all exit configurations."""
     oc, hbm = L.Decoder(_golden.bundle_path(cfg)), L.Decoder(_golden.bundle_path(cfg))
+    oc.set_onchip(True)
     hbm.set_onchip(False)
     assert oc.onchip and not hbm.onchip
     orc = pyoracle.Oracle(_golden.bundle_path(cfg))
@@ -330,3 +337,31 @@ def test_onchip_regime_equals_hbm_regime_and_oracle(L, cfg):
     a = oc.simulate_snr(snr, 3000, seed=4, zero_codeword=True).as_array()
     b = hbm.simulate_snr(snr, 3000, seed=4, zero_codeword=True).as_array()
     assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("cfg,tag", [("c2_irr_n500", "snr1.0"), ("c1a_reg632_wide", "snr4.0"), ("c5_n64800", "sel")])
+def test_packed_entry_points_equal_the_byte_form(L, cfg, tag):
+    """lutldpc_decode_packed[_device]: both labels of a symbol in one byte in, one BIT per decision out (73 KB instead of
+    194 KB per N=64800 frame across PCIe).  Same decoder, same results: the reference's fixture frames, shuffled over a
+    ragged batch of several column blocks (nvar = 500 also has a ragged last byte)."""
+    import torch
+    fx = pyoracle.read_fixture(_golden.fixture_path(cfg, tag))
+    a = _golden.fixture_args(cfg, tag)
+    dec = _dec(L, cfg)
+    dec.set_exit_conditions(dec.max_iters, a["psc"], a["pisc"])
+    idx = np.random.default_rng(3).integers(0, len(fx["ret"]), 777)
+    both = (fx["cha"][idx] | (fx["msg"][idx] << 4)).astype(np.uint8)
+    packed, it = dec.decode_packed(both)
+    nb = (dec.nvar + 7) // 8
+    assert packed.shape == (777, nb)
+    bits = np.unpackbits(packed, axis=1, bitorder="little")[:, :dec.nvar]
+    assert np.array_equal(it, fx["ret"][idx])
+    assert np.array_equal(bits, fx["out"][idx])
+    assert not np.unpackbits(packed, axis=1, bitorder="little")[:, dec.nvar:].any()  # padding bits of the last byte
+    d_in = torch.from_numpy(both).cuda()
+    d_out = torch.zeros((777, nb), dtype=torch.uint8, device="cuda")
+    d_it = torch.zeros(777, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    dec.decode_packed_device(777, d_in.data_ptr(), d_out.data_ptr(), d_it.data_ptr())
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy(), packed) and np.array_equal(d_it.cpu().numpy(), it)
