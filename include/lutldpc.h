@@ -210,6 +210,31 @@ int lutldpc_last_call_stats(const lutldpc_decoder* h, double* device_ms, int64_t
 int lutldpc_set_repack(lutldpc_decoder* h, int on, double alpha);
 int lutldpc_get_repack_count(const lutldpc_decoder* h, int64_t* repacks);
 
+/* ---- parity-check matrices.
+ * lutldpc_alist_graph == LDPC_Parity(alist) (itpp/itpp/base/gf2mat.cpp:46-210, itpp/itpp/comm/ldpc.cpp:167-180: the
+ * row lists define H) followed by the graph flattening of LDPC_Code_LUT::decoder_parameterization
+ * (src/LDPC_Code_LUT.cpp:488-541): dv_vec / dc_vec / cn_msg_idx with the reference's edge numbering, i.e. the graph
+ * arrays of lutldpc_desc.  rank_mode: 0 = leave nchk_lin_indep at -1, 1 = GF(2) row rank on the host, 2 = on the
+ * device (:493-499; the reference's dense elimination takes 528 s for N=64800, the device elimination seconds).
+ * The arrays are malloc'ed by the library; release them with lutldpc_graph_free. */
+typedef struct lutldpc_graph {
+  int32_t nvar, nchk, num_edges, nchk_lin_indep;
+  int32_t* dv_vec;      /* [nvar] */
+  int32_t* dc_vec;      /* [nchk] */
+  int32_t* cn_msg_idx;  /* [num_edges] */
+} lutldpc_graph;
+int lutldpc_alist_graph(const char* alist_path, int rank_mode, lutldpc_graph* out);
+void lutldpc_graph_free(lutldpc_graph* g);
+/* lutldpc_create_systematic == LDPC_Generator_Systematic::construct (itpp/itpp/comm/ldpc.cpp:894-999) for the
+ * parity-check matrix of `src`, on the device: Gauss-Jordan elimination over GF(2) finds nchk_lin_indep independent
+ * (parity) columns, the columns of H are renumbered to [information | parity] as construct() permutes *H in place
+ * (:976-986), and *out is a decoder for that column-permuted code (same trees and thresholds) that carries the
+ * generator: lutldpc_encode gives [u, P*u] and lutldpc_simulate_snr accepts zero_codeword = 0.  Parity columns are
+ * taken in natural column order (construct()'s natural_ordering variant; the reference's default draws a random order,
+ * so its permutation differs -- both are systematic generators of the same code).  col_perm (may be NULL) receives
+ * the new index of every old column. */
+int lutldpc_create_systematic(const lutldpc_decoder* src, lutldpc_decoder** out, int32_t* col_perm);
+
 /* ---- on-chip regime (no counterpart in the reference).  Decoders with min-sum checks whose per-column state
  * (E message words, N channel words, N hard bytes for 8 frames) fits shared memory at least twice per SM -- the
  * (3,6) N=1000, irregular N=500 and (6,32) N=2048 codes -- decode a batch in ONE persistent kernel: a CTA keeps the

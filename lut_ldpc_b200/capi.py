@@ -36,6 +36,28 @@ class _Info(C.Structure):
                 ("onchip", C.c_int32), ("onchip_smem_bytes", C.c_int32)]
 
 
+class _Graph(C.Structure):
+    _fields_ = [("nvar", C.c_int32), ("nchk", C.c_int32), ("num_edges", C.c_int32), ("nchk_lin_indep", C.c_int32),
+                ("dv_vec", C.POINTER(C.c_int32)), ("dc_vec", C.POINTER(C.c_int32)), ("cn_msg_idx", C.POINTER(C.c_int32))]
+
+
+def alist_graph(path, rank_mode=0):
+    """LDPC_Parity(alist) + LDPC_Code_LUT::decoder_parameterization: dict with nvar, nchk, num_edges, nchk_lin_indep
+    (-1 unless rank_mode 1 = host / 2 = device) and the numpy arrays dv_vec, dc_vec, cn_msg_idx."""
+    L = load_library()
+    g = _Graph()
+    rc = L.lutldpc_alist_graph(os.fsencode(path), int(rank_mode), C.byref(g))
+    if rc != 0:
+        raise LutLdpcError(rc, (L.lutldpc_last_error(None) or b"").decode())
+    try:
+        return dict(nvar=g.nvar, nchk=g.nchk, num_edges=g.num_edges, nchk_lin_indep=g.nchk_lin_indep,
+                    dv_vec=np.ctypeslib.as_array(g.dv_vec, (g.nvar,)).copy(),
+                    dc_vec=np.ctypeslib.as_array(g.dc_vec, (g.nchk,)).copy(),
+                    cn_msg_idx=np.ctypeslib.as_array(g.cn_msg_idx, (g.num_edges,)).copy())
+    finally:
+        L.lutldpc_graph_free(C.byref(g))
+
+
 class _SimParams(C.Structure):
     _fields_ = [("snr_db", C.c_double), ("n_frames", C.c_int64), ("seed", C.c_uint64), ("first_frame", C.c_uint64),
                 ("zero_codeword", C.c_int32), ("batch_frames", C.c_int32)]
@@ -74,7 +96,8 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_decode_quantized_traced", "lutldpc_encode", "lutldpc_syndrome_check", "lutldpc_simulate_snr",
            "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device",
            "lutldpc_set_repack", "lutldpc_get_repack_count", "lutldpc_syndrome_check_device_noalloc",
-           "lutldpc_noalloc_max_frames", "lutldpc_set_onchip", "lutldpc_decode_packed", "lutldpc_decode_packed_device"]
+           "lutldpc_noalloc_max_frames", "lutldpc_set_onchip", "lutldpc_decode_packed", "lutldpc_decode_packed_device",
+           "lutldpc_alist_graph", "lutldpc_graph_free", "lutldpc_create_systematic"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
                  7: "count", 8: "encode", 10: "repack", 11: "retire", 12: "onchip"}
@@ -119,6 +142,10 @@ def load_library():
     L.lutldpc_noalloc_max_frames.argtypes = [vp]
     L.lutldpc_set_onchip.argtypes = [vp, i32]
     L.lutldpc_decode_packed.argtypes = [vp, i32, vp, vp, vp]
+    L.lutldpc_alist_graph.argtypes = [C.c_char_p, i32, C.POINTER(_Graph)]
+    L.lutldpc_graph_free.argtypes = [C.POINTER(_Graph)]
+    L.lutldpc_graph_free.restype = None
+    L.lutldpc_create_systematic.argtypes = [vp, C.POINTER(vp), vp]
     L.lutldpc_decode_packed_device.argtypes = [vp, i32, vp, vp, vp]
     L.lutldpc_get_profile.argtypes = [vp, vp, vp, vp, vp]
     _lib = L
@@ -132,14 +159,30 @@ def _p(a):
 class Decoder:
     """One lutldpc_decoder handle (an LDPC_Code_LUT bound to the current CUDA device)."""
 
-    def __init__(self, bundle_path):
+    def __init__(self, bundle_path, _handle=None):
         """bundle_path: the reference's codec file (lut_codec.it, IT++ it_file) or a decoder bundle."""
         self._L = load_library()
         h = C.c_void_p()
-        rc = self._L.lutldpc_create_from_bundle(os.fsencode(bundle_path), C.byref(h))
+        if _handle is not None:
+            h = _handle
+        else:
+            rc = self._L.lutldpc_create_from_bundle(os.fsencode(bundle_path), C.byref(h))
+            if rc != 0:
+                raise LutLdpcError(rc, (self._L.lutldpc_last_error(None) or b"").decode())
+        self._h = h
+        self._refresh_info()
+
+    def systematic(self):
+        """LDPC_Generator_Systematic::construct on the device: (decoder of the column-permuted code with the generator
+        attached, col_perm = new index of every old column)."""
+        h = C.c_void_p()
+        perm = np.zeros(self.nvar, np.int32)
+        rc = self._L.lutldpc_create_systematic(self._h, C.byref(h), _p(perm))
         if rc != 0:
             raise LutLdpcError(rc, (self._L.lutldpc_last_error(None) or b"").decode())
-        self._h = h
+        return Decoder(None, _handle=h), perm
+
+    def _refresh_info(self):
         info = _Info()
         self._ck(self._L.lutldpc_get_info(self._h, C.byref(info)))
         self.info = info

@@ -104,6 +104,73 @@ int lutldpc_create(const lutldpc_desc* d, lutldpc_decoder** out) {
   return finish_create(h, out);
 }
 
+// ------------------------------------------------------------------------------------ graphs and generators
+int lutldpc_alist_graph(const char* alist_path, int rank_mode, lutldpc_graph* out) {
+  if (!alist_path || !out) { g_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
+  memset(out, 0, sizeof *out);
+  ParityRows H;
+  std::string err;
+  if (!load_alist_file(alist_path, H, err)) { g_create_error = err; return LUTLDPC_ERR_MODEL; }
+  FlatGraph g;
+  flatten_graph(H, g);
+  int rank = -1;
+  if (rank_mode == 1) rank = gf2_rank_host(H);
+  else if (rank_mode == 2) {
+    Gf2Result r;
+    if (!gf2_systematic_device(H, r, false, nullptr, err)) { g_create_error = err; return LUTLDPC_ERR_CUDA; }
+    rank = r.rank;
+  } else if (rank_mode != 0) { g_create_error = "rank_mode must be 0 (none), 1 (host) or 2 (device)"; return LUTLDPC_ERR_ARG; }
+  out->nvar = g.nvar; out->nchk = g.nchk; out->num_edges = g.num_edges; out->nchk_lin_indep = rank;
+  out->dv_vec = (int32_t*)malloc(sizeof(int32_t) * std::max(1, g.nvar));
+  out->dc_vec = (int32_t*)malloc(sizeof(int32_t) * std::max(1, g.nchk));
+  out->cn_msg_idx = (int32_t*)malloc(sizeof(int32_t) * std::max(1, g.num_edges));
+  if (!out->dv_vec || !out->dc_vec || !out->cn_msg_idx) { lutldpc_graph_free(out); g_create_error = "out of memory"; return LUTLDPC_ERR_ARG; }
+  memcpy(out->dv_vec, g.dv.data(), sizeof(int32_t) * g.nvar);
+  memcpy(out->dc_vec, g.dc.data(), sizeof(int32_t) * g.nchk);
+  memcpy(out->cn_msg_idx, g.cn_msg_idx.data(), sizeof(int32_t) * g.num_edges);
+  return LUTLDPC_OK;
+}
+
+void lutldpc_graph_free(lutldpc_graph* g) {
+  if (!g) return;
+  free(g->dv_vec); free(g->dc_vec); free(g->cn_msg_idx);
+  memset(g, 0, sizeof *g);
+}
+
+int lutldpc_create_systematic(const lutldpc_decoder* src, lutldpc_decoder** out, int32_t* col_perm) {
+  if (!src || !out) { g_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
+  *out = nullptr;
+  if (cudaSetDevice(src->device) != cudaSuccess) { g_create_error = "cudaSetDevice failed"; return LUTLDPC_ERR_CUDA; }
+  ParityRows H, Hp;
+  std::string err;
+  const DecoderModel& sm = src->m;
+  if (!rows_from_graph(sm.nvar, sm.nchk, sm.dv, sm.dc, sm.cn_msg_idx, H, err)) { g_create_error = err; return LUTLDPC_ERR_MODEL; }
+  Gf2Result r;
+  if (!gf2_systematic_device(H, r, true, nullptr, err)) { g_create_error = err; return LUTLDPC_ERR_CUDA; }
+  if (r.rank == 0 || r.rank >= sm.nvar) {
+    if (r.d_P) cudaFree(r.d_P);
+    g_create_error = "parity-check matrix has no information columns";
+    return LUTLDPC_ERR_MODEL;
+  }
+  lutldpc_decoder* h = new (std::nothrow) lutldpc_decoder();
+  if (!h) { cudaFree(r.d_P); g_create_error = "out of memory"; return LUTLDPC_ERR_ARG; }
+  h->m = sm;
+  permute_columns(H, r.col_perm, Hp);
+  FlatGraph g;
+  flatten_graph(Hp, g);
+  h->m.dv = g.dv; h->m.dc = g.dc; h->m.cn_msg_idx = g.cn_msg_idx;
+  h->m.nchk_lin_indep = r.rank;
+  h->m.gen.clear(); h->m.gen_rows = h->m.gen_cols = 0;
+  if (!finalize_model(h->m, err)) { cudaFree(r.d_P); delete h; g_create_error = err; return LUTLDPC_ERR_MODEL; }
+  h->d_gen_bits = r.d_P;
+  h->gen_bits_wp = r.P_words_per_row; h->gen_bits_rows = r.rank; h->gen_bits_cols = sm.nvar - r.rank;
+  int rc = finish_create(h, out);
+  if (rc != LUTLDPC_OK) return rc;
+  (*out)->psc = src->psc; (*out)->pisc = src->pisc; (*out)->init_mode = src->init_mode;
+  if (col_perm) memcpy(col_perm, r.col_perm.data(), sizeof(int32_t) * sm.nvar);
+  return LUTLDPC_OK;
+}
+
 void lutldpc_destroy(lutldpc_decoder* h) {
   if (!h) return;
   cudaSetDevice(h->device);
@@ -117,7 +184,7 @@ int lutldpc_get_info(const lutldpc_decoder* h, lutldpc_info* info) {
   memset(info, 0, sizeof *info);
   info->nvar = m.nvar; info->nchk = m.nchk; info->nchk_lin_indep = m.nchk_lin_indep; info->ninfo = m.ninfo();
   info->num_edges = m.num_edges; info->max_iters = h->max_iters; info->Nq_Cha = m.Nq_Cha; info->min_lut = m.minLUT;
-  info->has_gen = !m.gen.empty(); info->n_degree_classes = (int)h->vn_classes.size(); info->rate = m.rate();
+  info->has_gen = h->has_generator(); info->n_degree_classes = (int)h->vn_classes.size(); info->rate = m.rate();
   int nvc = (int)h->vn_classes.size();
   for (int c = 0; c < nvc; ++c) {  // first iteration slot is representative (shapes rarely change per slot)
     info->lookups_per_frame_iter += h->var_progs[c].n_ops * h->vn_classes[c].n;

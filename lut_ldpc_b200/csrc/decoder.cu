@@ -21,6 +21,7 @@ static int env_int(const char* name, int dflt) {
 }
 
 lutldpc_decoder::~lutldpc_decoder() {
+  if (d_gen_bits) cudaFree(d_gen_bits);
   if (h_active) cudaFreeHost(h_active);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "../../include/lutldpc.h"
+#include "gf2.hpp"
 #include "kernels.hpp"
 #include "onchip.hpp"
 #include "model.hpp"
@@ -108,6 +109,10 @@ struct lutldpc_decoder {
   lutldpc::DevBuf<int32_t> d_vn_edge0, d_dv, d_cn_start, d_cn_msg_idx, d_chk_equ_idx, d_cha2msg;
   lutldpc::DevBuf<double> d_qb_cha, d_qb_msg;
   lutldpc::DevBuf<uint8_t> d_prog_blob, d_gen;
+  // bit-packed parity part of a generator made on the device (lutldpc_create_systematic): [gen_rows][gen_bits_wp] words
+  uint32_t* d_gen_bits = nullptr;
+  int gen_bits_wp = 0, gen_bits_rows = 0, gen_bits_cols = 0;
+  bool has_generator() const { return !m.gen.empty() || d_gen_bits != nullptr; }
   lutldpc::GraphArrays g;
   std::vector<lutldpc::NodeClass> vn_classes, cn_classes;
   std::vector<lutldpc::NodeClass> cn_exact;  // min-sum: checks grouped by degree, list = edge rows [n][degree]

@@ -118,6 +118,7 @@ struct ChanParams {
   double sigma, four_over_N0;
   int n_qb_cha, n_qb_msg, use_map, Nq_cha, q_cha, Nq_msg, q_msg;
   int sorted;  // both threshold vectors ascend: binary search gives quant_nonlin's value
+  int same_q;  // qb_Msg and qb_Cha are the same vector
 };
 
 // BPSK + AWGN + LLR + both quantisers -> channel labels, initial messages, channel hard decision,
@@ -159,7 +160,8 @@ __global__ void __launch_bounds__(128) k_channel(const uint8_t* __restrict__ cw,
         const double llr = cp.four_over_N0 * x;
         const int c = cp.sorted ? quant_sorted16(llr, s_qc) : quant_nonlin_s(llr, s_qc, cp.n_qb_cha);
         const int mm = cp.use_map ? s_map[c]
-                                  : (cp.sorted ? quant_sorted16(llr, s_qm) : quant_nonlin_s(llr, s_qm, cp.n_qb_msg));
+                       : cp.same_q ? c  // qb_Msg == qb_Cha element for element: the second quantiser repeats the first
+                                   : (cp.sorted ? quant_sorted16(llr, s_qm) : quant_nonlin_s(llr, s_qm, cp.n_qb_msg));
         cword[i] |= lab2code_s((uint32_t)c, cp.Nq_cha, cp.q_cha) << (4 * j);
         mword[i] |= lab2code_s((uint32_t)mm, cp.Nq_msg, cp.q_msg) << (4 * j);
         slicer[i] |= (x > 0.0 ? 0u : 1u) << j;
@@ -265,9 +267,10 @@ extern "C" {
 int lutldpc_encode(lutldpc_decoder* h, int n_frames, const uint8_t* info, uint8_t* codeword) {
   if (!h) return LUTLDPC_ERR_ARG;
   if (n_frames < 0 || (n_frames && (!info || !codeword))) return h->fail(LUTLDPC_ERR_ARG, "bad argument");
-  if (h->m.gen.empty()) return h->fail(LUTLDPC_ERR_STATE, "decoder has no generator matrix");
+  if (!h->has_generator()) return h->fail(LUTLDPC_ERR_STATE, "decoder has no generator matrix");
   CKH(cudaSetDevice(h->device), "cudaSetDevice");
-  const int N = h->m.nvar, K = h->m.gen_cols, rows = h->m.gen_rows;
+  const bool bits = h->d_gen_bits != nullptr;
+  const int N = h->m.nvar, K = bits ? h->gen_bits_cols : h->m.gen_cols, rows = bits ? h->gen_bits_rows : h->m.gen_rows;
   if (K + rows != N) return h->fail(LUTLDPC_ERR_MODEL, "generator shape does not match nvar");
   cudaStream_t st = h->stream;
   const int maxb = h->max_batch_frames();
@@ -280,7 +283,8 @@ int lutldpc_encode(lutldpc_decoder* h, int n_frames, const uint8_t* info, uint8_
     dim3 gk(K, (W + 127) / 128), gr(rows, (W + 127) / 128), gn(N, (W + 127) / 128);
     k_bits_to_rows<<<gk, 128, 0, st>>>(h->buf_lab_cha.p, K, K, W, nf, h->buf_cw.p);
     CKL("bits_to_rows");
-    k_encode<<<gr, 128, 0, st>>>(h->d_gen.p, rows, K, W, h->buf_cw.p);
+    if (bits) CKH(launch_encode_bits(h->d_gen_bits, h->gen_bits_wp, rows, K, W, h->buf_cw.p, st), "encode_bits");
+    else k_encode<<<gr, 128, 0, st>>>(h->d_gen.p, rows, K, W, h->buf_cw.p);
     CKL("encode");
     CKH(h->buf_out.ensure((size_t)nf * N), "alloc out");
     k_rows_to_bits<<<gn, 128, 0, st>>>(h->buf_cw.p, N, W, nf, h->buf_out.p);
@@ -295,14 +299,15 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
   if (!h) return LUTLDPC_ERR_ARG;
   if (!p || !acc || p->n_frames < 0) return h->fail(LUTLDPC_ERR_ARG, "bad argument");
   const DecoderModel& m = h->m;
-  if (!p->zero_codeword && m.gen.empty())
+  if (!p->zero_codeword && !h->has_generator())
     return h->fail(LUTLDPC_ERR_STATE, "zero_codeword=0 needs a generator matrix in the decoder");
   if (h->init_mode == LUTLDPC_INIT_CONT && (int)m.qb_Msg.size() != m.Nq_Msg[0] - 1)
     return h->fail(LUTLDPC_ERR_STATE, "decoder has no message quantiser qb_Msg for continuous inputs");
   CKH(cudaSetDevice(h->device), "cudaSetDevice");
   cudaStream_t st = h->stream;
   const int N = m.nvar, K = m.ninfo();
-  if (!p->zero_codeword && (m.gen_cols != K || m.gen_rows != N - K))
+  const bool gen_bits = h->d_gen_bits != nullptr;
+  if (!p->zero_codeword && ((gen_bits ? h->gen_bits_cols : m.gen_cols) != K || (gen_bits ? h->gen_bits_rows : m.gen_rows) != N - K))
     return h->fail(LUTLDPC_ERR_MODEL, "generator shape does not match the code");
   // frames in flight: large batches run the decoder at its efficient point (N=64800: 32768 frames per batch decode
   // 5 % faster per frame than 8192: fewer repacks and tail iterations per frame)
@@ -323,6 +328,7 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
   cp.sorted = 1;
   for (size_t i = 1; i < m.qb_Cha.size(); ++i) cp.sorted &= m.qb_Cha[i - 1] < m.qb_Cha[i];
   for (size_t i = 1; i < m.qb_Msg.size(); ++i) cp.sorted &= m.qb_Msg[i - 1] < m.qb_Msg[i];
+  cp.same_q = m.qb_Cha == m.qb_Msg;
   const uint32_t k0 = (uint32_t)p->seed, k1 = (uint32_t)(p->seed >> 32);
   int64_t total_launches = 0;
   // whole-call events (all batches); owned by the handle, so no error path can leak them
@@ -342,7 +348,8 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
       CKH(h->buf_cw.ensure((size_t)N * W), "alloc cw");
       k_info_bits<<<dim3(K, gw.x), 128, 0, st>>>(h->buf_cw.p, K, W, nf, first, k0, k1);
       CKL("info_bits");
-      k_encode<<<dim3(N - K, gw.x), 128, 0, st>>>(h->d_gen.p, N - K, K, W, h->buf_cw.p);
+      if (gen_bits) CKH(launch_encode_bits(h->d_gen_bits, h->gen_bits_wp, N - K, K, W, h->buf_cw.p, st), "encode_bits");
+      else k_encode<<<dim3(N - K, gw.x), 128, 0, st>>>(h->d_gen.p, N - K, K, W, h->buf_cw.p);
       CKL("encode");
       h->launched(KIND_ENCODE);
     }

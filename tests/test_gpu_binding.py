@@ -19,28 +19,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "oracle", "_ref", "b200_binding_test")
 
 
-def write_alist(cfg, path):
-    """Parity-check matrix of a golden decoder bundle as an alist file (itpp/itpp/base/gf2mat.cpp:57-150: 1-based,
-    `N M`, max weights, column weights, row weights, column lists, row lists, zero padded).  The bundle holds the
-    graph as decoder_parameterization flattened it (src/LDPC_Code_LUT.cpp:513-528): edges VN-major, cn_msg_idx =
-    edges of each check."""
-    orc = pyoracle.Oracle(_golden.bundle_path(cfg))
-    dv, dc, idx = orc.dv, orc.dc, orc.cn_msg_idx
-    edge_vn = np.repeat(np.arange(orc.nvar), dv)
-    cs = np.concatenate([[0], np.cumsum(dc)])
-    rows = [np.sort(edge_vn[idx[cs[c]:cs[c + 1]]]) for c in range(orc.nchk)]
-    cols = [[] for _ in range(orc.nvar)]
-    for c, r in enumerate(rows):
-        for v in r:
-            cols[v].append(c)
-    mc, mr = int(dv.max()), int(dc.max())
-    with open(path, "w") as f:
-        f.write("%d %d\n%d %d\n" % (orc.nvar, orc.nchk, mc, mr))
-        f.write(" ".join(str(int(x)) for x in dv) + "\n" + " ".join(str(int(x)) for x in dc) + "\n")
-        for cl in cols:
-            f.write(" ".join(str(c + 1) for c in cl + [-1] * (mc - len(cl))) + "\n")
-        for r in rows:
-            f.write(" ".join(str(int(v) + 1) for v in list(r) + [-1] * (mr - len(r))) + "\n")
+from _alist import write_alist  # noqa: E402
 
 
 @pytest.mark.parametrize("cfg,args", [
