@@ -308,6 +308,38 @@ def run_b200(args):
            "call": "ber_sim.py LDPC_BER_Sim_LUT.sim_snr_point -> lutldpc_simulate_snr (Philox4x32-10 AWGN, quantiser, "
                    "lut_decode, error counting on the device) + all_reduce(SUM) of 264 int64 counters per step"}
 
+    # ---- random codewords (north_star: "throughput on synthetic random-codeword frames").  The generator comes from
+    # lutldpc_create_systematic: GF(2) Gauss-Jordan elimination of H on the device (LDPC_Generator_Systematic::construct;
+    # the reference needs minutes for N=64800), a decoder for the column-permuted code, a bit-packed encoder.  Same
+    # Monte-Carlo step as `sim` with LDPC.zero_codeword=false: source bits -> encode -> BPSK/AWGN -> ... -> count.
+    t0 = time.perf_counter()
+    sysd, _perm = dec.systematic()
+    torch.cuda.synchronize()
+    construct_s = time.perf_counter() - t0
+    sysd.set_exit_conditions(sysd.max_iters, True, True)
+    if _golden.MANIFEST[cfg]["init_mode"] == "qcha":
+        sysd.set_initial_message_mode(L.INIT_QCHA)
+    sysd.simulate_snr(snr, F, seed=99, first_frame=0, zero_codeword=False, batch_frames=F)
+    rc_ms, rc_acc = 0.0, None
+    for i in range(sim_steps):
+        c = sysd.simulate_snr(snr, F, seed=99, first_frame=(i + 1) * F + rank * (sim_steps + 1) * F, zero_codeword=False,
+                              batch_frames=F)
+        rc_ms += sysd.last_call_stats()["device_ms"]
+        rc_acc = c.as_array() if rc_acc is None else rc_acc + c.as_array()
+    sysd.set_profiling(True)
+    sysd.simulate_snr(snr, F, seed=98, zero_codeword=False, batch_frames=F)
+    rc_prof = sysd.get_profile()
+    sysd.set_profiling(False)
+    rc_ms = max_over_ranks(rc_ms)
+    random_cw = {"value": round(sum_over_ranks(F) * sim_steps * K / (rc_ms * 1e-3) / 1e9, 4), "unit": UNIT,
+                 "ms_per_step": round(rc_ms / sim_steps, 3), "steps": sim_steps,
+                 "fer": float(rc_acc[1]) / float(rc_acc[0]), "mean_iterations": round(float(rc_acc[6]) / float(rc_acc[0]), 2),
+                 "generator_construction_s": round(construct_s, 3),
+                 "profile_ms_one_step": {k: round(v[0], 3) for k, v in rc_prof.items() if v[0] >= 0.5},
+                 "call": "lutldpc_create_systematic (rank + generator by Gauss-Jordan elimination on the device) + "
+                         "lutldpc_simulate_snr with zero_codeword = 0 (device timing, rank-local frame ranges)"}
+    sysd.close()
+
     # ---- the same batch through the packed host entry point (one byte per symbol in, one bit per decision out)
     both_h = torch.empty((F, N), dtype=torch.uint8, pin_memory=True)
     both_h.copy_(cha_h | (msg_h << 4))
@@ -340,7 +372,7 @@ def run_b200(args):
                      "mean_iterations": round(sum_iters / F, 2), "decode_failures": int((it_host < 0).sum()),
                      "frame_errors": int(wrong.sum()), "undetected_frame_errors": int((wrong & (it_host >= 0)).sum()),
                      "edge_updates_per_s": round(2.0 * E * sum_iters_all * args.steps / (ms * 1e-3), 1)},
-            "roofline": roofline, "sim": sim, "e2e_packed": e2e_packed, "clocks": clocks, "gpu_launches": int(launches),
+            "roofline": roofline, "sim": sim, "random_codeword": random_cw, "e2e_packed": e2e_packed, "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": round(e2e_value, 4), "unit": UNIT, "h2d_bytes_per_step": int(2 * F * N) * world,
                     "d2h_bytes_per_step": int(F * N + 4 * F) * world, "steps": e2e_steps,
                     "call": "lutldpc_decode_quantized (pinned host u8 labels in, bits + iteration counts out; chunks pipelined over copy and decode streams)"}}

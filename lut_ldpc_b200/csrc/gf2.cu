@@ -81,36 +81,55 @@ __global__ void k_gf2_gather_P(const unsigned long long* __restrict__ A, size_t 
   P[(size_t)t * Wp + w] = out;
 }
 
-// parity rows of a batch: cw[K + t][.] = XOR over the set bits k of P[t] of cw[k][.]; rows are bytes of 8 frames,
-// a thread owns 4 of them (32 frames).  CTA = 8 parity rows x 128 thread columns; the information rows of a 32-bit
-// piece of P are staged in shared memory once for the 8 parity rows.
+// parity rows of a batch: cw[K + t][.] = XOR over the set bits k of P[t] of cw[k][.]; rows are bytes of 8 frames, a
+// thread owns 4 of them (32 frames).  CTA = kEncRows parity rows x 128 thread columns: the 32 information rows of one
+// 32-bit piece of P are staged in shared memory once for all kEncRows parity rows (the information block is re-read
+// rows / kEncRows times in all), and combined four at a time ("four Russians"): the 16 XOR combinations of every group
+// of 4 staged rows are built once per piece, so a parity row costs one shared-memory load and one XOR per 4 columns of P
+// whatever their bits are.
+constexpr int kEncRows = 64;
 __global__ void __launch_bounds__(128) k_encode_bits(const uint32_t* __restrict__ P, int Wp, int rows, int K, int W4,
                                                      uint32_t* __restrict__ cw /* [nvar][W4] words of 4 bytes */) {
-  __shared__ uint32_t tile[32][128];
-  __shared__ uint32_t pw[8];
-  const int w = blockIdx.x * 128 + threadIdx.x;
-  const int t0 = blockIdx.y * 8;
-  uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  for (int kw = 0; kw < Wp; ++kw) {
+  __shared__ uint32_t comb[4][16][128];  // [group of 4 information rows][subset][thread]: 32 KiB
+  __shared__ uint32_t pw[kEncRows];
+  const int tx = threadIdx.x, w = blockIdx.x * 128 + tx;
+  const int t0 = blockIdx.y * kEncRows;
+  uint32_t acc[kEncRows];
+#pragma unroll
+  for (int r = 0; r < kEncRows; ++r) acc[r] = 0;
+  for (int kh = 0; kh < 2 * Wp; ++kh) {  // 16 columns of P (half a word) per stage
+    const int kw = kh >> 1, sh = 16 * (kh & 1);
     __syncthreads();
-    if (threadIdx.x < 8) pw[threadIdx.x] = t0 + threadIdx.x < rows ? P[(size_t)(t0 + threadIdx.x) * Wp + kw] : 0u;
-    for (int b = 0; b < 32; ++b) {
-      const int k = 32 * kw + b;
-      tile[b][threadIdx.x] = (k < K && w < W4) ? cw[(size_t)k * W4 + w] : 0u;
+    if (tx < kEncRows) pw[tx] = t0 + tx < rows ? (P[(size_t)(t0 + tx) * Wp + kw] >> sh) & 0xFFFFu : 0u;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      uint32_t u[4];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int k = 16 * kh + 4 * g + b;
+        u[b] = (k < K && w < W4) ? cw[(size_t)k * W4 + w] : 0u;
+      }
+      uint32_t c[16];
+      c[0] = 0;
+#pragma unroll
+      for (int m = 1; m < 16; ++m) {  // subset m = subset without its lowest row ^ that row
+        const int low = m & -m, b = low == 1 ? 0 : low == 2 ? 1 : low == 4 ? 2 : 3;
+        c[m] = c[m ^ low] ^ u[b];
+      }
+#pragma unroll
+      for (int m = 0; m < 16; ++m) comb[g][m][tx] = c[m];
     }
     __syncthreads();
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      uint32_t m = pw[r];  // uniform over the CTA
-      while (m) {
-        const int b = __ffs(m) - 1;
-        m &= m - 1;
-        acc[r] ^= tile[b][threadIdx.x];
-      }
+    for (int r = 0; r < kEncRows; ++r) {
+      const uint32_t m = pw[r];  // uniform over the CTA
+#pragma unroll
+      for (int g = 0; g < 4; ++g) acc[r] ^= comb[g][(m >> (4 * g)) & 15][tx];
     }
   }
   if (w < W4)
-    for (int r = 0; r < 8; ++r)
+#pragma unroll
+    for (int r = 0; r < kEncRows; ++r)
       if (t0 + r < rows) cw[(size_t)(K + t0 + r) * W4 + w] = acc[r];
 }
 
@@ -199,7 +218,7 @@ bool gf2_systematic_device(const ParityRows& H, Gf2Result& out, bool want_genera
 
 cudaError_t launch_encode_bits(const uint32_t* d_P, int Wp, int rows, int K, int W, uint8_t* d_cw, cudaStream_t st) {
   const int W4 = W / 4;  // W is a multiple of 32 bytes
-  dim3 grid((W4 + 127) / 128, (rows + 7) / 8);
+  dim3 grid((W4 + 127) / 128, (rows + kEncRows - 1) / kEncRows);
   k_encode_bits<<<grid, 128, 0, st>>>(d_P, Wp, rows, K, W4, reinterpret_cast<uint32_t*>(d_cw));
   return cudaGetLastError();
 }
