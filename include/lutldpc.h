@@ -235,6 +235,35 @@ void lutldpc_graph_free(lutldpc_graph* g);
  * the new index of every old column. */
 int lutldpc_create_systematic(const lutldpc_decoder* src, lutldpc_decoder** out, int32_t* col_perm);
 
+/* ---- LUT design on the host == LDPC_Code_LUT::design_luts (src/LDPC_Code_LUT.cpp:699-746): tree templates
+ * (get_lut_tree_templates, src/LDPC_DE.cpp:1124-1290: "auto_bin_balanced" or "filename=<tree template ini>"),
+ * discrete density evolution with LUT export (LDPC_DE_LUT::evolve, :198-326, joint_root strategy, min-sum or LUT
+ * check nodes), quantiser thresholds (get_quant_bound, :561-601) and Nq_Cha_2_Nq_Msg_map, for the empirical ensemble
+ * of the code (get_empirical_ensemble, src/LDPC_Ensemble.cpp:391-423).  Pure host code, no device needed.  The
+ * result is table-exact: thresholds and trees equal the reference's element for element, the trees come back in the
+ * reference's own text serialisation -- exactly the var_tree_string / chk_tree_string of lutldpc_desc, so
+ * lutldpc_alist_graph + lutldpc_design_luts + lutldpc_create is LDPC_BER_Sim_LUT::load without a codec file.
+ * sigma2 = design_thr^2 or 10^(-design_SNRdB/10) / (2 rate) (src/LDPC_BER_Sim.cpp:478-484).
+ * Arrays of the result are malloc'ed by the library; release them with lutldpc_design_free. */
+typedef struct lutldpc_design_params {
+  const int32_t* dv_vec; int32_t nvar;      /* variable-node degrees */
+  const int32_t* dc_vec; int32_t nchk;      /* check-node degrees */
+  int32_t max_iters, Nq_Cha, min_lut;
+  const int32_t* Nq_Msg;                    /* [max_iters] */
+  const int32_t* reuse_vec;                 /* [max_iters] or NULL */
+  double sigma2;
+  const char* tree_method;                  /* NULL = "auto_bin_balanced" */
+} lutldpc_design_params;
+typedef struct lutldpc_design_result {
+  double* qb_Cha; int32_t n_qb_Cha;
+  double* qb_Msg; int32_t n_qb_Msg;
+  int32_t* Nq_Cha_2_Nq_Msg_map; int32_t n_map;
+  char* var_tree_string; size_t var_tree_len;
+  char* chk_tree_string; size_t chk_tree_len;
+} lutldpc_design_result;
+int lutldpc_design_luts(const lutldpc_design_params* p, lutldpc_design_result* out);
+void lutldpc_design_free(lutldpc_design_result* r);
+
 /* ---- on-chip regime (no counterpart in the reference).  Decoders with min-sum checks whose per-column state
  * (E message words, N channel words, N hard bytes for 8 frames) fits shared memory at least twice per SM -- the
  * (3,6) N=1000, irregular N=500 and (6,32) N=2048 codes -- decode a batch in ONE persistent kernel: a CTA keeps the

@@ -58,6 +58,49 @@ def alist_graph(path, rank_mode=0):
         L.lutldpc_graph_free(C.byref(g))
 
 
+class _DesignParams(C.Structure):
+    _fields_ = [("dv_vec", C.POINTER(C.c_int32)), ("nvar", C.c_int32), ("dc_vec", C.POINTER(C.c_int32)), ("nchk", C.c_int32),
+                ("max_iters", C.c_int32), ("Nq_Cha", C.c_int32), ("min_lut", C.c_int32), ("Nq_Msg", C.POINTER(C.c_int32)),
+                ("reuse_vec", C.POINTER(C.c_int32)), ("sigma2", C.c_double), ("tree_method", C.c_char_p)]
+
+
+class _DesignResult(C.Structure):
+    _fields_ = [("qb_Cha", C.POINTER(C.c_double)), ("n_qb_Cha", C.c_int32), ("qb_Msg", C.POINTER(C.c_double)),
+                ("n_qb_Msg", C.c_int32), ("map", C.POINTER(C.c_int32)), ("n_map", C.c_int32),
+                ("var_tree_string", C.POINTER(C.c_char)), ("var_tree_len", C.c_size_t),
+                ("chk_tree_string", C.POINTER(C.c_char)), ("chk_tree_len", C.c_size_t)]
+
+
+def design_luts(dv, dc, max_iters, Nq_Cha, Nq_Msg, sigma2, reuse_vec=None, min_lut=True, tree_method="auto_bin_balanced"):
+    """LDPC_Code_LUT::design_luts on the host (no device needed): dict with qb_Cha, qb_Msg, Nq_Cha_2_Nq_Msg_map and
+    the var / chk tree strings (bytes, the reference's text serialisation)."""
+    L = load_library()
+    L.lutldpc_design_luts.argtypes = [C.POINTER(_DesignParams), C.POINTER(_DesignResult)]
+    L.lutldpc_design_free.argtypes = [C.POINTER(_DesignResult)]
+    L.lutldpc_design_free.restype = None
+    dv = np.ascontiguousarray(dv, np.int32)
+    dc = np.ascontiguousarray(dc, np.int32)
+    nq = np.ascontiguousarray(Nq_Msg, np.int32)
+    assert nq.shape == (max_iters,)
+    ru = None if reuse_vec is None else np.ascontiguousarray(reuse_vec, np.int32)
+    i32p = C.POINTER(C.c_int32)
+    p = _DesignParams(dv.ctypes.data_as(i32p), len(dv), dc.ctypes.data_as(i32p), len(dc), int(max_iters), int(Nq_Cha),
+                      int(bool(min_lut)), nq.ctypes.data_as(i32p), ru.ctypes.data_as(i32p) if ru is not None else None,
+                      float(sigma2), os.fsencode(tree_method))
+    r = _DesignResult()
+    rc = L.lutldpc_design_luts(C.byref(p), C.byref(r))
+    if rc != 0:
+        raise LutLdpcError(rc, (L.lutldpc_last_error(None) or b"").decode())
+    try:
+        return dict(qb_Cha=np.ctypeslib.as_array(r.qb_Cha, (r.n_qb_Cha,)).copy(),
+                    qb_Msg=np.ctypeslib.as_array(r.qb_Msg, (r.n_qb_Msg,)).copy(),
+                    Nq_Cha_2_Nq_Msg_map=np.ctypeslib.as_array(r.map, (r.n_map,)).copy(),
+                    var_tree_string=C.string_at(r.var_tree_string, r.var_tree_len),
+                    chk_tree_string=C.string_at(r.chk_tree_string, r.chk_tree_len))
+    finally:
+        L.lutldpc_design_free(C.byref(r))
+
+
 class _SimParams(C.Structure):
     _fields_ = [("snr_db", C.c_double), ("n_frames", C.c_int64), ("seed", C.c_uint64), ("first_frame", C.c_uint64),
                 ("zero_codeword", C.c_int32), ("batch_frames", C.c_int32)]
@@ -97,7 +140,8 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_last_call_stats", "lutldpc_set_profiling", "lutldpc_get_profile", "lutldpc_quantize_device",
            "lutldpc_set_repack", "lutldpc_get_repack_count", "lutldpc_syndrome_check_device_noalloc",
            "lutldpc_noalloc_max_frames", "lutldpc_set_onchip", "lutldpc_decode_packed", "lutldpc_decode_packed_device",
-           "lutldpc_alist_graph", "lutldpc_graph_free", "lutldpc_create_systematic"]
+           "lutldpc_alist_graph", "lutldpc_graph_free", "lutldpc_create_systematic",
+           "lutldpc_design_luts", "lutldpc_design_free"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
                  7: "count", 8: "encode", 10: "repack", 11: "retire", 12: "onchip"}

@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "decoder.hpp"
+#include "design.hpp"
 
 using namespace lutldpc;
 
@@ -102,6 +103,52 @@ int lutldpc_create(const lutldpc_desc* d, lutldpc_decoder** out) {
     return LUTLDPC_ERR_MODEL;
   }
   return finish_create(h, out);
+}
+
+// ------------------------------------------------------------------------------------ LUT design (host only)
+int lutldpc_design_luts(const lutldpc_design_params* p, lutldpc_design_result* out) {
+  if (!p || !out) { g_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
+  memset(out, 0, sizeof *out);
+  if (!p->dv_vec || !p->dc_vec || !p->Nq_Msg || p->nvar <= 0 || p->nchk <= 0 || p->max_iters <= 0) {
+    g_create_error = "lutldpc_design_params: missing array or non-positive size";
+    return LUTLDPC_ERR_ARG;
+  }
+  design::Params dp;
+  dp.dv.assign(p->dv_vec, p->dv_vec + p->nvar);
+  dp.dc.assign(p->dc_vec, p->dc_vec + p->nchk);
+  dp.max_iters = p->max_iters; dp.Nq_Cha = p->Nq_Cha;
+  dp.Nq_Msg.assign(p->Nq_Msg, p->Nq_Msg + p->max_iters);
+  if (p->reuse_vec) dp.reuse_vec.assign(p->reuse_vec, p->reuse_vec + p->max_iters);
+  dp.min_lut = p->min_lut != 0; dp.sigma2 = p->sigma2;
+  if (p->tree_method) dp.tree_method = p->tree_method;
+  design::Result r;
+  std::string err;
+  if (!design::design_luts(dp, r, err)) { g_create_error = err; return LUTLDPC_ERR_MODEL; }
+  auto dup = [](const void* src, size_t bytes) -> void* {
+    void* d = malloc(bytes ? bytes : 1);
+    if (d && bytes) memcpy(d, src, bytes);
+    return d;
+  };
+  out->n_qb_Cha = (int32_t)r.qb_Cha.size(); out->n_qb_Msg = (int32_t)r.qb_Msg.size(); out->n_map = (int32_t)r.cha2msg.size();
+  out->qb_Cha = (double*)dup(r.qb_Cha.data(), r.qb_Cha.size() * 8);
+  out->qb_Msg = (double*)dup(r.qb_Msg.data(), r.qb_Msg.size() * 8);
+  std::vector<int32_t> m32(r.cha2msg.begin(), r.cha2msg.end());
+  out->Nq_Cha_2_Nq_Msg_map = (int32_t*)dup(m32.data(), m32.size() * 4);
+  out->var_tree_len = r.var_tree_string.size(); out->chk_tree_len = r.chk_tree_string.size();
+  out->var_tree_string = (char*)dup(r.var_tree_string.data(), r.var_tree_string.size());
+  out->chk_tree_string = (char*)dup(r.chk_tree_string.data(), r.chk_tree_string.size());
+  if (!out->qb_Cha || !out->qb_Msg || !out->Nq_Cha_2_Nq_Msg_map || !out->var_tree_string || !out->chk_tree_string) {
+    lutldpc_design_free(out);
+    g_create_error = "out of memory";
+    return LUTLDPC_ERR_ARG;
+  }
+  return LUTLDPC_OK;
+}
+
+void lutldpc_design_free(lutldpc_design_result* r) {
+  if (!r) return;
+  free(r->qb_Cha); free(r->qb_Msg); free(r->Nq_Cha_2_Nq_Msg_map); free(r->var_tree_string); free(r->chk_tree_string);
+  memset(r, 0, sizeof *r);
 }
 
 // ------------------------------------------------------------------------------------ graphs and generators

@@ -5,9 +5,13 @@
 //   ber_sim -p params.ini [-b basedir] [-s seed] [-c custom-name] [--gpus G] [--batch F]
 //
 // Differences, all at the edges of the hot path:
-//  * the decoder is not designed here: Sim.codec_filename must name a designed decoder -- the lut_codec.it
-//    a reference run saved (LDPC_Code_LUT::save_code; looked up under Sim.codes_dir like the reference does,
-//    src/LDPC_BER_Sim.cpp:63,84-86,524) or a decoder bundle; LUT.* design keys only cross-check max_iter;
+//  * the decoder is either loaded -- Sim.codec_filename names the lut_codec.it a reference run saved
+//    (LDPC_Code_LUT::save_code; looked up under Sim.codes_dir like the reference does, src/LDPC_BER_Sim.cpp:63,84-86,
+//    524) or a decoder bundle -- or, as in the reference's load() (:434-520), DESIGNED from LDPC.parity_filename
+//    (<codes_dir>/<name>.alist) and the [LUT] keys: alist import + graph flattening (lutldpc_alist_graph), LUT design
+//    by density evolution on the host (lutldpc_design_luts, table-exact with the reference), and for
+//    LDPC.zero_codeword = false the systematic generator by GF(2) elimination on the device
+//    (lutldpc_create_systematic).  The shipped params/ber.ini.*.example files run as they are;
 //  * results are written both as the reference's IT++ results file (<name>_rseedNNNN.it, the variables of
 //    LDPC_BER_Sim_Results::write_itfile, src/LDPC_BER_Sim.cpp:342-361, readable by scripts/analyze_results.m)
 //    and as JSON with the same variable names plus the counters only the GPU path keeps;
@@ -176,30 +180,103 @@ int main(int argc, char** argv) {
     const bool zero_cw = ini.flag("LDPC.zero_codeword", true);
     const bool pci = ini.flag("LDPC.parity_check_iter", true);
     const std::string codec = ini.get("Sim.codec_filename", "");
-    if (codec.empty())
-      throw std::runtime_error("LDPC_BER_Sim_LUT::load(): Sim.codec_filename (lut_codec.it or decoder bundle of a designed "
-                               "LDPC_Code_LUT) is required: LUT design is not part of the GPU path");
-    // codes_path / codec_filename (src/LDPC_BER_Sim.cpp:524), else relative to the base directory
-    std::string codec_file = path(ini.get("Sim.codes_dir", "codes") + "/" + codec);
-    {
-      struct stat sb;
-      if (codec[0] == '/' || stat(codec_file.c_str(), &sb) != 0) codec_file = path(codec);
-    }
+    const std::string codes_dir = ini.get("Sim.codes_dir", "codes");
     const std::string imode = ini.get("LUT.initial_message_mode", "from_continuous_input");
-
     const int ndev = lutldpc_device_count();
     if (ndev <= 0) throw std::runtime_error("no CUDA device (there is no CPU fallback)");
     if (gpus < 1 || gpus > ndev) throw std::runtime_error("--gpus exceeds the number of visible devices");
     std::vector<std::unique_ptr<LDPC_Code_LUT>> C(gpus);
+    auto configure = [&](LDPC_Code_LUT& c) {
+      const int mi = ini.has("LUT.max_iter") ? (int)ini.num("LUT.max_iter", 30) : c.get_nrof_iterations();
+      c.set_exit_conditions(mi, pci, pci);  // psc = pisc = parity_check_iter, src/LDPC_BER_Sim.cpp:500
+      c.set_initial_message_mode(imode == "from_quantized_channel_llrs" ? LDPC_Code_LUT::QCHA : LDPC_Code_LUT::CONT);
+    };
+    if (!codec.empty()) {
+      // codes_path / codec_filename (src/LDPC_BER_Sim.cpp:524), else relative to the base directory
+      std::string codec_file = path(codes_dir + "/" + codec);
+      struct stat sb;
+      if (codec[0] == '/' || stat(codec_file.c_str(), &sb) != 0) codec_file = path(codec);
+      for (int g = 0; g < gpus; ++g) {
+        if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
+        C[g].reset(new LDPC_Code_LUT(codec_file));
+      }
+      if (!zero_cw && !C[0]->has_generator())
+        throw std::runtime_error("LDPC.zero_codeword=false needs a decoder bundle that carries the generator");
+    } else {
+      // ---- LDPC_BER_Sim_LUT::load, src/LDPC_BER_Sim.cpp:434-507: alist -> graph -> design_luts
+      if (!ini.has("LDPC.parity_filename"))
+        throw std::runtime_error("LDPC_BER_Sim_LUT::load(): LDPC.parity_filename (or Sim.codec_filename) is required");
+      const std::string alist = path(codes_dir + "/" + ini.get("LDPC.parity_filename", "") + ".alist");
+      if (!ini.has("LUT.design_thr") && !ini.has("LUT.design_SNRdB"))
+        throw std::runtime_error("LDPC_BER_Sim_LUT::load(): Either design_thr or design_SNRdB must be specified");  // :478-484
+      const int max_iter = (int)ini.num("LUT.max_iter", 30);
+      const int q_cha = (int)ini.num("LUT.qbits_channel", 4), q_msg = (int)ini.num("LUT.qbits_message_uniform", 3);
+      std::vector<int32_t> nq(max_iter, 1 << q_msg), reuse(max_iter, 0);
+      if (ini.has("LUT.qbits_messages")) {  // :398-400
+        std::vector<double> v = parse_vec(ini.get("LUT.qbits_messages", ""));
+        if ((int)v.size() != max_iter) throw std::runtime_error("LUT.qbits_messages must have max_iter entries");
+        for (int i = 0; i < max_iter; ++i) nq[i] = 1 << (int)v[i];
+      }
+      if (ini.has("LUT.reuse_lut")) {
+        std::vector<double> v = parse_vec(ini.get("LUT.reuse_lut", ""));
+        if ((int)v.size() != max_iter) throw std::runtime_error("LUT.reuse_lut must have max_iter entries");
+        for (int i = 0; i < max_iter; ++i) reuse[i] = v[i] != 0;
+      }
+      // auto_bin_high and root_only behave as auto_bin_balanced in the reference's ber_sim (:487-488)
+      std::string method = "auto_bin_balanced";
+      if (ini.get("LUT.tree_mode", "auto_bin_balanced") == "file")
+        method = "filename=" + path(ini.get("LUT.trees_dir", "trees") + "/" + ini.get("LUT.trees_filename", ""));
+      lutldpc_graph gr;
+      // rank like decoder_parameterization (src/LDPC_Code_LUT.cpp:493-499); on the device for the large codes
+      if (lutldpc_alist_graph(alist.c_str(), 0, &gr) != LUTLDPC_OK) throw std::runtime_error(lutldpc_last_error(nullptr));
+      const int nvar0 = gr.nvar;
+      lutldpc_graph_free(&gr);
+      if (lutldpc_alist_graph(alist.c_str(), nvar0 >= 100000 ? 0 : (nvar0 > 20000 ? 2 : 1), &gr) != LUTLDPC_OK)
+        throw std::runtime_error(lutldpc_last_error(nullptr));
+      if (gr.nchk_lin_indep < 0) gr.nchk_lin_indep = gr.nchk;
+      const double rate = 1.0 - (double)gr.nchk_lin_indep / gr.nvar;
+      const double thr = ini.num("LUT.design_thr", 0);
+      const double sigma2 = ini.has("LUT.design_thr") ? thr * thr : std::pow(10.0, -ini.num("LUT.design_SNRdB", 0) / 10) / (2 * rate);
+      lutldpc_design_params dp;
+      memset(&dp, 0, sizeof dp);
+      dp.dv_vec = gr.dv_vec; dp.nvar = gr.nvar; dp.dc_vec = gr.dc_vec; dp.nchk = gr.nchk;
+      dp.max_iters = max_iter; dp.Nq_Cha = 1 << q_cha; dp.min_lut = ini.flag("LUT.min_lut", true);
+      dp.Nq_Msg = nq.data(); dp.reuse_vec = reuse.data(); dp.sigma2 = sigma2; dp.tree_method = method.c_str();
+      lutldpc_design_result dr;
+      if (lutldpc_design_luts(&dp, &dr) != LUTLDPC_OK) {
+        std::string e = lutldpc_last_error(nullptr);
+        lutldpc_graph_free(&gr);
+        throw std::runtime_error("LDPC_Code_LUT::design_luts(): " + e);
+      }
+      lutldpc_desc d;
+      memset(&d, 0, sizeof d);
+      d.nvar = gr.nvar; d.nchk = gr.nchk; d.nchk_lin_indep = gr.nchk_lin_indep; d.num_edges = gr.num_edges;
+      d.max_iters = max_iter; d.Nq_Cha = dp.Nq_Cha; d.min_lut = dp.min_lut;
+      d.dv_vec = gr.dv_vec; d.dc_vec = gr.dc_vec; d.cn_msg_idx = gr.cn_msg_idx;
+      d.Nq_Msg = nq.data(); d.reuse_vec = reuse.data(); d.Nq_Cha_2_Nq_Msg_map = dr.Nq_Cha_2_Nq_Msg_map;
+      d.qb_Cha = dr.qb_Cha; d.qb_Msg = dr.qb_Msg; d.n_qb_Msg = dr.n_qb_Msg;
+      d.var_tree_string = dr.var_tree_string; d.var_tree_len = dr.var_tree_len;
+      d.chk_tree_string = dr.chk_tree_string; d.chk_tree_len = dr.chk_tree_len;
+      try {
+        for (int g = 0; g < gpus; ++g) {
+          if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
+          C[g].reset(new LDPC_Code_LUT(d));
+          // LDPC.zero_codeword = false: generator + column-permuted H, as load() builds G before the codec (:447-473)
+          if (!zero_cw) C[g].reset(new LDPC_Code_LUT(*C[g], LDPC_Code_LUT::with_generator_t()));
+        }
+      } catch (...) {
+        lutldpc_design_free(&dr);
+        lutldpc_graph_free(&gr);
+        throw;
+      }
+      lutldpc_design_free(&dr);
+      lutldpc_graph_free(&gr);
+      std::cout << "Designed LUT decoder for " << alist << " (sigma2 = " << sigma2 << ", " << max_iter << " iterations)" << std::endl;
+    }
     for (int g = 0; g < gpus; ++g) {
       if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
-      C[g].reset(new LDPC_Code_LUT(codec_file));
-      const int mi = ini.has("LUT.max_iter") ? (int)ini.num("LUT.max_iter", 30) : C[g]->get_nrof_iterations();
-      C[g]->set_exit_conditions(mi, pci, pci);  // psc = pisc = parity_check_iter, src/LDPC_BER_Sim.cpp:500
-      C[g]->set_initial_message_mode(imode == "from_quantized_channel_llrs" ? LDPC_Code_LUT::QCHA : LDPC_Code_LUT::CONT);
+      configure(*C[g]);
     }
-    if (!zero_cw && !C[0]->has_generator())
-      throw std::runtime_error("LDPC.zero_codeword=false needs a decoder bundle that carries the generator");
     const int N = C[0]->get_nvar(), K = C[0]->get_ninfo();
     std::ostringstream name;  // gen_filename, src/LDPC_BER_Sim.cpp:553-568
     name << results_prefix << "_N" << N << "_R" << C[0]->get_rate() << "_maxIter" << C[0]->get_nrof_iterations() << "_zcw"

@@ -50,6 +50,14 @@ class LDPC_Code_LUT : public Channel_Code {
     if (rc != LUTLDPC_OK) throw std::runtime_error(std::string("LDPC_Code_LUT::set_code(): ") + lutldpc_last_error(nullptr));
     fetch_info();
   }
+  // LDPC_Generator_Systematic(H) + LDPC_Code_LUT(H, G) for the code of `other` (src/LDPC_BER_Sim.cpp:447-473): a
+  // decoder for the column-permuted code that carries the systematic generator (lutldpc_create_systematic)
+  struct with_generator_t {};
+  LDPC_Code_LUT(const LDPC_Code_LUT& other, with_generator_t) : h_(nullptr) {
+    int rc = lutldpc_create_systematic(other.h_, &h_, nullptr);
+    if (rc != LUTLDPC_OK) throw std::runtime_error(std::string("LDPC_Generator_Systematic::construct(): ") + lutldpc_last_error(nullptr));
+    fetch_info();
+  }
   ~LDPC_Code_LUT() override { lutldpc_destroy(h_); }
   LDPC_Code_LUT(const LDPC_Code_LUT&) = delete;
   LDPC_Code_LUT& operator=(const LDPC_Code_LUT&) = delete;

@@ -55,3 +55,28 @@ def sel_llr(cfg):
     import numpy as np
     k = np.frombuffer(lzma.open(os.path.join(GOLD, cfg + ".sel.llr_i16.xz"), "rb").read(), "<i2")
     return ((k.astype(np.float64) + 0.5) * 0.01).reshape(-1, MANIFEST[cfg]["design_report"]["nvar"])
+
+
+def read_bundle(path):
+    """A decoder bundle (layout: oracle/ref_driver.cpp write_bundle) as a dict of numpy arrays / bytes."""
+    import struct
+    import numpy as np
+    b = open(path, "rb").read()
+    assert b[:8] == b"LUTLDPC1"
+    h = struct.unpack("<10i", b[8:48])
+    d = dict(nvar=h[0], nchk=h[1], nchk_lin_indep=h[2], num_edges=h[3], max_iters=h[4], Nq_Cha=h[5], min_lut=h[6])
+    off = 48
+
+    def arr(dt, n):
+        nonlocal off
+        a = np.frombuffer(b, dt, n, off).copy()
+        off += a.nbytes
+        return a
+    d["dv_vec"], d["dc_vec"], d["cn_msg_idx"] = arr("<i4", h[0]), arr("<i4", h[1]), arr("<i4", h[3])
+    d["Nq_Msg"], d["reuse_vec"], d["Nq_Cha_2_Nq_Msg_map"] = arr("<i4", h[4]), arr("<i4", h[4]), arr("<i4", h[5])
+    d["qb_Cha"], d["qb_Msg"] = arr("<f8", h[5] - 1), arr("<f8", h[7])
+    for k in ("var_tree_string", "chk_tree_string"):
+        (n,) = struct.unpack_from("<i", b, off)
+        d[k] = b[off + 4:off + 4 + n]
+        off += 4 + n
+    return d

@@ -206,3 +206,42 @@ def test_multi_gpu_harness_is_split_invariant(L):
     for k in ("sim_Nframes", "sim_frame_errors", "sim_data_bit_errors", "sim_uncoded_bit_errors", "sim_sum_iterations"):
         assert r1[k] == r2[k], k
     assert r1["sim_frame_errors"][0] > 100
+
+
+def test_ber_sim_designs_its_decoder_like_the_shipped_examples(L, tmp_path):
+    """ber_sim without a codec file, as the reference ships its examples: params/ber.ini.irregular.example (alist +
+    design_thr, auto trees, random codewords) and params/ber.ini.regular.example ((6,32) code, tree template file, 4/3
+    bits, QCHA initial messages, design_SNRdB).  The alist import, the LUT design (host) and the systematic generator
+    (device) all run inside the binary; FER must agree with the reference's own runs of the same configurations."""
+    from _alist import write_alist
+    exe = os.path.join(ROOT, "lut_ldpc_b200", "ber_sim")
+    if not os.path.exists(exe):
+        pytest.skip("ber_sim binary not built")
+    (tmp_path / "codes").mkdir()
+    (tmp_path / "trees").mkdir()
+    write_alist("c2_irr_n500", str(tmp_path / "codes" / "rate0.50_dv02-17_dc08-09_lut_q4_N500.alist"))
+    write_alist("c4_reg632_high", str(tmp_path / "codes" / "rate0.84_reg_v6c32_N2048.alist"))
+    (tmp_path / "trees" / "6_32_wide.ini").write_text(
+        "[var_iter_000]\n   var_deg_006 = riiim/m//im/m///m//c/\n\n[DT]\n   var_deg_006 = rim/m/m//im/m/m//c/\n")
+    irr = tmp_path / "ber.ini.irregular"
+    irr.write_text("[Sim]\nSNRdB = 1:1:2\nNframes = 20000\nNfers = 1000000\nfer_min = 0\nber_min = 0\n"
+                   "[LDPC]\nparity_filename = rate0.50_dv02-17_dc08-09_lut_q4_N500\nzero_codeword = false\n"
+                   "[LUT]\nmax_iter = 50\ndesign_thr = 0.88\nqbits_channel = 4\nqbits_message_uniform = 4\n")
+    reg = tmp_path / "ber.ini.regular"
+    reg.write_text("[Sim]\nSNRdB = 4:.5:4.5\nNframes = 20000\nNfers = 1000000\nfer_min = 0\nber_min = 0\n"
+                   "[LDPC]\nparity_filename = rate0.84_reg_v6c32_N2048\nzero_codeword = false\n"
+                   "[LUT]\nmax_iter = 8\ndesign_SNRdB = 3.9\nqbits_channel = 4\nqbits_message_uniform = 3\n"
+                   "tree_mode = file\ntrees_filename = 6_32_wide.ini\n"
+                   "initial_message_mode = from_quantized_channel_llrs\n")
+    for ini, cfg, snrs in ((irr, "c2_irr_n500", ("1.00", "2.00")), (reg, "c1a_reg632_wide", ("4.00", "4.50"))):
+        out = subprocess.run([exe, "-p", str(ini), "-b", str(tmp_path), "-s", "1"], capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, (out.stdout[-1000:], out.stderr[-1000:])
+        assert "Designed LUT decoder" in out.stdout
+        lines = [l for l in out.stdout.splitlines() if l.startswith("SNR = ")]
+        assert len(lines) == 2
+        for line, s in zip(lines, snrs):
+            frames = int(line.split("Simulated ")[1].split(" frames")[0])
+            fer = float(line.split("FER: ")[1])
+            ref = REF[cfg][s]
+            assert frames == 20000
+            assert _agree(round(fer * frames), frames, ref["frame_errors"], ref["frames"], z=3.29), (cfg, s, fer, ref)
