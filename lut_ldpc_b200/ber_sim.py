@@ -73,6 +73,20 @@ class SimParams:
             setattr(self, k, v)
 
 
+def next_chunk(frames, frame_errors, nfers, chunk_max, chunk_min=1024):
+    """Frames of the next chunk of an SNR point.  The reference stops at the first frame after which more than Nfers
+    frame errors have been seen (src/LDPC_BER_Sim.cpp:289); chunks are sized from the running FER estimate so that the
+    GPU path overshoots that point by a fraction of a chunk instead of a whole maximal one: a small first chunk, then
+    about 1.25 x the frames expected to bring the missing frame errors."""
+    if nfers >= (1 << 40):
+        return chunk_max
+    if frames == 0:
+        return min(chunk_max, max(chunk_min, 64 * (nfers + 1)))
+    fer = max(frame_errors, 0.5) / frames
+    want = int(1.25 * (nfers + 1 - frame_errors) / fer) + 1
+    return max(min(chunk_min, chunk_max), min(chunk_max, want))
+
+
 def split_frames(todo, first_frame, rank, world):
     """Contiguous, disjoint share of `todo` frames starting at global index first_frame."""
     per = (todo + world - 1) // world
@@ -135,7 +149,7 @@ class LDPC_BER_Sim_LUT:
         acc = np.zeros(N_COUNTERS, np.int64)
         used = 0
         while acc[0] < self.p.Nframes and acc[1] <= self.p.Nfers:
-            todo = int(min(self.p.Nframes - acc[0], self.chunk * self.world))
+            todo = int(min(self.p.Nframes - acc[0], next_chunk(acc[0], acc[1], self.p.Nfers, self.chunk * self.world)))
             lo, n = split_frames(todo, first_frame + used, self.rank, self.world)
             t0 = time.perf_counter()
             mine = self._simulate(snr, n, lo)

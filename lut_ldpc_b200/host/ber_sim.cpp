@@ -295,7 +295,19 @@ int main(int argc, char** argv) {
       if (!stop) {
         // sim_snr_point: frames until Nframes or more than Nfers frame errors (:260-291), at chunk granularity
         while ((int64_t)pt.c.frames < Nframes && (int64_t)pt.c.frame_errors <= Nfers) {
-          int64_t todo = std::min<int64_t>(Nframes - (int64_t)pt.c.frames, chunk_per_gpu * gpus);
+          // chunk size from the running FER estimate: the reference stops at the first frame with more than Nfers
+          // frame errors (:289); a small first chunk, then ~1.25 x the frames expected to bring the missing errors,
+          // so the overshoot is a fraction of a chunk instead of a whole maximal one
+          int64_t want = chunk_per_gpu * gpus;
+          if (Nfers < (1LL << 40)) {
+            if (pt.c.frames == 0) want = std::min<int64_t>(want, std::max<int64_t>(1024, 64 * (Nfers + 1)));
+            else {
+              const double fer = std::max<double>((double)pt.c.frame_errors, 0.5) / (double)pt.c.frames;
+              want = std::max<int64_t>(std::min<int64_t>(1024, want),
+                                       std::min<int64_t>(want, (int64_t)(1.25 * (double)(Nfers + 1 - (int64_t)pt.c.frame_errors) / fer) + 1));
+            }
+          }
+          int64_t todo = std::min<int64_t>(Nframes - (int64_t)pt.c.frames, want);
           std::vector<lutldpc_sim_counters> part(gpus);
           std::vector<std::thread> th;
           std::vector<std::string> errs(gpus);

@@ -109,3 +109,18 @@ def test_world_size_2_matches_world_size_1(tmp_path):
     one = bs.LDPC_BER_Sim_LUT(p, simulate=_fake(lambda s: {1.0: 0.3, 2.0: 0.02}.get(s, 0.0)), chunk_frames=256)
     want = one.run(verbose=False)
     assert got == want
+
+
+def test_chunks_follow_the_fer_estimate_so_the_nfers_stop_overshoots_little():
+    """The reference stops at the first frame with more than Nfers frame errors (src/LDPC_BER_Sim.cpp:289); the GPU
+    path can only stop between chunks, so chunks are sized from the running FER estimate."""
+    assert bs.next_chunk(0, 0, 20, 8192) == 1344                 # small first chunk: 64 x (Nfers + 1)
+    assert bs.next_chunk(0, 0, 10 ** 15, 8192) == 8192           # no Nfers rule: always the maximal chunk
+    assert bs.next_chunk(1344, 700, 20, 8192) == 1024            # already past the limit at high FER: minimal chunk
+    assert bs.next_chunk(1344, 10, 20, 8192) == 1849             # 11 errors missing at FER 10/1344 -> 1.25 x 1478
+    assert bs.next_chunk(8192, 0, 20, 8192) == 8192              # no error seen yet: maximal chunk
+    # a simulated point: FER 0.5, Nfers 20 -> the reference would stop after ~42 frames; one small chunk here
+    p = bs.SimParams(None, SNRdB=[1.0], Nframes=10 ** 6, Nfers=20, fer_min=0.0, ber_min=0.0)
+    sim = bs.LDPC_BER_Sim_LUT(p, simulate=_fake(lambda s: 0.5), chunk_frames=8192)
+    acc, used, _ = sim.sim_snr_point(1.0, 0)
+    assert acc[1] > 20 and used == 1344
