@@ -67,6 +67,19 @@ class SimParams:
         self.zero_codeword = _flag(g("LDPC", "zero_codeword", "true"))
         self.parity_check_iter = _flag(g("LDPC", "parity_check_iter", "true"))
         self.max_iter = int(float(g("LUT", "max_iter", 30)))
+        # design keys (src/LDPC_BER_Sim.cpp:386-413), used when no codec file is named
+        self.codes_dir = g("Sim", "codes_dir", "codes")
+        self.parity_filename = g("LDPC", "parity_filename", "")
+        self.design_thr = float(g("LUT", "design_thr", 0)) if g("LUT", "design_thr", None) is not None else None
+        self.design_SNRdB = float(g("LUT", "design_SNRdB", 0)) if g("LUT", "design_SNRdB", None) is not None else None
+        self.qbits_channel = int(float(g("LUT", "qbits_channel", 4)))
+        self.qbits_message_uniform = int(float(g("LUT", "qbits_message_uniform", 3)))
+        self.qbits_messages = [int(x) for x in parse_vec(g("LUT", "qbits_messages", ""))] if g("LUT", "qbits_messages", "") else None
+        self.reuse_lut = [int(x) for x in parse_vec(g("LUT", "reuse_lut", ""))] if g("LUT", "reuse_lut", "") else None
+        self.tree_mode = g("LUT", "tree_mode", "auto_bin_balanced")
+        self.trees_dir = g("LUT", "trees_dir", "trees")
+        self.trees_filename = g("LUT", "trees_filename", "")
+        self.min_lut = _flag(g("LUT", "min_lut", "true"))
         self.initial_message_mode = g("LUT", "initial_message_mode", "from_continuous_input")
         self.has_lut_section = cp.has_section("LUT") or g("Sim", "codec_type", "none") == "LUT"
         for k, v in over.items():
@@ -111,11 +124,34 @@ class LDPC_BER_Sim_LUT:
 
     def load(self, basedir="."):
         """LDPC_BER_Sim_LUT::load (src/LDPC_BER_Sim.cpp:434-550) minus the design step."""
-        from .capi import Decoder, INIT_CONT, INIT_QCHA
-        if not self.p.codec_filename:
-            raise RuntimeError("LDPC_BER_Sim_LUT::load(): Sim.codec_filename (lut_codec.it or bundle of a designed decoder) is required")
-        path = self.p.codec_filename if os.path.isabs(self.p.codec_filename) else os.path.join(basedir, self.p.codec_filename)
-        self.dec = Decoder(path)
+        from .capi import Decoder, INIT_CONT, INIT_QCHA, alist_graph, design_luts
+        p = self.p
+        if p.codec_filename:
+            path = p.codec_filename if os.path.isabs(p.codec_filename) else os.path.join(basedir, p.codec_filename)
+            self.dec = Decoder(path)
+        else:
+            # alist -> graph (+ rank) -> design_luts -> decoder, and for LDPC.zero_codeword = false the systematic
+            # generator: LDPC_BER_Sim_LUT::load, src/LDPC_BER_Sim.cpp:434-507
+            if not p.parity_filename:
+                raise RuntimeError("LDPC_BER_Sim_LUT::load(): LDPC.parity_filename (or Sim.codec_filename) is required")
+            if p.design_thr is None and p.design_SNRdB is None:
+                raise RuntimeError("LDPC_BER_Sim_LUT::load(): Either design_thr or design_SNRdB must be specified")
+            alist = os.path.join(basedir, p.codes_dir, p.parity_filename + ".alist")
+            nvar = alist_graph(alist)["nvar"]
+            graph = alist_graph(alist, rank_mode=0 if nvar >= 100000 else (2 if nvar > 20000 else 1))
+            rank = graph["nchk_lin_indep"] if graph["nchk_lin_indep"] >= 0 else graph["nchk"]
+            rate = 1.0 - rank / graph["nvar"]
+            sigma2 = p.design_thr ** 2 if p.design_thr is not None else 10.0 ** (-p.design_SNRdB / 10) / (2 * rate)
+            nq = [1 << q for q in (p.qbits_messages or [p.qbits_message_uniform] * p.max_iter)]
+            method = "auto_bin_balanced"  # the other auto modes behave like it in the reference's ber_sim (:487-488)
+            if p.tree_mode == "file":
+                method = "filename=" + os.path.join(basedir, p.trees_dir, p.trees_filename)
+            design = design_luts(graph["dv_vec"], graph["dc_vec"], p.max_iter, 1 << p.qbits_channel, nq, sigma2,
+                                 reuse_vec=p.reuse_lut, min_lut=p.min_lut, tree_method=method)
+            self.dec = Decoder.from_design(graph, design, p.max_iter, 1 << p.qbits_channel, nq, reuse_vec=p.reuse_lut,
+                                           min_lut=p.min_lut)
+            if not p.zero_codeword:
+                self.dec = self.dec.systematic()[0]
         self.dec.set_exit_conditions(self.p.max_iter, self.p.parity_check_iter, self.p.parity_check_iter)  # :500
         self.dec.set_initial_message_mode(INIT_QCHA if self.p.initial_message_mode == "from_quantized_channel_llrs"
                                           else INIT_CONT)

@@ -58,6 +58,16 @@ def alist_graph(path, rank_mode=0):
         L.lutldpc_graph_free(C.byref(g))
 
 
+class _Desc(C.Structure):
+    _fields_ = [("nvar", C.c_int32), ("nchk", C.c_int32), ("nchk_lin_indep", C.c_int32), ("num_edges", C.c_int32),
+                ("max_iters", C.c_int32), ("Nq_Cha", C.c_int32), ("min_lut", C.c_int32),
+                ("dv_vec", C.c_void_p), ("dc_vec", C.c_void_p), ("cn_msg_idx", C.c_void_p), ("Nq_Msg", C.c_void_p),
+                ("reuse_vec", C.c_void_p), ("Nq_Cha_2_Nq_Msg_map", C.c_void_p), ("qb_Cha", C.c_void_p), ("qb_Msg", C.c_void_p),
+                ("n_qb_Msg", C.c_int32), ("var_tree_string", C.c_char_p), ("var_tree_len", C.c_size_t),
+                ("chk_tree_string", C.c_char_p), ("chk_tree_len", C.c_size_t), ("gen_parity", C.c_void_p),
+                ("gen_rows", C.c_int32), ("gen_cols", C.c_int32)]
+
+
 class _DesignParams(C.Structure):
     _fields_ = [("dv_vec", C.POINTER(C.c_int32)), ("nvar", C.c_int32), ("dc_vec", C.POINTER(C.c_int32)), ("nchk", C.c_int32),
                 ("max_iters", C.c_int32), ("Nq_Cha", C.c_int32), ("min_lut", C.c_int32), ("Nq_Msg", C.POINTER(C.c_int32)),
@@ -160,7 +170,6 @@ def load_library():
     L.lutldpc_last_error.restype = C.c_char_p
     L.lutldpc_last_error.argtypes = [vp]
     L.lutldpc_create_from_bundle.argtypes = [C.c_char_p, C.POINTER(vp)]
-    L.lutldpc_create.argtypes = [vp, C.POINTER(vp)]
     L.lutldpc_destroy.argtypes = [vp]
     L.lutldpc_destroy.restype = None
     L.lutldpc_get_info.argtypes = [vp, C.POINTER(_Info)]
@@ -215,6 +224,29 @@ class Decoder:
                 raise LutLdpcError(rc, (self._L.lutldpc_last_error(None) or b"").decode())
         self._h = h
         self._refresh_info()
+
+    @classmethod
+    def from_design(cls, graph, design, max_iters, Nq_Cha, Nq_Msg, reuse_vec=None, min_lut=True):
+        """lutldpc_create from the graph arrays of alist_graph() and the tables of design_luts(): the decoder
+        LDPC_BER_Sim_LUT::load builds when the params name an alist instead of a codec file."""
+        L = load_library()
+        keep = [np.ascontiguousarray(graph[k], np.int32) for k in ("dv_vec", "dc_vec", "cn_msg_idx")]
+        nq = np.ascontiguousarray(Nq_Msg, np.int32)
+        ru = np.ascontiguousarray(reuse_vec if reuse_vec is not None else np.zeros(max_iters), np.int32)
+        mp = np.ascontiguousarray(design["Nq_Cha_2_Nq_Msg_map"], np.int32)
+        qc, qm = np.ascontiguousarray(design["qb_Cha"], np.float64), np.ascontiguousarray(design["qb_Msg"], np.float64)
+        rank = graph["nchk_lin_indep"] if graph["nchk_lin_indep"] >= 0 else graph["nchk"]
+        d = _Desc(graph["nvar"], graph["nchk"], rank, graph["num_edges"], int(max_iters), int(Nq_Cha), int(bool(min_lut)),
+                  keep[0].ctypes.data, keep[1].ctypes.data, keep[2].ctypes.data, nq.ctypes.data, ru.ctypes.data,
+                  mp.ctypes.data if len(mp) == Nq_Cha else None, qc.ctypes.data, qm.ctypes.data, len(qm),
+                  design["var_tree_string"], len(design["var_tree_string"]),
+                  design["chk_tree_string"], len(design["chk_tree_string"]), None, 0, 0)
+        h = C.c_void_p()
+        L.lutldpc_create.argtypes = [C.POINTER(_Desc), C.POINTER(C.c_void_p)]
+        rc = L.lutldpc_create(C.byref(d), C.byref(h))
+        if rc != 0:
+            raise LutLdpcError(rc, (L.lutldpc_last_error(None) or b"").decode())
+        return cls(None, _handle=h)
 
     def systematic(self):
         """LDPC_Generator_Systematic::construct on the device: (decoder of the column-permuted code with the generator

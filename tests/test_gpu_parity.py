@@ -365,3 +365,50 @@ def test_packed_entry_points_equal_the_byte_form(L, cfg, tag):
     dec.decode_packed_device(777, d_in.data_ptr(), d_out.data_ptr(), d_it.data_ptr())
     torch.cuda.synchronize()
     assert np.array_equal(d_out.cpu().numpy(), packed) and np.array_equal(d_it.cpu().numpy(), it)
+
+
+@pytest.mark.parametrize("cfg", ["c1b_reg36_n1000", "x_varq_reuse", "x_lutcn_irr_n500", "c4_reg632_high", "c3_irr_n10000"])
+def test_decoder_built_from_alist_and_own_design_is_bit_exact(L, cfg, tmp_path):
+    """The whole set-up chain without any reference-written decoder file: alist import + graph flattening
+    (lutldpc_alist_graph), LUT design by density evolution on the host (lutldpc_design_luts), lutldpc_create from the
+    resulting arrays -- and then the reference's fixture frames (decisions, returns, every per-iteration message dump)
+    must come out exactly as the reference decoded them with ITS OWN design of the same code."""
+    import test_design_host as T
+    from _alist import write_alist
+    from lut_ldpc_b200 import capi
+    alist = str(tmp_path / (cfg + ".alist"))
+    write_alist(cfg, alist)
+    kv = T._args(cfg)
+    graph = capi.alist_graph(alist, rank_mode=1)
+    max_iter = int(kv["max-iter"])
+    nq = np.full(max_iter, 1 << int(kv["qmsg"]), np.int32)
+    for i, q in enumerate(kv.get("qmsg-list", "").split(",")[:max_iter] if "qmsg-list" in kv else []):
+        nq[i] = 1 << int(q)
+    reuse = np.zeros(max_iter, np.int32)
+    for i, r in enumerate(kv.get("reuse", "").split(",")[:max_iter] if "reuse" in kv else []):
+        reuse[i] = int(r) != 0
+    rate = 1.0 - graph["nchk_lin_indep"] / graph["nvar"]
+    sigma2 = float(kv["design-thr"]) ** 2 if "design-thr" in kv else 10.0 ** (-float(kv["design-snr"]) / 10) / (2 * rate)
+    method = "auto_bin_balanced"
+    if "tree" in kv:
+        name = kv["tree"].split("/")[-1]
+        (tmp_path / name).write_text(T.TEMPLATES[name])
+        method = "filename=" + str(tmp_path / name)
+    min_lut = kv.get("min-lut", "1") != "0"
+    design = capi.design_luts(graph["dv_vec"], graph["dc_vec"], max_iter, 1 << int(kv["qcha"]), nq, sigma2, reuse_vec=reuse,
+                              min_lut=min_lut, tree_method=method)
+    dec = L.Decoder.from_design(graph, design, max_iter, 1 << int(kv["qcha"]), nq, reuse_vec=reuse, min_lut=min_lut)
+    ref = _dec(L, cfg)
+    assert (dec.nvar, dec.nchk_lin_indep, dec.num_edges, dec.lookups_per_frame_iter) == \
+           (ref.nvar, ref.nchk_lin_indep, ref.num_edges, ref.lookups_per_frame_iter)
+    for tag in sorted(_golden.MANIFEST[cfg]["fixtures"]):
+        fx = pyoracle.read_fixture(_golden.fixture_path(cfg, tag))
+        a = _golden.fixture_args(cfg, tag)
+        dec.set_exit_conditions(dec.max_iters, a["psc"], a["pisc"])
+        out, it = dec.decode_quantized(fx["cha"], fx["msg"])
+        assert np.array_equal(it, fx["ret"]) and np.array_equal(out, fx["out"])
+        for f, recs in enumerate(fx["traces"][:1]):
+            o, i2, mine = dec.decode_quantized_traced(fx["cha"], fx["msg"], f, len(recs) + 4)
+            assert len(mine) == len(recs)
+            for (k0, i0, m0), (k1, i1, m1) in zip(recs, mine):
+                assert (k0, i0) == (k1, i1) and pyoracle.same_msgs(m0, m1), (cfg, tag, f, k0, i0)
