@@ -186,6 +186,12 @@ typedef struct lutldpc_sim_counters {
 /* counters are ADDED to *acc (so successive calls / ranks accumulate) */
 int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc);
 
+/* The same step for at most one batch of frames, handing back per frame what LDPC_Code_LUT::decode prints at
+ * output_verbosity > 0 (the "Stimuli Pair" lines, src/LDPC_Code_LUT.cpp:228-238: the golden vectors of the reference's
+ * VHDL flow): llr_cha [n_frames][nvar] = the quantised channel labels llr_in_cha, out_bits [n_frames][nvar] = LLRout. */
+int lutldpc_simulate_snr_stimuli(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc,
+                                 uint8_t* llr_cha, uint8_t* out_bits);
+
 /* ---- per-kernel device times.  With profiling on, an event is recorded after every kernel launch
  * of the handle; lutldpc_get_profile returns, per kind, the summed device milliseconds and launch
  * counts since profiling was switched on.  Kinds: 0 reset, 1 pack, 2 channel, 3 min-sum check pass,

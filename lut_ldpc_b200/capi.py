@@ -151,7 +151,7 @@ EXPORTS = ["lutldpc_abi_version", "lutldpc_device_count", "lutldpc_set_device", 
            "lutldpc_set_repack", "lutldpc_get_repack_count", "lutldpc_syndrome_check_device_noalloc",
            "lutldpc_noalloc_max_frames", "lutldpc_set_onchip", "lutldpc_decode_packed", "lutldpc_decode_packed_device",
            "lutldpc_alist_graph", "lutldpc_graph_free", "lutldpc_create_systematic",
-           "lutldpc_design_luts", "lutldpc_design_free"]
+           "lutldpc_design_luts", "lutldpc_design_free", "lutldpc_simulate_snr_stimuli"]
 PROFILE_KINDS = 64
 PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndrome", 5: "finalize", 6: "unpack",
                  7: "count", 8: "encode", 10: "repack", 11: "retire", 12: "onchip"}
@@ -188,6 +188,7 @@ def load_library():
     L.lutldpc_encode.argtypes = [vp, i32, vp, vp]
     L.lutldpc_syndrome_check.argtypes = [vp, i32, vp, vp]
     L.lutldpc_simulate_snr.argtypes = [vp, C.POINTER(_SimParams), C.POINTER(SimCounters)]
+    L.lutldpc_simulate_snr_stimuli.argtypes = [vp, C.POINTER(_SimParams), C.POINTER(SimCounters), vp, vp]
     L.lutldpc_last_call_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64)]
     L.lutldpc_quantize_device.argtypes = [vp, i32, vp, vp, vp]
     L.lutldpc_set_profiling.argtypes = [vp, i32]
@@ -405,6 +406,16 @@ class Decoder:
         acc = acc if acc is not None else SimCounters()
         self._ck(self._L.lutldpc_simulate_snr(self._h, C.byref(p), C.byref(acc)))
         return acc
+
+    def simulate_snr_stimuli(self, snr_db, n_frames, seed=0, first_frame=0, zero_codeword=True):
+        """One batch of the fused step, returning (counters, llr_in_cha labels [F, nvar], LLRout [F, nvar]): the pairs
+        the reference prints as "Stimuli Pair" at output_verbosity > 0."""
+        p = _SimParams(float(snr_db), int(n_frames), int(seed), int(first_frame), int(bool(zero_codeword)), 0)
+        acc = SimCounters()
+        cha = np.zeros((n_frames, self.nvar), np.uint8)
+        out = np.zeros((n_frames, self.nvar), np.uint8)
+        self._ck(self._L.lutldpc_simulate_snr_stimuli(self._h, C.byref(p), C.byref(acc), _p(cha), _p(out)))
+        return acc, cha, out
 
     def set_profiling(self, on):
         self._ck(self._L.lutldpc_set_profiling(self._h, int(bool(on))))

@@ -232,6 +232,19 @@ __global__ void k_count_frames(const uint32_t* __restrict__ ferr, const int32_t*
   }
 }
 
+// channel codes [nvar][W] -> frame-major reference labels [F][nvar] (the llr_in_cha of the "Stimuli Pair" print)
+__global__ void k_codes_to_labels(const uint32_t* __restrict__ cha, int N, int W, int F, int Nq, int q, uint8_t* out) {
+  int w = blockIdx.y * blockDim.x + threadIdx.x, v = blockIdx.x;
+  if (w >= W || v >= N) return;
+  const uint32_t word = cha[(size_t)v * W + w], nz = Nq >> 1;
+  for (int j = 0; j < 8; ++j) {
+    int f = 8 * w + j;
+    if (f >= F) break;
+    const uint32_t c = (word >> (4 * j)) & 0xF, sign = (c >> (q - 1)) & 1, mag = c & ((1u << (q - 1)) - 1);
+    out[(size_t)f * N + v] = (uint8_t)(sign ? nz - 1 - mag : nz + mag);
+  }
+}
+
 // frame-major 0/1 bytes <-> bit-per-frame rows, for lutldpc_encode
 __global__ void k_bits_to_rows(const uint8_t* __restrict__ in, int ncols_in, int K, int W, int F, uint8_t* rows) {
   int w = blockIdx.y * blockDim.x + threadIdx.x, k = blockIdx.x;
@@ -295,7 +308,22 @@ int lutldpc_encode(lutldpc_decoder* h, int n_frames, const uint8_t* info, uint8_
   return LUTLDPC_OK;
 }
 
+static int simulate_impl(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc, uint8_t* dump_cha,
+                         uint8_t* dump_bits);
+
 int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc) {
+  return simulate_impl(h, p, acc, nullptr, nullptr);
+}
+
+int lutldpc_simulate_snr_stimuli(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc,
+                                 uint8_t* llr_cha, uint8_t* out_bits) {
+  if (!h) return LUTLDPC_ERR_ARG;
+  if (!llr_cha || !out_bits) return h->fail(LUTLDPC_ERR_ARG, "NULL buffer");
+  return simulate_impl(h, p, acc, llr_cha, out_bits);
+}
+
+static int simulate_impl(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc, uint8_t* dump_cha,
+                         uint8_t* dump_bits) {
   if (!h) return LUTLDPC_ERR_ARG;
   if (!p || !acc || p->n_frames < 0) return h->fail(LUTLDPC_ERR_ARG, "bad argument");
   const DecoderModel& m = h->m;
@@ -314,6 +342,7 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
   int batch = p->batch_frames > 0 ? p->batch_frames : 32768;
   batch = std::min(batch, h->max_batch_frames());
   batch = std::max(256, batch / 256 * 256);
+  if (dump_cha && p->n_frames > batch) return h->fail(LUTLDPC_ERR_ARG, "lutldpc_simulate_snr_stimuli: n_frames exceeds one batch");
   const size_t n_cnt = 8 + LUTLDPC_ITER_HIST_MAX;
   CKH(h->buf_cnt.ensure(n_cnt), "alloc counters");
   CKH(cudaMemsetAsync(h->buf_cnt.p, 0, n_cnt * 8, st), "memset counters");
@@ -358,8 +387,19 @@ int lutldpc_simulate_snr(lutldpc_decoder* h, const lutldpc_sim_params* p, lutldp
                                              h->b.hard, h->b.msg0, h->buf_cnt.p + 5);
     CKL("channel");
     h->launched(KIND_CHANNEL);
+    if (dump_cha) {  // llr_in_cha of every frame, as labels
+      CKH(h->buf_lab_cha.ensure((size_t)nf * N), "alloc labels");
+      k_codes_to_labels<<<dim3(N, gw.x), 128, 0, st>>>(h->b.cha, N, W, nf, cp.Nq_cha, cp.q_cha, h->buf_lab_cha.p);
+      CKL("codes_to_labels");
+      CKH(cudaMemcpyAsync(dump_cha, h->buf_lab_cha.p, (size_t)nf * N, cudaMemcpyDeviceToHost, st), "D2H labels");
+    }
     rc = h->run_decode(nullptr);
     if (rc) return rc;
+    if (dump_bits) {  // LLRout of every frame
+      CKH(h->buf_out.ensure((size_t)nf * N), "alloc out");
+      CKH(launch_unpack(h->g, h->b, h->buf_out.p, st), "unpack");
+      CKH(cudaMemcpyAsync(dump_bits, h->buf_out.p, (size_t)nf * N, cudaMemcpyDeviceToHost, st), "D2H bits");
+    }
     int rows_per = 64;
     k_count_data<<<dim3((K + rows_per - 1) / rows_per, gw.x), 128, 0, st>>>(h->b.hard, h->buf_cw.p, p->zero_codeword != 0,
                                                                           K, W, rows_per, h->buf_ferr.p, h->buf_cnt.p + 3);

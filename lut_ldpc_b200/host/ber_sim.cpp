@@ -182,6 +182,7 @@ int main(int argc, char** argv) {
     const std::string codec = ini.get("Sim.codec_filename", "");
     const std::string codes_dir = ini.get("Sim.codes_dir", "codes");
     const std::string imode = ini.get("LUT.initial_message_mode", "from_continuous_input");
+    const int verbosity = (int)ini.num("LUT.output_verbosity", 0);
     const int ndev = lutldpc_device_count();
     if (ndev <= 0) throw std::runtime_error("no CUDA device (there is no CPU fallback)");
     if (gpus < 1 || gpus > ndev) throw std::runtime_error("--gpus exceeds the number of visible devices");
@@ -319,6 +320,23 @@ int main(int argc, char** argv) {
             lutldpc_sim_params sp;
             sp.snr_db = snr; sp.n_frames = n; sp.seed = seed + seed_off; sp.first_frame = next_frame + (uint64_t)off;
             sp.zero_codeword = zero_cw; sp.batch_frames = batch;
+            if (verbosity > 0) {
+              // LUT.output_verbosity > 0: the "Stimuli Pair" print of LDPC_Code_LUT::decode (src/LDPC_Code_LUT.cpp:228-238),
+              // frame by frame in frame order -- the golden vectors of the reference's VHDL flow
+              std::vector<uint8_t> lab((size_t)n * N), bits((size_t)n * N);
+              C[g]->simulate_snr_stimuli(sp, part[g], lab.data(), bits.data());
+              for (int64_t f = 0; f < n; ++f) {
+                std::cout << "Stimuli Pair (Quantized channel LLR decoder inputs in hex format and decoder output in binary format): "
+                          << std::endl;
+                char buf[16];
+                for (int v = 0; v < N; ++v) { snprintf(buf, sizeof buf, "%08X  ", lab[(size_t)f * N + v]); std::cout << buf; }
+                std::cout << std::endl;
+                for (int v = 0; v < N; ++v) std::cout << (int)bits[(size_t)f * N + v] << "  ";
+                std::cout << std::endl << std::endl;
+              }
+              off += n;
+              continue;
+            }
             th.emplace_back([&, g, sp]() {
               try { C[g]->simulate_snr(sp, part[g]); } catch (const std::exception& e) { errs[g] = e.what(); }
             });

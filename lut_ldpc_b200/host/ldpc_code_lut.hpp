@@ -117,6 +117,11 @@ class LDPC_Code_LUT : public Channel_Code {
   // the frame loop of LDPC_BER_Sim::sim_snr_point on the device; counters are added to acc
   void simulate_snr(const lutldpc_sim_params& p, lutldpc_sim_counters& acc) { ck(lutldpc_simulate_snr(h_, &p, &acc), "simulate_snr"); }
 
+  // one batch of the same step, with the per-frame pairs LDPC_Code_LUT::decode prints at output_verbosity > 0
+  void simulate_snr_stimuli(const lutldpc_sim_params& p, lutldpc_sim_counters& acc, uint8_t* llr_cha, uint8_t* out_bits) {
+    ck(lutldpc_simulate_snr_stimuli(h_, &p, &acc, llr_cha, out_bits), "simulate_snr_stimuli");
+  }
+
   // getters, src/LDPC_Code_LUT.hpp:246-285
   int get_nvar() const { return info_.nvar; }
   int get_nchk() const { return info_.nchk; }

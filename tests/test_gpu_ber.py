@@ -245,3 +245,38 @@ def test_ber_sim_designs_its_decoder_like_the_shipped_examples(L, tmp_path):
             ref = REF[cfg][s]
             assert frames == 20000
             assert _agree(round(fer * frames), frames, ref["frame_errors"], ref["frames"], z=3.29), (cfg, s, fer, ref)
+
+
+def test_stimuli_pairs_of_the_fused_step(L, tmp_path):
+    """output_verbosity > 0: the reference prints, per frame, the quantised channel labels and the decoded word
+    ("Stimuli Pair", src/LDPC_Code_LUT.cpp:228-238, the golden vectors of its VHDL flow).  The fused step hands them back
+    (lutldpc_simulate_snr_stimuli): decoding the returned labels again gives the returned words, the counters are those
+    of the same frames, and ber_sim prints the pairs in the reference's format."""
+    dec = L.Decoder(_golden.bundle_path("c2_irr_n500"))
+    dec.set_exit_conditions(dec.max_iters, True, True)
+    acc, cha, out = dec.simulate_snr_stimuli(1.5, 700, seed=12, first_frame=40, zero_codeword=True)
+    plain = dec.simulate_snr(1.5, 700, seed=12, first_frame=40, zero_codeword=True)
+    assert np.array_equal(acc.as_array(), plain.as_array())
+    assert cha.max() < 16 and set(np.unique(out)) <= {0, 1}
+    # this decoder's channel and message quantisers coincide (Nq_Cha = Nq_Msg(0) = 16): llr_in_msg = llr_in_cha
+    out2, it2 = dec.decode_quantized(cha, cha)
+    assert np.array_equal(out2, out)
+    assert int((out[:, :dec.ninfo] != 0).any(axis=1).sum()) == acc.frame_errors
+    assert int(out[:, :dec.ninfo].sum()) == acc.data_bit_errors and int(np.abs(it2).sum()) == acc.sum_iters
+    exe = os.path.join(ROOT, "lut_ldpc_b200", "ber_sim")
+    if not os.path.exists(exe):
+        pytest.skip("ber_sim binary not built")
+    ini = tmp_path / "v.ini"
+    ini.write_text("[Sim]\nSNRdB = 2\nNframes = 20\nNfers = 20\nfer_min = 0\nber_min = 0\ncodec_filename = %s\n"
+                   "[LDPC]\nzero_codeword = true\n[LUT]\nmax_iter = 50\noutput_verbosity = 1\n" % _golden.bundle_path("c2_irr_n500"))
+    o = subprocess.run([exe, "-p", str(ini), "-b", str(tmp_path)], capture_output=True, text=True, timeout=300)
+    assert o.returncode == 0, o.stderr[-1000:]
+    lines = o.stdout.splitlines()
+    heads = [i for i, l in enumerate(lines) if l.startswith("Stimuli Pair (Quantized channel LLR decoder inputs in hex format")]
+    assert len(heads) == 20
+    labels = lines[heads[0] + 1].split()
+    bits = lines[heads[0] + 2].split()
+    assert len(labels) == 500 and len(bits) == 500 and all(len(x) == 8 and int(x, 16) < 16 for x in labels)
+    assert set(bits) <= {"0", "1"}
+    o1, _ = dec.decode_quantized(np.array([[int(x, 16) for x in labels]], np.uint8), np.array([[int(x, 16) for x in labels]], np.uint8))
+    assert [str(b) for b in o1[0]] == bits
