@@ -279,6 +279,47 @@ void lutldpc_design_free(lutldpc_design_result* r);
  * LUTLDPC_ERR_STATE.  Traced decodes always take the HBM regime. */
 int lutldpc_set_onchip(lutldpc_decoder* h, int on);
 
+/* ---- BP comparison decoder == what ber_sim runs for a [BP] section (src/LDPC_BER_Sim.cpp:74-78,157-244,
+ * prog/ber_sim.cpp:136-147): IT++'s LDPC_Code (itpp/itpp/comm/ldpc.h:757-1000) with an LLR_calc_unit
+ * (itpp/itpp/comm/llr.h:120-330), batched.  Integer arithmetic on QLLR = int32 throughout, so results are bit-identical
+ * to LDPC_Code::bp_decode (itpp/itpp/comm/ldpc.cpp:1398-1622): same Boxplus table, same saturation, same operation
+ * order per node degree (incl. the hard-coded degree-6 check update whose association differs from the general one).
+ *   lutldpc_bp_create           LDPC_Code(H[, G]) + set_exit_conditions + set_llrcalc   (src/LDPC_BER_Sim.cpp:197-201)
+ *                               with_generator: LDPC_Generator_Systematic(H) first -- the decoder is then for the
+ *                               column-permuted code [information | parity] and carries the encoder (col_perm as in
+ *                               lutldpc_create_systematic)
+ *   lutldpc_bp_decode_llr       LDPC_Code::decode(const vec&) for n frames: to_qllr, bp_decode, bits = qllrout < 0
+ *   lutldpc_bp_decode_qllr      LDPC_Code::bp_decode for n frames: QLLR in, QLLR out, return values
+ *   lutldpc_bp_simulate_snr     the frame loop of LDPC_BER_Sim::sim_snr_point around it (same noise as
+ *                               lutldpc_simulate_snr for the same seed and frame index)
+ * Buffers are host memory, frame-major.  Graph degrees the reference refuses at decode time (check degree < 2 or > 200,
+ * variable degree 0: it_error, ldpc.cpp:1439-1443,1523-1527,1563) are refused at creation. */
+typedef struct lutldpc_bp lutldpc_bp;
+typedef struct lutldpc_bp_params {
+  int32_t max_iters;               /* BP.max_iter, default 30 */
+  int32_t psc, pisc;               /* ber_sim sets both to LDPC.parity_check_iter (src/LDPC_BER_Sim.cpp:200) */
+  int32_t qllr_scale_res;          /* Dint1, default 12 */
+  int32_t qllr_table_size;         /* Dint2, default 300; 0 = min-sum */
+  int32_t qllr_spacing_res;        /* Dint3, default 7 */
+  int32_t qllr_total_res;          /* Dint4, default 8*sizeof(QLLR)-4 = 28 */
+} lutldpc_bp_params;
+int lutldpc_bp_create(const lutldpc_graph* g, const lutldpc_bp_params* p, int with_generator, lutldpc_bp** out,
+                      int32_t* col_perm);
+void lutldpc_bp_destroy(lutldpc_bp* h);
+const char* lutldpc_bp_last_error(const lutldpc_bp* h);   /* h == NULL: error of the last failed lutldpc_bp_create */
+int lutldpc_bp_get_info(const lutldpc_bp* h, lutldpc_info* info);   /* nvar, nchk, nchk_lin_indep, ninfo, num_edges,
+                                                                        max_iters, has_gen, rate; rest 0 */
+int lutldpc_bp_decode_llr(lutldpc_bp* h, int n_frames, const double* llr, uint8_t* out_bits /* [n][nvar] */,
+                          int32_t* out_iters /* bp_decode's return values, may be NULL */);
+int lutldpc_bp_decode_qllr(lutldpc_bp* h, int n_frames, const int32_t* qllr_in, int32_t* qllr_out, int32_t* out_iters);
+int lutldpc_bp_encode(lutldpc_bp* h, int n_frames, const uint8_t* info, uint8_t* codeword);
+int lutldpc_bp_simulate_snr(lutldpc_bp* h, const lutldpc_sim_params* p, lutldpc_sim_counters* acc);
+/* device ms and kernel launches of the last decode/simulate call, like lutldpc_last_call_stats */
+int lutldpc_bp_last_call_stats(const lutldpc_bp* h, double* device_ms, int64_t* kernel_launches, int64_t* frame_iterations);
+/* frames that have returned are dropped from the batch once at most half of the slots are still running (the
+ * analogue of lutldpc_set_repack); on = 0 keeps every frame in its slot.  Results do not depend on it. */
+int lutldpc_bp_set_repack(lutldpc_bp* h, int on);
+
 #ifdef __cplusplus
 }
 #endif

@@ -82,6 +82,13 @@ class SimParams:
         self.min_lut = _flag(g("LUT", "min_lut", "true"))
         self.initial_message_mode = g("LUT", "initial_message_mode", "from_continuous_input")
         self.has_lut_section = cp.has_section("LUT") or g("Sim", "codec_type", "none") == "LUT"
+        # [BP]: the comparison decoder (src/LDPC_BER_Sim.cpp:74-78)
+        self.bp_max_iter = int(float(g("BP", "max_iter", 30)))
+        self.qllr_scale_res = int(float(g("BP", "qllr_scale_res", 12)))
+        self.qllr_table_size = int(float(g("BP", "qllr_table_size", 300)))
+        self.qllr_spacing_res = int(float(g("BP", "qllr_spacing_res", 7)))
+        self.qllr_total_res = int(float(g("BP", "qllr_total_res", 28)))
+        self.has_bp_section = cp.has_section("BP") or g("Sim", "codec_type", "none") == "BP"
         for k, v in over.items():
             setattr(self, k, v)
 
@@ -220,6 +227,42 @@ class LDPC_BER_Sim_LUT:
                 "sim_frame_errors": [int(a[1]) for _, a in P], "sim_Ndatabits": [int(a[2]) for _, a in P],
                 "sim_data_bit_errors": [int(a[3]) for _, a in P], "sim_uncoded_bit_errors": [int(a[5]) for _, a in P],
                 "sim_sum_iterations": [int(a[6]) for _, a in P], "sim_decode_failures": [int(a[7]) for _, a in P]}
+
+
+class LDPC_BER_Sim(LDPC_BER_Sim_LUT):
+    """The same harness around the BP comparison decoder: LDPC_BER_Sim::load (src/LDPC_BER_Sim.cpp:157-244) builds
+    IT++'s LDPC_Code from the alist with the LLR_calc_unit of the [BP] section; the frame loop is
+    lutldpc_bp_simulate_snr.  (In the reference this is the base class and the LUT harness derives from it; here the
+    shared part -- run, sim_snr_point, the stop rules and the all-reduce -- lives in LDPC_BER_Sim_LUT.)"""
+
+    def load(self, basedir="."):
+        from .capi import BpDecoder, alist_graph
+        p = self.p
+        if p.codec_filename:
+            raise RuntimeError("LDPC_BER_Sim::load(): stored bp_codec.it files are not supported, name the alist "
+                               "(LDPC.parity_filename)")
+        if not p.parity_filename:
+            raise RuntimeError("LDPC_BER_Sim::load(): LDPC.parity_filename is required")
+        alist = os.path.join(basedir, p.codes_dir, p.parity_filename + ".alist")
+        if not os.path.exists(alist):
+            raise RuntimeError("Parity file" + alist + " does not exist!")  # :162-164
+        self.dec = BpDecoder(alist_graph(alist), max_iters=p.bp_max_iter, psc=p.parity_check_iter, pisc=p.parity_check_iter,
+                             qllr_scale_res=p.qllr_scale_res, qllr_table_size=p.qllr_table_size,
+                             qllr_spacing_res=p.qllr_spacing_res, qllr_total_res=p.qllr_total_res,
+                             with_generator=not p.zero_codeword)
+        return self
+
+
+def make_sim(params, **kw):
+    """prog/ber_sim.cpp:136-147: a [LUT] section (or Sim.codec_type = LUT) selects the LUT decoder, else a [BP]
+    section the BP decoder, else it_error."""
+    if params.has_lut_section:
+        return LDPC_BER_Sim_LUT(params, **kw)
+    if params.has_bp_section:
+        return LDPC_BER_Sim(params, **kw)
+    raise RuntimeError("You must specify the type of decoder in the params file by either explicitly setting at least one "
+                       "parameter in the [LUT] or [BP] section of the parameter file or loading a codec via its filename "
+                       "and specifying its type")
 
 
 def counters_from_array(a):

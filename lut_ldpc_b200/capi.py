@@ -157,6 +157,11 @@ PROFILE_NAMES = {0: "reset", 1: "pack", 2: "channel", 3: "cn_minsum", 4: "syndro
                  7: "count", 8: "encode", 10: "repack", 11: "retire", 12: "onchip"}
 
 
+class _BpParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("max_iters", "psc", "pisc", "qllr_scale_res", "qllr_table_size",
+                                         "qllr_spacing_res", "qllr_total_res")]
+
+
 def load_library():
     global _lib
     if _lib is not None:
@@ -202,6 +207,18 @@ def load_library():
     L.lutldpc_create_systematic.argtypes = [vp, C.POINTER(vp), vp]
     L.lutldpc_decode_packed_device.argtypes = [vp, i32, vp, vp, vp]
     L.lutldpc_get_profile.argtypes = [vp, vp, vp, vp, vp]
+    L.lutldpc_bp_create.argtypes = [C.POINTER(_Graph), C.POINTER(_BpParams), i32, C.POINTER(vp), vp]
+    L.lutldpc_bp_destroy.argtypes = [vp]
+    L.lutldpc_bp_destroy.restype = None
+    L.lutldpc_bp_last_error.restype = C.c_char_p
+    L.lutldpc_bp_last_error.argtypes = [vp]
+    L.lutldpc_bp_get_info.argtypes = [vp, C.POINTER(_Info)]
+    L.lutldpc_bp_decode_llr.argtypes = [vp, i32, vp, vp, vp]
+    L.lutldpc_bp_decode_qllr.argtypes = [vp, i32, vp, vp, vp]
+    L.lutldpc_bp_encode.argtypes = [vp, i32, vp, vp]
+    L.lutldpc_bp_simulate_snr.argtypes = [vp, C.POINTER(_SimParams), C.POINTER(SimCounters)]
+    L.lutldpc_bp_last_call_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(i64)]
+    L.lutldpc_bp_set_repack.argtypes = [vp, i32]
     _lib = L
     return L
 
@@ -447,4 +464,83 @@ class Decoder:
     def last_call_stats(self):
         ms, nl, fi = C.c_double(0), C.c_int64(0), C.c_int64(0)
         self._ck(self._L.lutldpc_last_call_stats(self._h, C.byref(ms), C.byref(nl), C.byref(fi)))
+        return dict(device_ms=ms.value, kernel_launches=nl.value, frame_iterations=fi.value)
+
+
+class BpDecoder:
+    """One lutldpc_bp handle: IT++'s LDPC_Code with the LLR_calc_unit of ber_sim's [BP] section, batched
+    (itpp/itpp/comm/ldpc.cpp:1398-1622; src/LDPC_BER_Sim.cpp:74-78,197-201)."""
+
+    def __init__(self, graph, max_iters=30, psc=True, pisc=None, qllr_scale_res=12, qllr_table_size=300,
+                 qllr_spacing_res=7, qllr_total_res=28, with_generator=False):
+        """graph: the dict of alist_graph().  pisc defaults to psc, as LDPC_BER_Sim::load passes parity_check_iter twice."""
+        self._L = load_library()
+        pisc = psc if pisc is None else pisc
+        dv = np.ascontiguousarray(graph["dv_vec"], np.int32)
+        dc = np.ascontiguousarray(graph["dc_vec"], np.int32)
+        idx = np.ascontiguousarray(graph["cn_msg_idx"], np.int32)
+        i32p = C.POINTER(C.c_int32)
+        g = _Graph(int(dv.size), int(dc.size), int(idx.size), int(graph.get("nchk_lin_indep", -1)),
+                   dv.ctypes.data_as(i32p), dc.ctypes.data_as(i32p), idx.ctypes.data_as(i32p))
+        par = _BpParams(int(max_iters), int(bool(psc)), int(bool(pisc)), int(qllr_scale_res), int(qllr_table_size),
+                        int(qllr_spacing_res), int(qllr_total_res))
+        h = C.c_void_p()
+        self.col_perm = np.empty(dv.size, np.int32)
+        rc = self._L.lutldpc_bp_create(C.byref(g), C.byref(par), int(bool(with_generator)), C.byref(h), _p(self.col_perm))
+        if rc != 0:
+            raise LutLdpcError(rc, (self._L.lutldpc_bp_last_error(None) or b"").decode())
+        self._h = h
+        info = _Info()
+        self._ck(self._L.lutldpc_bp_get_info(self._h, C.byref(info)))
+        self.nvar, self.nchk, self.ninfo, self.num_edges = info.nvar, info.nchk, info.ninfo, info.num_edges
+        self.nchk_lin_indep, self.max_iters, self.has_gen, self.rate = info.nchk_lin_indep, info.max_iters, bool(info.has_gen), info.rate
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.lutldpc_bp_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise LutLdpcError(rc, (self._L.lutldpc_bp_last_error(self._h) or b"").decode())
+
+    def set_repack(self, on):
+        self._ck(self._L.lutldpc_bp_set_repack(self._h, int(bool(on))))
+
+    def decode_llr(self, llr):
+        """LDPC_Code::decode for [n, nvar] LLRs -> (hard decisions of all nvar bits [n, nvar], bp_decode returns [n])."""
+        llr = np.ascontiguousarray(llr, np.float64).reshape(-1, self.nvar)
+        n = llr.shape[0]
+        bits = np.empty((n, self.nvar), np.uint8)
+        iters = np.empty(n, np.int32)
+        self._ck(self._L.lutldpc_bp_decode_llr(self._h, n, _p(llr), _p(bits), _p(iters)))
+        return bits, iters
+
+    def decode_qllr(self, qllr):
+        """LDPC_Code::bp_decode for [n, nvar] QLLRs -> (LLRout [n, nvar] int32, returns [n])."""
+        q = np.ascontiguousarray(qllr, np.int32).reshape(-1, self.nvar)
+        n = q.shape[0]
+        out = np.empty((n, self.nvar), np.int32)
+        iters = np.empty(n, np.int32)
+        self._ck(self._L.lutldpc_bp_decode_qllr(self._h, n, _p(q), _p(out), _p(iters)))
+        return out, iters
+
+    def encode(self, info):
+        info = np.ascontiguousarray(info, np.uint8).reshape(-1, self.ninfo)
+        cw = np.empty((info.shape[0], self.nvar), np.uint8)
+        self._ck(self._L.lutldpc_bp_encode(self._h, info.shape[0], _p(info), _p(cw)))
+        return cw
+
+    def simulate_snr(self, snr_db, n_frames, seed=0, first_frame=0, zero_codeword=True, batch_frames=0, acc=None):
+        p = _SimParams(float(snr_db), int(n_frames), int(seed), int(first_frame), int(bool(zero_codeword)),
+                       int(batch_frames))
+        acc = acc if acc is not None else SimCounters()
+        self._ck(self._L.lutldpc_bp_simulate_snr(self._h, C.byref(p), C.byref(acc)))
+        return acc
+
+    def last_call_stats(self):
+        ms, nl, fi = C.c_double(), C.c_int64(), C.c_int64()
+        self._ck(self._L.lutldpc_bp_last_call_stats(self._h, C.byref(ms), C.byref(nl), C.byref(fi)))
         return dict(device_ms=ms.value, kernel_launches=nl.value, frame_iterations=fi.value)

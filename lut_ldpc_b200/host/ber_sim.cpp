@@ -32,6 +32,7 @@
 #include <vector>
 #include <sys/stat.h>
 
+#include "ldpc_code_bp.hpp"
 #include "ldpc_code_lut.hpp"
 
 // Minimal IT++ it_file (format version 3) writer: "IT++" 0x03, then per variable u64 hdr_bytes, data_bytes,
@@ -162,9 +163,14 @@ int main(int argc, char** argv) {
   auto path = [&](const std::string& p) { return (!p.empty() && p[0] == '/') ? p : basedir + "/" + p; };
   Ini ini;
   if (!ini.read(path(params))) { std::cerr << "cannot read " << path(params) << "\n"; return 1; }
-  // prog/ber_sim.cpp:134-147: the LUT simulation is selected by a [LUT] section or Sim.codec_type
-  if (!ini.has_section("LUT") && ini.get("Sim.codec_type", "none") != "LUT") {
-    std::cerr << "Only the LUT decoder ([LUT] section) is implemented on the GPU path\n";
+  // prog/ber_sim.cpp:134-147: a [LUT] section (or Sim.codec_type = LUT) selects the LUT decoder, else a [BP] section
+  // (or codec_type = BP) the BP comparison decoder
+  const bool use_lut = ini.has_section("LUT") || ini.get("Sim.codec_type", "none") == "LUT";
+  const bool use_bp = !use_lut && (ini.has_section("BP") || ini.get("Sim.codec_type", "none") == "BP");
+  if (!use_lut && !use_bp) {
+    std::cerr << "You must specify the type of decoder in the params file by either\n * explicitly setting at least one "
+                 "parameter in the [LUT] or [BP] section of the parameter file\n * loading a codec via its filename and "
+                 "specifying its type\n";
     return 1;
   }
   try {
@@ -187,12 +193,26 @@ int main(int argc, char** argv) {
     if (ndev <= 0) throw std::runtime_error("no CUDA device (there is no CPU fallback)");
     if (gpus < 1 || gpus > ndev) throw std::runtime_error("--gpus exceeds the number of visible devices");
     std::vector<std::unique_ptr<LDPC_Code_LUT>> C(gpus);
+    std::vector<std::unique_ptr<LDPC_Code>> Cbp(gpus);
     auto configure = [&](LDPC_Code_LUT& c) {
       const int mi = ini.has("LUT.max_iter") ? (int)ini.num("LUT.max_iter", 30) : c.get_nrof_iterations();
       c.set_exit_conditions(mi, pci, pci);  // psc = pisc = parity_check_iter, src/LDPC_BER_Sim.cpp:500
       c.set_initial_message_mode(imode == "from_quantized_channel_llrs" ? LDPC_Code_LUT::QCHA : LDPC_Code_LUT::CONT);
     };
-    if (!codec.empty()) {
+    if (use_bp) {
+      // ---- LDPC_BER_Sim::load, src/LDPC_BER_Sim.cpp:157-244: LDPC_Parity(alist) [+ LDPC_Generator_Systematic] ->
+      // LDPC_Code, exit conditions (max_iter, pci, pci) and the LLR_calc_unit of the [BP] section
+      if (!codec.empty()) throw std::runtime_error("LDPC_BER_Sim::load(): stored bp_codec.it files are not supported, name the alist");
+      const std::string alist = path(codes_dir + "/" + ini.get("LDPC.parity_filename", "") + ".alist");
+      struct stat sb;
+      if (stat(alist.c_str(), &sb) != 0) throw std::runtime_error("Parity file" + alist + " does not exist!");  // :162-164
+      LLR_calc_unit lc((short)ini.num("BP.qllr_scale_res", 12), (short)ini.num("BP.qllr_table_size", 300),
+                       (short)ini.num("BP.qllr_spacing_res", 7), (short)ini.num("BP.qllr_total_res", 28));
+      for (int g = 0; g < gpus; ++g) {
+        if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
+        Cbp[g].reset(new LDPC_Code(alist, !zero_cw, (int)ini.num("BP.max_iter", 30), pci, pci, lc));
+      }
+    } else if (!codec.empty()) {
       // codes_path / codec_filename (src/LDPC_BER_Sim.cpp:524), else relative to the base directory
       std::string codec_file = path(codes_dir + "/" + codec);
       struct stat sb;
@@ -274,14 +294,18 @@ int main(int argc, char** argv) {
       lutldpc_graph_free(&gr);
       std::cout << "Designed LUT decoder for " << alist << " (sigma2 = " << sigma2 << ", " << max_iter << " iterations)" << std::endl;
     }
-    for (int g = 0; g < gpus; ++g) {
+    for (int g = 0; g < gpus && use_lut; ++g) {
       if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
       configure(*C[g]);
     }
-    const int N = C[0]->get_nvar(), K = C[0]->get_ninfo();
-    std::ostringstream name;  // gen_filename, src/LDPC_BER_Sim.cpp:553-568
-    name << results_prefix << "_N" << N << "_R" << C[0]->get_rate() << "_maxIter" << C[0]->get_nrof_iterations() << "_zcw"
-         << (int)zero_cw << "_frames" << Nframes << (C[0]->is_min_lut() ? "_minLUT" : "_LUT") << custom;
+    const int N = use_bp ? Cbp[0]->get_nvar() : C[0]->get_nvar(), K = use_bp ? Cbp[0]->get_ninfo() : C[0]->get_ninfo();
+    const int nchk = use_bp ? Cbp[0]->get_ncheck() : C[0]->get_nchk();
+    const double rate = use_bp ? Cbp[0]->get_rate() : C[0]->get_rate();
+    std::ostringstream name;  // gen_filename, src/LDPC_BER_Sim.cpp:104-114 (BP), :553-568 (LUT)
+    name << results_prefix << "_N" << N << "_R" << rate << "_maxIter" << (use_bp ? Cbp[0]->get_nrof_iterations() : C[0]->get_nrof_iterations())
+         << "_zcw" << (int)zero_cw << "_frames" << Nframes;
+    if (use_lut) name << (C[0]->is_min_lut() ? "_minLUT" : "_LUT");
+    name << custom;
 
     // ---- run(), src/LDPC_BER_Sim.cpp:121-155
     auto t0 = std::chrono::steady_clock::now();
@@ -320,7 +344,7 @@ int main(int argc, char** argv) {
             lutldpc_sim_params sp;
             sp.snr_db = snr; sp.n_frames = n; sp.seed = seed + seed_off; sp.first_frame = next_frame + (uint64_t)off;
             sp.zero_codeword = zero_cw; sp.batch_frames = batch;
-            if (verbosity > 0) {
+            if (verbosity > 0 && use_lut) {
               // LUT.output_verbosity > 0: the "Stimuli Pair" print of LDPC_Code_LUT::decode (src/LDPC_Code_LUT.cpp:228-238),
               // frame by frame in frame order -- the golden vectors of the reference's VHDL flow
               std::vector<uint8_t> lab((size_t)n * N), bits((size_t)n * N);
@@ -338,7 +362,10 @@ int main(int argc, char** argv) {
               continue;
             }
             th.emplace_back([&, g, sp]() {
-              try { C[g]->simulate_snr(sp, part[g]); } catch (const std::exception& e) { errs[g] = e.what(); }
+              try {
+                if (use_bp) Cbp[g]->simulate_snr(sp, part[g]);
+                else C[g]->simulate_snr(sp, part[g]);
+              } catch (const std::exception& e) { errs[g] = e.what(); }
             });
             off += n;
           }
@@ -387,8 +414,8 @@ int main(int argc, char** argv) {
     arr("sim_Nuncodedbits", &lutldpc_sim_counters::uncoded_bits);
     arr("sim_sum_iterations", &lutldpc_sim_counters::sum_iters);
     arr("sim_decode_failures", &lutldpc_sim_counters::decode_failures);
-    js << "  \"ldpc_nvar\": " << N << ",\n  \"ldpc_nchk\": " << C[0]->get_nchk() << ",\n  \"ldpc_code_rate\": "
-       << C[0]->get_rate() << ",\n  \"ldpc_ninfo\": " << K << ",\n  \"runtime\": " << runtime << ",\n  \"gpus\": " << gpus
+    js << "  \"ldpc_nvar\": " << N << ",\n  \"ldpc_nchk\": " << nchk << ",\n  \"ldpc_code_rate\": "
+       << rate << ",\n  \"ldpc_ninfo\": " << K << ",\n  \"runtime\": " << runtime << ",\n  \"gpus\": " << gpus
        << ",\n  \"gitversion\": \"lut_ldpc_b200\"\n}\n";
     js.close();
     {  // LDPC_BER_Sim_Results::write_itfile, src/LDPC_BER_Sim.cpp:342-361
@@ -407,8 +434,8 @@ int main(int argc, char** argv) {
       it.vec("sim_data_bit_errors", col(&lutldpc_sim_counters::data_bit_errors));
       it.vec("sim_uncoded_bit_errors", col(&lutldpc_sim_counters::uncoded_bit_errors));
       it.vec("ldpc_nvar", {(double)N});
-      it.vec("ldpc_nchk", {(double)C[0]->get_nchk()});
-      it.vec("ldpc_code_rate", {C[0]->get_rate()});
+      it.vec("ldpc_nchk", {(double)nchk});
+      it.vec("ldpc_code_rate", {rate});
       it.f64("runtime", runtime);
       it.str("gitversion", "lut_ldpc_b200");
     }

@@ -195,3 +195,70 @@ def same_msgs(ref_msgs, mine):
         import hashlib
         return hashlib.sha256(mine.tobytes()).digest() == ref_msgs
     return np.array_equal(ref_msgs, mine)
+
+
+# ---- BP comparison decoder (oracle/bp_oracle.c: LDPC_Code::bp_decode, itpp/itpp/comm/ldpc.cpp:1398-1622)
+class BpParams:
+    """max_iter, exit conditions and the four LLR_calc_unit parameters of the [BP] section (src/LDPC_BER_Sim.cpp:74-78)."""
+
+    def __init__(self, max_iter=30, psc=True, pisc=True, d1=12, d2=300, d3=7, d4=28):
+        self.max_iter, self.psc, self.pisc, self.d1, self.d2, self.d3, self.d4 = max_iter, bool(psc), bool(pisc), d1, d2, d3, d4
+
+
+def bp_to_qllr(llr, d1=12, d4=28):
+    L = lib()
+    llr = np.ascontiguousarray(llr, np.float64)
+    out = np.empty(llr.shape, np.int32)
+    L.bp_oracle_to_qllr(C.c_int(d1), C.c_int(d4), _p(llr), C.c_int(llr.size), _p(out))
+    return out
+
+
+def bp_logexp_table(d1=12, d2=300, d3=7, d4=28):
+    out = np.empty(d2, np.int32)
+    lib().bp_oracle_logexp_table(C.c_int(d1), C.c_int(d2), C.c_int(d3), C.c_int(d4), _p(out))
+    return out
+
+
+def bp_decode(dv, dc, cn_msg_idx, qllr_in, par):
+    """One frame or [n][nvar] frames of QLLR through bp_decode -> (qllr_out, ret)."""
+    L = lib()
+    L.bp_oracle_decode.restype = C.c_int
+    dv = np.ascontiguousarray(dv, np.int32)
+    dc = np.ascontiguousarray(dc, np.int32)
+    idx = np.ascontiguousarray(cn_msg_idx, np.int32)
+    q = np.ascontiguousarray(qllr_in, np.int32)
+    single = q.ndim == 1
+    q2 = q.reshape(-1, dv.size)
+    out = np.empty_like(q2)
+    ret = np.empty(q2.shape[0], np.int32)
+    for f in range(q2.shape[0]):
+        row = np.ascontiguousarray(q2[f])
+        o = np.empty(dv.size, np.int32)
+        ret[f] = L.bp_oracle_decode(C.c_int(dv.size), C.c_int(dc.size), _p(dv), _p(dc), _p(idx), C.c_int(par.max_iter),
+                                    C.c_int(par.psc), C.c_int(par.pisc), C.c_int(par.d1), C.c_int(par.d2), C.c_int(par.d3),
+                                    C.c_int(par.d4), _p(row), _p(o))
+        out[f] = o
+    return (out[0], int(ret[0])) if single else (out, ret)
+
+
+def read_bp_fixture(path):
+    """BPFIX001 (oracle/ref_driver.cpp cmd_bpfixture): the reference's LLRs, to_qllr, bp_decode output/return, decode() bits."""
+    import lzma
+    import struct
+    raw = (lzma.open(path).read() if str(path).endswith(".xz") else open(path, "rb").read())
+    assert raw[:8] == b"BPFIX001"
+    N, nf, mi, psc, pisc, d1, d2, d3, d4, K, with_llr = struct.unpack("<11i", raw[8:52])
+    snr, scale = struct.unpack("<2d", raw[52:68])
+    off = 68
+    fx = dict(nvar=N, ninfo=K, par=BpParams(mi, psc, pisc, d1, d2, d3, d4), snr=snr, scale=scale,
+              llr=np.empty((nf, N)) if with_llr else None, qin=np.empty((nf, N), np.int32), qout=np.empty((nf, N), np.int32),
+              ret=np.empty(nf, np.int32), syst=np.empty((nf, K), np.uint8))
+    for f in range(nf):
+        if with_llr:
+            fx["llr"][f] = np.frombuffer(raw, "<f8", N, off); off += 8 * N
+        fx["qin"][f] = np.frombuffer(raw, "<i4", N, off); off += 4 * N
+        fx["qout"][f] = np.frombuffer(raw, "<i4", N, off); off += 4 * N
+        fx["ret"][f] = struct.unpack("<i", raw[off:off + 4])[0]; off += 4
+        fx["syst"][f] = np.frombuffer(raw, "u1", K, off); off += K
+    assert off == len(raw)
+    return fx

@@ -381,9 +381,99 @@ static int cmd_results(const Args& a) {
   return 0;
 }
 
+
+// ---- the BP comparison decoder of ber_sim's [BP] section (src/LDPC_BER_Sim.cpp:157-244): IT++'s LDPC_Code with the
+// LLR_calc_unit the .ini names.  bpfixture records, per frame, the channel LLRs, to_qllr of them, bp_decode's
+// soft output and its return value; bpsim is the frame loop of sim_snr_point around LDPC_Code::decode.
+static LDPC_Code* load_bp(const Args& a, const std::string& alist, LDPC_Parity** Hout) {
+  LDPC_Parity* H = new LDPC_Parity(alist, "alist");
+  LDPC_Code* C = new LDPC_Code(H);
+  bool psc = a.num("psc", 1) != 0, pisc = a.num("pisc", a.num("psc", 1)) != 0;  // load(): (max_iter, pci, pci), :200
+  C->set_exit_conditions((int)a.num("max-iter", 30), psc, pisc);
+  C->set_llrcalc(LLR_calc_unit((short)a.num("d1", 12), (short)a.num("d2", 300), (short)a.num("d3", 7),
+                               (short)a.num("d4", 8 * (int)sizeof(QLLR) - 4)));
+  if (Hout) *Hout = H;
+  return C;
+}
+
+static int cmd_bpfixture(const Args& a) {
+  if (a.pos.size() < 2) { fprintf(stderr, "bpfixture <code.alist> <out.fix> [options]\n"); return 2; }
+  LDPC_Code* C = load_bp(a, a.pos[0], nullptr);
+  int N = C->get_nvar();
+  int n_frames = (int)a.num("frames", 8);
+  double snr = a.num("snr", 1.0), scale = a.num("llr-scale", 1.0);
+  RNG_reset((unsigned)a.num("seed", 0));
+  double N0 = itpp::pow10(-snr / 10.0) / C->get_rate();
+  AWGN_Channel chan(N0 / 2); BPSK Mod;
+  LLR_calc_unit lc = C->get_llrcalc();
+  std::ofstream os(a.pos[1].c_str(), std::ios::binary);
+  os.write("BPFIX001", 8);
+  put_i32(os, N); put_i32(os, n_frames); put_i32(os, C->get_nrof_iterations());
+  put_i32(os, (int)(a.num("psc", 1) != 0)); put_i32(os, (int)(a.num("pisc", a.num("psc", 1)) != 0));
+  ivec d = lc.get_Dint();
+  for (int i = 0; i < 4; i++) put_i32(os, d(i));
+  put_i32(os, C->get_ninfo());
+  const bool with_llr = a.num("with-llr", 1) != 0;  // large codes: keep only to_qllr of the LLRs
+  put_i32(os, (int)with_llr);
+  put_f64(os, snr); put_f64(os, scale);
+  for (int ff = 0; ff < n_frames; ff++) {
+    vec x = chan(Mod.modulate_bits(zeros_b(N)));
+    vec llr = Mod.demodulate_soft_bits(x, N0) * scale;  // scale > 1 drives the saturation branches
+    QLLRvec qin = lc.to_qllr(llr), qout;
+    int ret = C->bp_decode(qin, qout);
+    bvec syst = C->decode(llr);  // the call ber_sim makes
+    if (with_llr) for (int i = 0; i < N; i++) put_f64(os, llr(i));
+    for (int i = 0; i < N; i++) put_i32(os, qin(i));
+    for (int i = 0; i < N; i++) put_i32(os, qout(i));
+    put_i32(os, ret);
+    for (int i = 0; i < syst.length(); i++) os.put((char)(int)syst(i));
+  }
+  return 0;
+}
+
+static int cmd_bpsim(const Args& a) {
+  if (a.pos.size() < 1) { fprintf(stderr, "bpsim <code.alist> --snr a,b,.. [options]\n"); return 2; }
+  double tl0 = now_s();
+  LDPC_Code* C = load_bp(a, a.pos[0], nullptr);
+  double tl1 = now_s();
+  int N = C->get_nvar(), K = C->get_ninfo();
+  int64_t Nframes = (int64_t)a.num("frames", 100);
+  int Nfers = (int)a.num("nfers", 1 << 30);
+  double max_seconds = a.num("max-seconds", 1e30);
+  std::vector<double> snrs = parse_list(a.get("snr", "1.0"));
+  RNG_reset((unsigned)a.num("seed", 0));
+  for (double snr : snrs) {
+    double N0 = itpp::pow10(-snr / 10.0) / C->get_rate();
+    AWGN_Channel chan(N0 / 2);
+    BERC berc_data, berc_uncoded; BLERC ferc; BPSK Mod;
+    ferc.set_blocksize(K);
+    bvec bitsin = zeros_b(K), bitsin_coded = zeros_b(N);
+    double t0 = now_s();
+    for (int64_t ff = 0; ff < Nframes; ff++) {
+      vec x = chan(Mod.modulate_bits(bitsin_coded));
+      vec softbits = Mod.demodulate_soft_bits(x, N0);
+      bvec bitsout_slicer = Mod.demodulate_bits(x);
+      bvec bitsout = C->decode(softbits);
+      berc_data.count(bitsin, bitsout);
+      berc_uncoded.count(bitsin_coded, bitsout_slicer);
+      ferc.count(bitsin, bitsout);
+      if (ferc.get_errors() > Nfers) break;
+      if (now_s() - t0 > max_seconds) break;
+    }
+    double wall = now_s() - t0;
+    printf("{\"cmd\":\"bpsim\",\"snr_db\":%.6g,\"frames\":%.0f,\"data_bits\":%.0f,\"data_bit_errors\":%.0f,"
+           "\"uncoded_bits\":%.0f,\"uncoded_bit_errors\":%.0f,\"frame_errors\":%.0f,"
+           "\"wall_s\":%.6f,\"load_s\":%.3f,\"nvar\":%d,\"ninfo\":%d}\n",
+           snr, ferc.get_total_blocks(), berc_data.get_total_bits(), berc_data.get_errors(),
+           berc_uncoded.get_total_bits(), berc_uncoded.get_errors(), ferc.get_errors(), wall, tl1 - tl0, N, K);
+    fflush(stdout);
+  }
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 2) {
-    fprintf(stderr, "usage: lutldpc_ref design|bundle|fixture|sim|results ...\n");
+    fprintf(stderr, "usage: lutldpc_ref design|bundle|fixture|sim|results|bpfixture|bpsim ...\n");
     return 2;
   }
   std::string cmd = argv[1];
@@ -393,6 +483,8 @@ int main(int argc, char** argv) {
   if (cmd == "fixture") return cmd_fixture(a);
   if (cmd == "sim") return cmd_sim(a);
   if (cmd == "results") return cmd_results(a);
+  if (cmd == "bpfixture") return cmd_bpfixture(a);
+  if (cmd == "bpsim") return cmd_bpsim(a);
   fprintf(stderr, "unknown command %s\n", cmd.c_str());
   return 2;
 }

@@ -6,6 +6,7 @@ import sys
 import textwrap
 
 import numpy as np
+import pytest
 
 from lut_ldpc_b200 import ber_sim as bs
 
@@ -124,3 +125,36 @@ def test_chunks_follow_the_fer_estimate_so_the_nfers_stop_overshoots_little():
     sim = bs.LDPC_BER_Sim_LUT(p, simulate=_fake(lambda s: 0.5), chunk_frames=8192)
     acc, used, _ = sim.sim_snr_point(1.0, 0)
     assert acc[1] > 20 and used == 1344
+
+
+BP_INI = """
+[Sim]
+   SNRdB = 1:1:3
+[LDPC]
+   parity_filename = somecode
+[BP]
+   max_iter = 40
+   qllr_table_size = 0   ; min-sum
+"""
+
+
+def test_bp_section_selects_the_bp_harness(tmp_path):
+    """prog/ber_sim.cpp:136-147: [LUT] wins, else [BP], else it_error; [BP] defaults of src/LDPC_BER_Sim.cpp:74-78"""
+    f = tmp_path / "bp.ini"
+    f.write_text(BP_INI)
+    p = bs.SimParams(str(f))
+    assert p.has_bp_section and not p.has_lut_section
+    assert (p.bp_max_iter, p.qllr_scale_res, p.qllr_table_size, p.qllr_spacing_res, p.qllr_total_res) == (40, 12, 0, 7, 28)
+    assert type(bs.make_sim(p)) is bs.LDPC_BER_Sim
+    f.write_text(INI)
+    assert type(bs.make_sim(bs.SimParams(str(f)))) is bs.LDPC_BER_Sim_LUT
+    f.write_text("[Sim]\nSNRdB = 1\n")
+    with pytest.raises(RuntimeError, match="type of decoder"):
+        bs.make_sim(bs.SimParams(str(f)))
+    f.write_text("[Sim]\nSNRdB = 1\ncodec_type = BP\n")
+    assert type(bs.make_sim(bs.SimParams(str(f)))) is bs.LDPC_BER_Sim
+    # the shared run loop works for the BP harness too (stop rules, chunking)
+    f.write_text(BP_INI)
+    sim = bs.make_sim(bs.SimParams(str(f), Nframes=3000, Nfers=10), simulate=_fake(lambda s: {1.0: 0.2}.get(s, 0.0)), chunk_frames=256)
+    r = sim.run(verbose=False)
+    assert r["sim_frame_errors"][0] > 10 and r["sim_Nframes"][1] == 3000 and r["sim_Nframes"][2] == 0

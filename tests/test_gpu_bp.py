@@ -1,0 +1,171 @@
+"""BP comparison decoder (the [BP] section of ber_sim: IT++'s LDPC_Code::bp_decode, batched on the GPU) through the C
+ABI: bit-exact against the reference's golden vectors (tests/golden/bp/) and against the C oracle on random batches
+with frames that return at different iterations; the Monte-Carlo step against the reference's BER/FER points."""
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+import _alist
+import _bpgolden
+import _golden
+import pyoracle
+
+pytestmark = pytest.mark.gpu
+BER = json.load(open(os.path.join(_golden.GOLD, "bp_ber_reference.json")))
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from lut_ldpc_b200 import capi
+    return capi
+
+
+def _dec(capi, g, par, **kw):
+    return capi.BpDecoder(g, max_iters=par.max_iter, psc=par.psc, pisc=par.pisc, qllr_scale_res=par.d1,
+                          qllr_table_size=par.d2, qllr_spacing_res=par.d3, qllr_total_res=par.d4, **kw)
+
+
+@pytest.mark.parametrize("name", _bpgolden.CASES)
+def test_bp_decode_matches_reference(capi, name):
+    """bp_decode: soft output and return value of every golden frame; decode(): the bits ber_sim counts"""
+    fx = _bpgolden.fixture(name)
+    g = _bpgolden.graph(name)
+    dec = _dec(capi, g, fx["par"])
+    assert dec.nvar == fx["nvar"] and dec.ninfo == fx["ninfo"]
+    out, ret = dec.decode_qllr(fx["qin"])
+    assert np.array_equal(ret, fx["ret"])
+    assert np.array_equal(out, fx["qout"])
+    if fx["llr"] is not None:
+        bits, ret2 = dec.decode_llr(fx["llr"])
+        assert np.array_equal(ret2, fx["ret"])
+        assert np.array_equal(bits[:, :fx["ninfo"]], fx["syst"])
+        assert np.array_equal(bits, (fx["qout"] < 0).astype(np.uint8))
+
+
+def _noisy_llr(g_nvar, n, snr_db, rate, seed):
+    rng = np.random.default_rng(seed)
+    N0 = 10 ** (-snr_db / 10) / rate
+    x = 1.0 + math.sqrt(N0 / 2) * rng.standard_normal((n, g_nvar))
+    return 4 * x / N0
+
+
+@pytest.mark.parametrize("name,snr,kw", [
+    ("c2_default", 1.6, {}),
+    ("c2_default", 2.2, dict(qllr_table_size=0)),
+    ("c1b_default", 1.8, {}),
+    ("synth_mixed", 2.5, {}),
+    ("synth_wide_dc48", 4.2, dict(qllr_total_res=12)),
+])
+def test_bp_batch_vs_oracle_with_and_without_repacking(capi, name, snr, kw):
+    """700 frames that return between iteration 0 and never: every frame equals the oracle's, whether the batch is
+    narrowed while it runs or not (soft output: fixed slots; bits: repacked batches)"""
+    g = _bpgolden.graph(name)
+    par = pyoracle.BpParams(max_iter=25, d2=kw.get("qllr_table_size", 300), d4=kw.get("qllr_total_res", 28))
+    dec = _dec(capi, g, par)
+    llr = _noisy_llr(g["nvar"], 700, snr, dec.rate, seed=11)
+    llr[5] = np.abs(llr[5])  # a frame whose initial syndrome check passes
+    qin = pyoracle.bp_to_qllr(llr, par.d1, par.d4)
+    want_out, want_ret = pyoracle.bp_decode(g["dv_vec"], g["dc_vec"], g["cn_msg_idx"], qin, par)
+    assert want_ret[5] == 0 and (want_ret > 0).sum() > 100 and len(set(want_ret.tolist())) > 5
+    out, ret = dec.decode_qllr(qin)
+    assert np.array_equal(ret, want_ret) and np.array_equal(out, want_out)
+    for on in (True, False):
+        dec.set_repack(on)
+        bits, ret2 = dec.decode_llr(llr)
+        assert np.array_equal(ret2, want_ret)
+        assert np.array_equal(bits, (want_out < 0).astype(np.uint8))
+
+
+def test_bp_alist_reader_and_create_errors(capi, tmp_path):
+    """the graph through lutldpc_alist_graph equals the one built in Python; degrees the reference refuses are refused"""
+    N, rows = _alist.synth_rows("mixed")
+    p = str(tmp_path / "mixed.alist")
+    _alist.write_alist_rows(N, rows, p)
+    ga, gp = capi.alist_graph(p), _alist.graph_from_rows(N, rows)
+    for k in ("dv_vec", "dc_vec", "cn_msg_idx"):
+        assert np.array_equal(ga[k], gp[k])
+    bad = _alist.graph_from_rows(6, [[0, 1, 2], [3], [2, 4, 5]])
+    with pytest.raises(capi.LutLdpcError, match=r"sumX2\(j\)=1"):
+        capi.BpDecoder(bad)
+    with pytest.raises(capi.LutLdpcError, match="Resolution too large"):
+        capi.BpDecoder(gp, qllr_total_res=29)
+
+
+def _agree(k1, n1, k2, n2, z=3.29):
+    pool = (k1 + k2) / (n1 + n2)
+    se = math.sqrt(max(pool * (1 - pool), 1e-300) * (1 / n1 + 1 / n2))
+    return abs(k1 / n1 - k2 / n2) <= z * se + 3.0 / min(n1, n2)
+
+
+@pytest.mark.parametrize("key", sorted(BER))
+def test_bp_ber_fer_against_reference_points(capi, key):
+    """FER inside the 99.9 % two-sample interval at every reference point; BER within a factor set by the burst
+    statistics (errors come in frames); the slicer's error rate equals Q(sqrt(2 R Eb/N0))"""
+    cfg = key.split(":")[0]
+    g = _alist.bundle_graph(cfg)
+    extra = BER[key]["_args"].split()
+    kv = {extra[i][2:]: int(extra[i + 1]) for i in range(0, len(extra) - 1, 2)}
+    dec = capi.BpDecoder(g, max_iters=kv.get("max-iter", 30), qllr_table_size=kv.get("d2", 300))
+    n = 20000 if g["nvar"] <= 1000 else 2048
+    for snr_s, r in sorted(BER[key].items()):
+        if snr_s.startswith("_"):
+            continue
+        c = dec.simulate_snr(float(snr_s), n, seed=9)
+        assert c.frames == n and c.data_bits == n * dec.ninfo and c.uncoded_bits == n * dec.nvar
+        assert _agree(c.frame_errors, c.frames, r["frame_errors"], r["frames"]), (key, snr_s, c.frame_errors, r)
+        if r["frame_errors"] >= 30:
+            per_frame_ref = r["data_bit_errors"] / r["frame_errors"]
+            per_frame = c.data_bit_errors / max(1, c.frame_errors)
+            assert 0.6 < per_frame / per_frame_ref < 1.6, (key, snr_s, per_frame, per_frame_ref)
+        p_unc = 0.5 * math.erfc(math.sqrt(dec.rate * 10 ** (float(snr_s) / 10)))
+        assert abs(c.uncoded_bit_errors / c.uncoded_bits - p_unc) < 4 * math.sqrt(p_unc / c.uncoded_bits)
+        assert c.sum_iters > 0 and sum(c.iter_hist) == n
+
+
+def test_bp_simulate_invariances(capi):
+    """the counters do not depend on repacking, on the batch size or on how the frame range is split (what the
+    multi-GPU harness relies on), and the noise is the LUT decoder's for the same seed"""
+    import lut_ldpc_b200 as L
+    g = _alist.bundle_graph("c2_irr_n500")
+    dec = capi.BpDecoder(g)
+    a = dec.simulate_snr(2.0, 3000, seed=4).as_array()
+    dec.set_repack(False)
+    assert np.array_equal(dec.simulate_snr(2.0, 3000, seed=4).as_array(), a)
+    dec.set_repack(True)
+    assert np.array_equal(dec.simulate_snr(2.0, 3000, seed=4, batch_frames=512).as_array(), a)
+    acc = dec.simulate_snr(2.0, 1000, seed=4)
+    acc = dec.simulate_snr(2.0, 2000, seed=4, first_frame=1000, acc=acc)
+    assert np.array_equal(acc.as_array(), a)
+    lut = L.Decoder(_golden.bundle_path("c2_irr_n500"))
+    assert lut.simulate_snr(2.0, 3000, seed=4).uncoded_bit_errors == a[5]
+
+
+def test_bp_generator_and_random_codewords(capi):
+    """LDPC_Generator_Systematic + LDPC_Code(H, G): codewords satisfy the permuted H, decode to themselves, and the
+    Monte-Carlo step with random codewords sees the error rates of the all-zero one"""
+    g = _alist.bundle_graph("c1b_reg36_n1000")
+    dec = capi.BpDecoder(g, with_generator=True)
+    assert dec.has_gen and dec.ninfo + dec.nchk_lin_indep == dec.nvar
+    assert sorted(dec.col_perm.tolist()) == list(range(dec.nvar))
+    rng = np.random.default_rng(3)
+    info = rng.integers(0, 2, (300, dec.ninfo), dtype=np.uint8)
+    cw = dec.encode(info)
+    assert np.array_equal(cw[:, :dec.ninfo], info)
+    # H of the permuted code: column v of the original is column col_perm[v]
+    orc_rows = _alist.synth_rows  # noqa: F841 (rows of the bundle graph below)
+    dv, idx = g["dv_vec"], g["cn_msg_idx"]
+    edge_vn = np.repeat(np.arange(g["nvar"]), dv)
+    cs = np.concatenate([[0], np.cumsum(g["dc_vec"])])
+    for c in range(0, g["nchk"], 7):
+        cols = dec.col_perm[edge_vn[idx[cs[c]:cs[c + 1]]]]
+        assert not (cw[:, cols].sum(axis=1) & 1).any()
+    llr = (1.0 - 2.0 * cw) * 6.0
+    bits, ret = dec.decode_llr(llr)
+    assert np.array_equal(bits, cw) and (ret == 0).all()
+    z = dec.simulate_snr(1.8, 20000, seed=1, zero_codeword=True)
+    r = dec.simulate_snr(1.8, 20000, seed=2, zero_codeword=False)
+    assert _agree(z.frame_errors, z.frames, r.frame_errors, r.frames)
+    assert abs(z.uncoded_bit_errors - r.uncoded_bit_errors) < 6 * math.sqrt(z.uncoded_bit_errors)
