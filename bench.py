@@ -363,6 +363,33 @@ def run_b200(args):
                   "call": "lutldpc_decode_packed (pinned host: cha | msg << 4 per symbol in, bit-packed decisions + "
                           "iteration counts out): the same decode with 2.65x fewer bytes across PCIe"}
 
+    # ---- the BP comparison decoder of ber_sim's [BP] section on the same code and SNR (IT++ LDPC_Code::bp_decode,
+    # int32 QLLR messages, [BP] defaults except max_iter = the LUT decoder's): Monte-Carlo step on the device
+    import _alist
+    from lut_ldpc_b200 import capi as _capi
+    bp_graph = _alist.bundle_graph(cfg)
+    bp_graph["nchk_lin_indep"] = N - K  # same rate as the LUT decoder of this bundle
+    bpd = _capi.BpDecoder(bp_graph, max_iters=dec.max_iters)
+    Fbp = min(F, 8192)
+    bpd.simulate_snr(snr, Fbp, seed=5, batch_frames=Fbp)
+    bp_ms, bp_acc, bp_fi = 0.0, None, 0
+    for i in range(sim_steps):
+        c = bpd.simulate_snr(snr, Fbp, seed=5, first_frame=(i + 1) * Fbp + rank * (sim_steps + 1) * Fbp, batch_frames=Fbp)
+        st = bpd.last_call_stats()
+        bp_ms += st["device_ms"]
+        bp_fi += st["frame_iterations"]
+        bp_acc = c.as_array() if bp_acc is None else bp_acc + c.as_array()
+    bp_ms = max_over_ranks(bp_ms)
+    bp_bytes = float(bp_fi) * (4 * E + N) * 4  # per frame-iteration: every edge message read and written in both passes + the channel value
+    bp = {"value": round(sum_over_ranks(Fbp) * sim_steps * K / (bp_ms * 1e-3) / 1e9, 4), "unit": UNIT,
+          "ms_per_step": round(bp_ms / sim_steps, 3), "frames_per_step_per_gpu": Fbp, "steps": sim_steps,
+          "fer": float(bp_acc[1]) / float(bp_acc[0]), "mean_iterations": round(float(bp_acc[6]) / float(bp_acc[0]), 2),
+          "algorithmic_GBps_rank0": round(bp_bytes / (bp_ms * 1e-3) / 1e9, 1),
+          "frac_of_hbm_peak": round(bp_bytes / (bp_ms * 1e-3) / 1e9 / peak, 4),
+          "call": "lutldpc_bp_simulate_snr (Philox AWGN, to_qllr, bp_decode with per-frame early return and batch "
+                  "narrowing, error counting on the device); (4 E + N) * 4 algorithmic bytes per frame-iteration"}
+    bpd.close()
+
     line = {"metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u4 (8 codes per u32, SWAR)", "data": "synthetic",
@@ -372,7 +399,7 @@ def run_b200(args):
                      "mean_iterations": round(sum_iters / F, 2), "decode_failures": int((it_host < 0).sum()),
                      "frame_errors": int(wrong.sum()), "undetected_frame_errors": int((wrong & (it_host >= 0)).sum()),
                      "edge_updates_per_s": round(2.0 * E * sum_iters_all * args.steps / (ms * 1e-3), 1)},
-            "roofline": roofline, "sim": sim, "random_codeword": random_cw, "e2e_packed": e2e_packed, "clocks": clocks, "gpu_launches": int(launches),
+            "roofline": roofline, "sim": sim, "random_codeword": random_cw, "e2e_packed": e2e_packed, "bp": bp, "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": round(e2e_value, 4), "unit": UNIT, "h2d_bytes_per_step": int(2 * F * N) * world,
                     "d2h_bytes_per_step": int(F * N + 4 * F) * world, "steps": e2e_steps,
                     "call": "lutldpc_decode_quantized (pinned host u8 labels in, bits + iteration counts out; chunks pipelined over copy and decode streams)"}}

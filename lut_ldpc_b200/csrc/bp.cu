@@ -47,18 +47,21 @@ __device__ __forceinline__ int bp_to_qllr(double l, const Calc& c) {
 __device__ __forceinline__ int bp_clamp(int v, int qmax) { return max(-qmax, min(qmax, v)); }
 // qsum, llr.h:320-329
 __device__ __forceinline__ int bp_qsum(int a, int b, int qmax) { return bp_clamp(a + b, qmax); }
-// logexp, llr.h:282-298 (x >= 0)
-__device__ __forceinline__ int bp_logexp(int x, const int* tab, const Calc& c) {
-  const int ind = x >> c.d3;
-  return ind >= c.d2 ? 0 : tab[ind];
-}
-// Boxplus, llr.cpp:148-185.  term1 = sign(a) sign(b) min(|a|,|b|): the reference's nested selects give the same
-// value when a or b is 0 (then min is 0).
+// logexp, llr.h:282-298 (x >= 0): 0 beyond the table -- tab[d2] holds that 0, so the index is clamped, not tested
+__device__ __forceinline__ int bp_logexp(int x, const int* tab, const Calc& c) { return tab[min(x >> c.d3, c.d2)]; }
+// Boxplus, llr.cpp:148-185: term1 + logexp(|a+b|) - logexp(|a-b|), saturated, with term1 = sign(a) sign(b) min(|a|,|b|)
+// (the reference's nested selects give 0 when a or b is 0, like the product).  {|a+b|, |a-b|} = {|a|+|b|, ||a|-|b||},
+// in this order when the signs agree and swapped when they differ, so the value is sign(a) sign(b) * r with
+// r = min + logexp(|a|+|b|) - logexp(max-min); the saturation is symmetric, so it commutes with the sign.  For a or b
+// = 0 both forms give logexp(max) - logexp(max) = 0.  Fewer operations on the integer ALU pipe, which bounds the pass.
 __device__ __forceinline__ int bp_boxplus(int a, int b, const int* tab, const Calc& c) {
-  const int mn = min(abs(a), abs(b));
-  const int t1 = ((a ^ b) < 0) ? -mn : mn;
-  if (c.d2 == 0) return bp_clamp(t1, c.qmax);
-  return bp_clamp(t1 + bp_logexp(abs(a + b), tab, c) - bp_logexp(abs(a - b), tab, c), c.qmax);
+  const int aa = abs(a), bb = abs(b);
+  const int mn = min(aa, bb), mx = max(aa, bb);
+  int r = mn;
+  if (c.d2 != 0) r += bp_logexp(aa + bb, tab, c) - bp_logexp(mx - mn, tab, c);
+  r = bp_clamp(r, c.qmax);
+  const int sg = (a ^ b) >> 31;  // 0 or -1
+  return (r ^ sg) - sg;
 }
 
 __device__ __forceinline__ bool slot_done(const uint32_t* donew, size_t s) { return (donew[s >> 5] >> (s & 31)) & 1u; }
@@ -102,86 +105,99 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_init(const int32_t* __restric
 // general left/right recursion (:1529-1553); degree 6 (:1497-1521) pairs its inputs differently and is kept as is.
 // With suf[k] = m[k] [+] m[k+1] [+] ... [+] m[dc-1] folded from the right (the reference's mr[dc-1-k]) and the running
 // left fold l (its ml[k-1]): out[0] = suf[1], out[k] = l [+] suf[k+1], out[dc-1] = l.
-template <int MAXDC>
-__global__ void __launch_bounds__(kBpThreads) k_bp_cn(const int32_t* __restrict__ cn_off, const int32_t* __restrict__ cn_edge,
-                                                       int M, int cpb, size_t S, int32_t* __restrict__ msg,
-                                                       const uint32_t* __restrict__ donew, Calc c,
-                                                       const int32_t* __restrict__ table) {
+// Checks are grouped by degree on the host (list = the checks of one degree), so that the common degrees run fully
+// unrolled out of registers without a predicate per input.  Row e of the message array starts e * S4 bytes after the
+// slot's column base: one 32 x 32 -> 64 bit multiply-add per access.
+__device__ __forceinline__ int32_t* bp_row(int32_t* col, uint32_t e, uint32_t S4) {
+  return reinterpret_cast<int32_t*>(reinterpret_cast<char*>(col) + (unsigned long long)e * S4);
+}
+
+// cls_edge = the edge ids of the class's checks, DC per check, back to back.  A block takes CPB checks: their
+// CPB * DC edge ids are staged in shared memory with one coalesced load, then every thread has all CPB * DC message
+// loads of its slot in flight before the first Boxplus -- the pass is bound by memory latency otherwise.
+template <int DC, int CPB>
+__global__ void __launch_bounds__(kBpThreads) k_bp_cn_deg(const int32_t* __restrict__ cls_edge, int n_list, uint32_t S4,
+                                                           int32_t* __restrict__ msg, const uint32_t* __restrict__ donew, Calc c,
+                                                           const int32_t* __restrict__ table) {
   extern __shared__ int s_tab[];
-  for (int i = threadIdx.x; i < c.d2; i += kBpThreads) s_tab[i] = table[i];
+  __shared__ uint32_t s_idx[CPB * DC];
+  const int t0 = blockIdx.x * CPB;
+  for (int i = threadIdx.x; i < CPB * DC; i += kBpThreads)
+    s_idx[i] = t0 * DC + i < n_list * DC ? (uint32_t)cls_edge[(size_t)t0 * DC + i] : 0u;
+  for (int i = threadIdx.x; i <= c.d2; i += kBpThreads) s_tab[i] = i < c.d2 ? table[i] : 0;
   __syncthreads();
   const size_t s = (size_t)blockIdx.y * kBpThreads + threadIdx.x;
   if (slot_done(donew, s)) return;
-  const int j1 = min(M, (int)(blockIdx.x + 1) * cpb);
-  for (int j = blockIdx.x * cpb; j < j1; ++j) {
-    const int e0 = cn_off[j], dc = cn_off[j + 1] - e0;
-    const int32_t* idx = cn_edge + e0;
-    int m[MAXDC];
+  int32_t* col = msg + s;
+  int m[CPB][DC];
 #pragma unroll
-    for (int k = 0; k < MAXDC; ++k)
-      if (k < dc) m[k] = msg[(size_t)idx[k] * S + s];
-    if (dc == 6) {
-      const int m01 = bp_boxplus(m[0], m[1], s_tab, c), m23 = bp_boxplus(m[2], m[3], s_tab, c),
-                m45 = bp_boxplus(m[4], m[5], s_tab, c);
+  for (int q = 0; q < CPB; ++q)
+#pragma unroll
+    for (int k = 0; k < DC; ++k) m[q][k] = *bp_row(col, s_idx[q * DC + k], S4);  // tail checks read row 0: harmless
+#pragma unroll
+  for (int q = 0; q < CPB; ++q) {
+    if (t0 + q >= n_list) break;
+    const uint32_t* e = s_idx + q * DC;
+    if constexpr (DC == 6) {
+      const int m01 = bp_boxplus(m[q][0], m[q][1], s_tab, c), m23 = bp_boxplus(m[q][2], m[q][3], s_tab, c),
+                m45 = bp_boxplus(m[q][4], m[q][5], s_tab, c);
       const int m03 = bp_boxplus(m01, m23, s_tab, c), m25 = bp_boxplus(m23, m45, s_tab, c),
                 m0145 = bp_boxplus(m01, m45, s_tab, c);
-      msg[(size_t)idx[0] * S + s] = bp_boxplus(m[1], m25, s_tab, c);
-      msg[(size_t)idx[1] * S + s] = bp_boxplus(m[0], m25, s_tab, c);
-      msg[(size_t)idx[2] * S + s] = bp_boxplus(m0145, m[3], s_tab, c);
-      msg[(size_t)idx[3] * S + s] = bp_boxplus(m0145, m[2], s_tab, c);
-      msg[(size_t)idx[4] * S + s] = bp_boxplus(m03, m[5], s_tab, c);
-      msg[(size_t)idx[5] * S + s] = bp_boxplus(m03, m[4], s_tab, c);
-      continue;
-    }
-    int suf[MAXDC];
-    if (dc == MAXDC) suf[MAXDC - 1] = m[MAXDC - 1];
+      *bp_row(col, e[0], S4) = bp_boxplus(m[q][1], m25, s_tab, c);
+      *bp_row(col, e[1], S4) = bp_boxplus(m[q][0], m25, s_tab, c);
+      *bp_row(col, e[2], S4) = bp_boxplus(m0145, m[q][3], s_tab, c);
+      *bp_row(col, e[3], S4) = bp_boxplus(m0145, m[q][2], s_tab, c);
+      *bp_row(col, e[4], S4) = bp_boxplus(m03, m[q][5], s_tab, c);
+      *bp_row(col, e[5], S4) = bp_boxplus(m03, m[q][4], s_tab, c);
+    } else {
+      int suf[DC];
+      suf[DC - 1] = m[q][DC - 1];
 #pragma unroll
-    for (int k = MAXDC - 2; k >= 1; --k) {
-      if (k == dc - 1) suf[k] = m[k];
-      else if (k < dc - 1) suf[k] = bp_boxplus(suf[k + 1], m[k], s_tab, c);
-    }
-    msg[(size_t)idx[0] * S + s] = suf[1];
-    int l = m[0];
+      for (int k = DC - 2; k >= 1; --k) suf[k] = bp_boxplus(suf[k + 1], m[q][k], s_tab, c);
+      *bp_row(col, e[0], S4) = suf[1];
+      int l = m[q][0];
 #pragma unroll
-    for (int k = 1; k <= MAXDC - 2; ++k)
-      if (k <= dc - 2) {
-        msg[(size_t)idx[k] * S + s] = bp_boxplus(l, suf[k + 1], s_tab, c);
-        l = bp_boxplus(l, m[k], s_tab, c);
+      for (int k = 1; k <= DC - 2; ++k) {
+        *bp_row(col, e[k], S4) = bp_boxplus(l, suf[k + 1], s_tab, c);
+        l = bp_boxplus(l, m[q][k], s_tab, c);
       }
-    msg[(size_t)idx[dc - 1] * S + s] = l;
+      *bp_row(col, e[DC - 1], S4) = l;
+    }
   }
 }
 
 // the same for any degree up to the reference's max_cnd = 200: inputs and right folds in shared memory
-__global__ void __launch_bounds__(kBpThreads) k_bp_cn_big(const int32_t* __restrict__ cn_off, const int32_t* __restrict__ cn_edge,
-                                                           int M, int cpb, int maxdc, size_t S, int32_t* __restrict__ msg,
+__global__ void __launch_bounds__(kBpThreads) k_bp_cn_big(const int32_t* __restrict__ list, int n_list, int cpb,
+                                                           const int32_t* __restrict__ cn_off, const int32_t* __restrict__ cn_edge,
+                                                           int maxdc, uint32_t S4, int32_t* __restrict__ msg,
                                                            const uint32_t* __restrict__ donew, Calc c,
                                                            const int32_t* __restrict__ table) {
   extern __shared__ int s_all[];
   int* s_tab = s_all;
-  int* s_m = s_all + c.d2 + threadIdx.x;               // [k * blockDim.x]
+  int* s_m = s_all + c.d2 + 1 + threadIdx.x;  // [k * blockDim.x]
   int* s_suf = s_m + (size_t)maxdc * blockDim.x;
   const int T = blockDim.x;
-  for (int i = threadIdx.x; i < c.d2; i += T) s_tab[i] = table[i];
+  for (int i = threadIdx.x; i <= c.d2; i += T) s_tab[i] = i < c.d2 ? table[i] : 0;
   __syncthreads();
   const size_t s = (size_t)blockIdx.y * T + threadIdx.x;
   if (slot_done(donew, s)) return;
-  const int j1 = min(M, (int)(blockIdx.x + 1) * cpb);
-  for (int j = blockIdx.x * cpb; j < j1; ++j) {
-    const int e0 = cn_off[j], dc = cn_off[j + 1] - e0;
-    const int32_t* idx = cn_edge + e0;
-    for (int k = 0; k < dc; ++k) s_m[k * T] = msg[(size_t)idx[k] * S + s];
+  int32_t* col = msg + s;
+  const int t1 = min(n_list, (int)(blockIdx.x + 1) * cpb);
+  for (int t = blockIdx.x * cpb; t < t1; ++t) {
+    const int j = list[t], e0 = cn_off[j], dc = cn_off[j + 1] - e0;
+    const uint32_t* idx = reinterpret_cast<const uint32_t*>(cn_edge + e0);
+    for (int k = 0; k < dc; ++k) s_m[k * T] = *bp_row(col, idx[k], S4);
     if (dc == 6) {
       const int m0 = s_m[0], m1 = s_m[T], m2 = s_m[2 * T], m3 = s_m[3 * T], m4 = s_m[4 * T], m5 = s_m[5 * T];
       const int m01 = bp_boxplus(m0, m1, s_tab, c), m23 = bp_boxplus(m2, m3, s_tab, c), m45 = bp_boxplus(m4, m5, s_tab, c);
       const int m03 = bp_boxplus(m01, m23, s_tab, c), m25 = bp_boxplus(m23, m45, s_tab, c),
                 m0145 = bp_boxplus(m01, m45, s_tab, c);
-      msg[(size_t)idx[0] * S + s] = bp_boxplus(m1, m25, s_tab, c);
-      msg[(size_t)idx[1] * S + s] = bp_boxplus(m0, m25, s_tab, c);
-      msg[(size_t)idx[2] * S + s] = bp_boxplus(m0145, m3, s_tab, c);
-      msg[(size_t)idx[3] * S + s] = bp_boxplus(m0145, m2, s_tab, c);
-      msg[(size_t)idx[4] * S + s] = bp_boxplus(m03, m5, s_tab, c);
-      msg[(size_t)idx[5] * S + s] = bp_boxplus(m03, m4, s_tab, c);
+      *bp_row(col, idx[0], S4) = bp_boxplus(m1, m25, s_tab, c);
+      *bp_row(col, idx[1], S4) = bp_boxplus(m0, m25, s_tab, c);
+      *bp_row(col, idx[2], S4) = bp_boxplus(m0145, m3, s_tab, c);
+      *bp_row(col, idx[3], S4) = bp_boxplus(m0145, m2, s_tab, c);
+      *bp_row(col, idx[4], S4) = bp_boxplus(m03, m5, s_tab, c);
+      *bp_row(col, idx[5], S4) = bp_boxplus(m03, m4, s_tab, c);
       continue;
     }
     int r = s_m[(dc - 1) * T];
@@ -190,56 +206,117 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_cn_big(const int32_t* __restr
       r = bp_boxplus(r, s_m[k * T], s_tab, c);
       s_suf[k * T] = r;
     }
-    msg[(size_t)idx[0] * S + s] = s_suf[T];
+    *bp_row(col, idx[0], S4) = s_suf[T];
     int l = s_m[0];
     for (int k = 1; k <= dc - 2; ++k) {
-      msg[(size_t)idx[k] * S + s] = bp_boxplus(l, s_suf[(k + 1) * T], s_tab, c);
+      *bp_row(col, idx[k], S4) = bp_boxplus(l, s_suf[(k + 1) * T], s_tab, c);
       l = bp_boxplus(l, s_m[k * T], s_tab, c);
     }
-    msg[(size_t)idx[dc - 1] * S + s] = l;
+    *bp_row(col, idx[dc - 1], S4) = l;
   }
 }
 
 // ---- step 2, variable to check (ldpc.cpp:1558-1611), soft output and its sign.  Degree 3 (:1583-1595) is the same
 // arithmetic as the differential update (:1596-1609); degrees 1 and 2 are not and are kept as they are.
-__global__ void __launch_bounds__(kBpThreads) k_bp_vn(const int32_t* __restrict__ vn_off, int N, int vpb, size_t S,
-                                                       int32_t* __restrict__ msg, const int32_t* __restrict__ qin,
-                                                       const uint32_t* __restrict__ donew, uint32_t* __restrict__ hardw,
-                                                       int32_t* __restrict__ soft, int qmax) {
+// Variables are grouped by degree like the checks (list = the variables of one degree).  A block takes VPB of them and
+// has all their channel values, messages and old sign words requested before the first sum.
+template <int DV, int VPB>
+__global__ void __launch_bounds__(kBpThreads) k_bp_vn_deg(const int32_t* __restrict__ list, int n_list,
+                                                           const int32_t* __restrict__ vn_off, uint32_t S4,
+                                                           int32_t* __restrict__ msg, const int32_t* __restrict__ qin,
+                                                           const uint32_t* __restrict__ donew, uint32_t* __restrict__ hardw,
+                                                           int32_t* __restrict__ soft, int qmax) {
+  __shared__ int s_i[VPB], s_e0[VPB];
+  if (threadIdx.x < VPB) {
+    const int t = blockIdx.x * VPB + threadIdx.x;
+    const int i = t < n_list ? list[t] : -1;
+    s_i[threadIdx.x] = i;
+    s_e0[threadIdx.x] = i >= 0 ? vn_off[i] : 0;
+  }
+  __syncthreads();
   const size_t s = (size_t)blockIdx.y * kBpThreads + threadIdx.x;
   const uint32_t dmask = donew[s >> 5];
   const bool done = (dmask >> (s & 31)) & 1u;
   if (dmask == 0xFFFFFFFFu) return;  // the whole warp has returned
-  const int i1 = min(N, (int)(blockIdx.x + 1) * vpb);
-  for (int i = blockIdx.x * vpb; i < i1; ++i) {
+  const uint32_t S32 = S4 >> 7;
+  const bool lane0 = (threadIdx.x & 31) == 0;
+  int L[VPB], m[VPB][DV];
+  uint32_t old[VPB];
+#pragma unroll
+  for (int v = 0; v < VPB; ++v) {
+    const int i = s_i[v];
+    L[v] = 0;
+    old[v] = 0;
+#pragma unroll
+    for (int k = 0; k < DV; ++k) m[v][k] = 0;
+    if (i < 0) continue;
+    if (!done) {
+      L[v] = *bp_row(const_cast<int32_t*>(qin) + s, (uint32_t)i, S4);
+      const char* e = reinterpret_cast<const char*>(bp_row(msg + s, (uint32_t)s_e0[v], S4));
+#pragma unroll
+      for (int k = 0; k < DV; ++k) m[v][k] = *reinterpret_cast<const int32_t*>(e + (size_t)k * S4);
+    }
+    if (dmask && lane0) old[v] = hardw[(size_t)i * S32 + (s >> 5)];
+  }
+#pragma unroll
+  for (int v = 0; v < VPB; ++v) {
+    const int i = s_i[v];
+    if (i < 0) break;
     int out = 0;
     if (!done) {
-      const int e0 = vn_off[i], dv = vn_off[i + 1] - e0;
-      const int L = qin[(size_t)i * S + s];
-      int32_t* e = msg + (size_t)e0 * S + s;
-      if (dv == 1) {
-        const int m0 = e[0];
-        e[0] = L;
-        out = bp_qsum(L, m0, qmax);
-      } else if (dv == 2) {
-        const int m0 = e[0], m1 = e[S];
-        const int o1 = bp_qsum(L, m0, qmax);
-        e[0] = bp_qsum(L, m1, qmax);
-        e[S] = o1;
-        out = bp_qsum(o1, m1, qmax);
+      char* e = reinterpret_cast<char*>(bp_row(msg + s, (uint32_t)s_e0[v], S4));
+      auto at = [&](int k) -> int32_t& { return *reinterpret_cast<int32_t*>(e + (size_t)k * S4); };
+      if constexpr (DV == 1) {
+        at(0) = L[v];
+        out = bp_qsum(L[v], m[v][0], qmax);
+      } else if constexpr (DV == 2) {
+        const int o1 = bp_qsum(L[v], m[v][0], qmax);
+        at(0) = bp_qsum(L[v], m[v][1], qmax);
+        at(1) = o1;
+        out = bp_qsum(o1, m[v][1], qmax);
       } else {
-        int t = L;
-        for (int k = 0; k < dv; ++k) t = bp_qsum(t, e[(size_t)k * S], qmax);
+        int t = L[v];
+#pragma unroll
+        for (int k = 0; k < DV; ++k) t = bp_qsum(t, m[v][k], qmax);
         out = t;
-        for (int k = 0; k < dv; ++k) e[(size_t)k * S] = bp_qsum(t, -e[(size_t)k * S], qmax);
+#pragma unroll
+        for (int k = 0; k < DV; ++k) at(k) = bp_qsum(t, -m[v][k], qmax);
       }
-      if (soft) soft[(size_t)i * S + s] = out;
+      if (soft) *bp_row(soft + s, (uint32_t)i, S4) = out;
     }
     const uint32_t bal = __ballot_sync(0xFFFFFFFFu, !done && out < 0);
-    if ((threadIdx.x & 31) == 0) {
-      uint32_t* hw = hardw + (size_t)i * (S >> 5) + (s >> 5);
-      *hw = (*hw & dmask) | (bal & ~dmask);
-    }
+    if (lane0) hardw[(size_t)i * S32 + (s >> 5)] = (old[v] & dmask) | (bal & ~dmask);
+  }
+}
+
+// any degree: two passes over the variable's messages (the second one finds them in L1)
+__global__ void __launch_bounds__(kBpThreads) k_bp_vn_any(const int32_t* __restrict__ list, int n_list,
+                                                           const int32_t* __restrict__ vn_off, uint32_t S4,
+                                                           int32_t* __restrict__ msg, const int32_t* __restrict__ qin,
+                                                           const uint32_t* __restrict__ donew, uint32_t* __restrict__ hardw,
+                                                           int32_t* __restrict__ soft, int qmax) {
+  const size_t s = (size_t)blockIdx.y * kBpThreads + threadIdx.x;
+  const uint32_t dmask = donew[s >> 5];
+  const bool done = (dmask >> (s & 31)) & 1u;
+  if (dmask == 0xFFFFFFFFu) return;
+  const uint32_t S32 = S4 >> 7;
+  const int i = list[blockIdx.x], e0 = vn_off[i], dv = vn_off[i + 1] - e0;
+  int out = 0;
+  if (!done) {
+    char* e = reinterpret_cast<char*>(bp_row(msg + s, (uint32_t)e0, S4));
+    auto at = [&](int k) -> int32_t& { return *reinterpret_cast<int32_t*>(e + (size_t)k * S4); };
+    int t = *bp_row(const_cast<int32_t*>(qin) + s, (uint32_t)i, S4);
+#pragma unroll 4
+    for (int k = 0; k < dv; ++k) t = bp_qsum(t, at(k), qmax);
+    out = t;
+#pragma unroll 4
+    for (int k = 0; k < dv; ++k) at(k) = bp_qsum(t, -at(k), qmax);
+    if (soft) *bp_row(soft + s, (uint32_t)i, S4) = out;
+  }
+  const uint32_t bal = __ballot_sync(0xFFFFFFFFu, !done && out < 0);
+  if ((threadIdx.x & 31) == 0) {
+    uint32_t* hw = hardw + (size_t)i * S32 + (s >> 5);
+    *hw = dmask ? ((*hw & dmask) | (bal & ~dmask)) : bal;
   }
 }
 
@@ -429,7 +506,11 @@ struct lutldpc_bp {
   Calc calc{};
   bool repack_on = true;
   std::vector<int32_t> table;
-  DevBuf<int32_t> d_vn_off, d_cn_off, d_cn_edge, d_cn_var, d_table;
+  DevBuf<int32_t> d_vn_off, d_cn_off, d_cn_edge, d_cn_var, d_table, d_cn_list, d_cls_edge;
+  struct CnClass { int dc, n, off, edge_off; };
+  DevBuf<int32_t> d_vn_list;
+  std::vector<CnClass> vn_classes;  // variables grouped by degree: d_vn_list[off .. off + n) (dc = the degree)
+  std::vector<CnClass> cn_classes;  // checks grouped by degree: d_cn_list[off .. off + n)
   uint32_t* d_P = nullptr;  // generator (gf2.cu)
   int P_wp = 0, gen_rows = 0, gen_cols = 0;
   // batch state
@@ -487,25 +568,60 @@ struct BatchIO {       // what a batch hands back
   const uint32_t* d_sent = nullptr;  // sent bits as slot rows (NULL: all-zero codeword)
 };
 
+template <int DC>
+void launch_cn_deg(lutldpc_bp* h, const lutldpc_bp::CnClass& cl, size_t S, int32_t* msg) {
+  constexpr int CPB = DC <= 9 ? 4 : DC <= 16 ? 2 : 1;  // CPB * DC message registers per thread
+  dim3 grid((cl.n + CPB - 1) / CPB, (unsigned)(S / kBpThreads));
+  k_bp_cn_deg<DC, CPB><<<grid, kBpThreads, ((size_t)h->calc.d2 + 1) * 4, h->stream>>>(h->d_cls_edge.p + cl.edge_off, cl.n, (uint32_t)(S * 4), msg,
+                                                                                   h->donew.p, h->calc, h->d_table.p);
+}
+
 int launch_cn(lutldpc_bp* h, size_t S, int32_t* msg) {
-  const int M = h->g.nchk, cpb = 4;
-  dim3 grid((M + cpb - 1) / cpb, (unsigned)(S / kBpThreads));
-  const size_t tab = (size_t)h->calc.d2 * 4;
-  cudaStream_t st = h->stream;
-  if (h->max_dc <= 8)
-    k_bp_cn<8><<<grid, kBpThreads, tab, st>>>(h->d_cn_off.p, h->d_cn_edge.p, M, cpb, S, msg, h->donew.p, h->calc, h->d_table.p);
-  else if (h->max_dc <= 16)
-    k_bp_cn<16><<<grid, kBpThreads, tab, st>>>(h->d_cn_off.p, h->d_cn_edge.p, M, cpb, S, msg, h->donew.p, h->calc, h->d_table.p);
-  else if (h->max_dc <= kCnRegsMax)
-    k_bp_cn<kCnRegsMax><<<grid, kBpThreads, tab, st>>>(h->d_cn_off.p, h->d_cn_edge.p, M, cpb, S, msg, h->donew.p, h->calc, h->d_table.p);
-  else {
-    const int T = 64;  // 2 * 200 * 64 * 4 = 100 KB at the reference's max_cnd
-    const size_t smem = tab + (size_t)2 * h->max_dc * T * 4;
-    dim3 g2((M + cpb - 1) / cpb, (unsigned)(S / T));
-    k_bp_cn_big<<<g2, T, smem, st>>>(h->d_cn_off.p, h->d_cn_edge.p, M, cpb, h->max_dc, S, msg, h->donew.p, h->calc, h->d_table.p);
+  for (const lutldpc_bp::CnClass& cl : h->cn_classes) {
+    switch (cl.dc) {
+#define BP_CN_CASE(D) case D: launch_cn_deg<D>(h, cl, S, msg); break;
+      BP_CN_CASE(2) BP_CN_CASE(3) BP_CN_CASE(4) BP_CN_CASE(5) BP_CN_CASE(6) BP_CN_CASE(7) BP_CN_CASE(8) BP_CN_CASE(9)
+      BP_CN_CASE(10) BP_CN_CASE(11) BP_CN_CASE(12) BP_CN_CASE(13) BP_CN_CASE(14) BP_CN_CASE(15) BP_CN_CASE(16)
+      BP_CN_CASE(17) BP_CN_CASE(18) BP_CN_CASE(19) BP_CN_CASE(20) BP_CN_CASE(21) BP_CN_CASE(22) BP_CN_CASE(23) BP_CN_CASE(24)
+      BP_CN_CASE(25) BP_CN_CASE(26) BP_CN_CASE(27) BP_CN_CASE(28) BP_CN_CASE(29) BP_CN_CASE(30) BP_CN_CASE(31) BP_CN_CASE(32)
+#undef BP_CN_CASE
+      default: {
+        const int T = 64, cpb = 4;  // 2 * 200 * 64 * 4 = 100 KB at the reference's max_cnd
+        const size_t smem = ((size_t)h->calc.d2 + 1) * 4 + (size_t)2 * h->max_dc * T * 4;
+        dim3 g2((cl.n + cpb - 1) / cpb, (unsigned)(S / T));
+        k_bp_cn_big<<<g2, T, smem, h->stream>>>(h->d_cn_list.p + cl.off, cl.n, cpb, h->d_cn_off.p, h->d_cn_edge.p, h->max_dc,
+                                                 (uint32_t)(S * 4), msg, h->donew.p, h->calc, h->d_table.p);
+      }
+    }
+    CKBL("bp check pass");
+    ++h->launches;
   }
-  CKBL("bp check pass");
-  ++h->launches;
+  return LUTLDPC_OK;
+}
+
+template <int DV>
+void launch_vn_deg(lutldpc_bp* h, const lutldpc_bp::CnClass& cl, size_t S, int32_t* msg, const int32_t* qin, int32_t* soft) {
+  constexpr int VPB = DV <= 2 ? 8 : DV <= 4 ? 4 : DV <= 8 ? 2 : 1;  // VPB * DV message registers per thread
+  dim3 grid((cl.n + VPB - 1) / VPB, (unsigned)(S / kBpThreads));
+  k_bp_vn_deg<DV, VPB><<<grid, kBpThreads, 0, h->stream>>>(h->d_vn_list.p + cl.off, cl.n, h->d_vn_off.p, (uint32_t)(S * 4), msg, qin,
+                                                          h->donew.p, h->hardw.p, soft, h->calc.qmax);
+}
+
+int launch_vn(lutldpc_bp* h, size_t S, int32_t* msg, const int32_t* qin, int32_t* soft) {
+  for (const lutldpc_bp::CnClass& cl : h->vn_classes) {
+    switch (cl.dc) {
+#define BP_VN_CASE(D) case D: launch_vn_deg<D>(h, cl, S, msg, qin, soft); break;
+      BP_VN_CASE(1) BP_VN_CASE(2) BP_VN_CASE(3) BP_VN_CASE(4) BP_VN_CASE(5) BP_VN_CASE(6) BP_VN_CASE(7) BP_VN_CASE(8)
+      BP_VN_CASE(9) BP_VN_CASE(10) BP_VN_CASE(11) BP_VN_CASE(12) BP_VN_CASE(13) BP_VN_CASE(14) BP_VN_CASE(15) BP_VN_CASE(16)
+#undef BP_VN_CASE
+      default:
+        k_bp_vn_any<<<dim3(cl.n, (unsigned)(S / kBpThreads)), kBpThreads, 0, h->stream>>>(h->d_vn_list.p + cl.off, cl.n, h->d_vn_off.p,
+                                                                                        (uint32_t)(S * 4), msg, qin, h->donew.p,
+                                                                                        h->hardw.p, soft, h->calc.qmax);
+    }
+    CKBL("bp variable pass");
+    ++h->launches;
+  }
   return LUTLDPC_OK;
 }
 
@@ -596,11 +712,7 @@ int run_batch(lutldpc_bp* h, int F, size_t S, const BatchIO& io) {
   while (active > 0 && iter < n_iter) {
     ++iter;
     if ((rc = launch_cn(h, S, msg))) return rc;
-    const int vpb = 4;
-    k_bp_vn<<<dim3((N + vpb - 1) / vpb, (unsigned)(S / kBpThreads)), kBpThreads, 0, st>>>(h->d_vn_off.p, N, vpb, S, msg, qin, h->donew.p,
-                                                                                         h->hardw.p, soft, h->calc.qmax);
-    CKBL("bp variable pass");
-    ++h->launches;
+    if ((rc = launch_vn(h, S, msg, qin, soft))) return rc;
     if (!h->par.psc) continue;
     if ((rc = syndrome_and_mark(iter))) return rc;
     active = count_active();
@@ -794,6 +906,24 @@ int lutldpc_bp_create(const lutldpc_graph* gr, const lutldpc_bp_params* p, int w
     h->max_dc = std::max(h->max_dc, (int)g.dc[j]);
   }
   for (int e = 0; e < g.num_edges; ++e) cn_var[e] = edge_var[g.cn_msg_idx[e]];
+  std::vector<int32_t> cn_list, cls_edge;  // checks by degree, ascending index within a degree; their edge ids
+  for (int d = 2; d <= h->max_dc; ++d) {
+    lutldpc_bp::CnClass cl{d, 0, (int)cn_list.size(), (int)cls_edge.size()};
+    for (int j = 0; j < g.nchk; ++j)
+      if (g.dc[j] == d) {
+        cn_list.push_back(j);
+        ++cl.n;
+        cls_edge.insert(cls_edge.end(), g.cn_msg_idx.begin() + cn_off[j], g.cn_msg_idx.begin() + cn_off[j + 1]);
+      }
+    if (cl.n) h->cn_classes.push_back(cl);
+  }
+  std::vector<int32_t> vn_list;
+  for (int d = 1; d <= h->max_dv; ++d) {
+    lutldpc_bp::CnClass cl{d, 0, (int)vn_list.size(), 0};
+    for (int i = 0; i < g.nvar; ++i)
+      if (g.dv[i] == d) { vn_list.push_back(i); ++cl.n; }
+    if (cl.n) h->vn_classes.push_back(cl);
+  }
   // LLR_calc_unit (llr.cpp:66-92)
   Calc& c = h->calc;
   c.d1 = p->qllr_scale_res; c.d2 = p->qllr_table_size; c.d3 = p->qllr_spacing_res;
@@ -812,8 +942,12 @@ int lutldpc_bp_create(const lutldpc_graph* gr, const lutldpc_bp_params* p, int w
   if (e == cudaSuccess) e = h->d_cn_edge.upload(g.cn_msg_idx);
   if (e == cudaSuccess) e = h->d_cn_var.upload(cn_var);
   if (e == cudaSuccess) e = h->d_table.upload(h->table);
+  if (e == cudaSuccess) e = h->d_cn_list.upload(cn_list);
+  if (e == cudaSuccess) e = h->d_cls_edge.upload(cls_edge);
+  if (e == cudaSuccess) e = h->d_vn_list.upload(vn_list);
   if (e == cudaSuccess && h->max_dc > kCnRegsMax)
-    e = cudaFuncSetAttribute(k_bp_cn_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)c.d2 * 4 + (size_t)2 * h->max_dc * 64 * 4));
+    e = cudaFuncSetAttribute(k_bp_cn_big, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(((size_t)c.d2 + 1) * 4 + (size_t)2 * h->max_dc * 64 * 4));
   if (e != cudaSuccess) {
     g_bp_create_error = std::string("device set-up: ") + cudaGetErrorString(e);
     cudaGetLastError();

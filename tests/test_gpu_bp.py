@@ -57,13 +57,14 @@ def _noisy_llr(g_nvar, n, snr_db, rate, seed):
     ("c2_default", 2.2, dict(qllr_table_size=0)),
     ("c1b_default", 1.8, {}),
     ("synth_mixed", 2.5, {}),
-    ("synth_wide_dc48", 4.2, dict(qllr_total_res=12)),
+    ("synth_wide_dc48", 5.0, dict(qllr_scale_res=4, qllr_spacing_res=2, qllr_total_res=12)),
 ])
 def test_bp_batch_vs_oracle_with_and_without_repacking(capi, name, snr, kw):
     """700 frames that return between iteration 0 and never: every frame equals the oracle's, whether the batch is
     narrowed while it runs or not (soft output: fixed slots; bits: repacked batches)"""
     g = _bpgolden.graph(name)
-    par = pyoracle.BpParams(max_iter=25, d2=kw.get("qllr_table_size", 300), d4=kw.get("qllr_total_res", 28))
+    par = pyoracle.BpParams(max_iter=25, d1=kw.get("qllr_scale_res", 12), d2=kw.get("qllr_table_size", 300),
+                            d3=kw.get("qllr_spacing_res", 7), d4=kw.get("qllr_total_res", 28))
     dec = _dec(capi, g, par)
     llr = _noisy_llr(g["nvar"], 700, snr, dec.rate, seed=11)
     llr[5] = np.abs(llr[5])  # a frame whose initial syndrome check passes
@@ -169,3 +170,38 @@ def test_bp_generator_and_random_codewords(capi):
     r = dec.simulate_snr(1.8, 20000, seed=2, zero_codeword=False)
     assert _agree(z.frame_errors, z.frames, r.frame_errors, r.frames)
     assert abs(z.uncoded_bit_errors - r.uncoded_bit_errors) < 6 * math.sqrt(z.uncoded_bit_errors)
+
+
+def test_ber_sim_with_a_bp_section(capi, tmp_path):
+    """a params file with a [BP] section (and no [LUT]) through both harnesses -- the C++ ber_sim binary and
+    ber_sim.py -- gives the reference's FER at its own points; random codewords (generator built inside) included"""
+    import subprocess
+    from lut_ldpc_b200 import ber_sim as bs
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    (tmp_path / "codes").mkdir()
+    _alist.write_alist("c2_irr_n500", str(tmp_path / "codes" / "irr500.alist"))
+    ini = tmp_path / "bp.ini"
+    ini.write_text("[Sim]\nSNRdB = 1:1:2\nNframes = 20000\nNfers = 1000000\nfer_min = 0\nber_min = 0\n"
+                   "[LDPC]\nparity_filename = irr500\nzero_codeword = false\n[BP]\nmax_iter = 30\n")
+    ref = BER["c2_irr_n500"]
+    # Python harness
+    p = bs.SimParams(str(ini))
+    sim = bs.make_sim(p, rand_seed=3, chunk_frames=8192)
+    assert type(sim) is bs.LDPC_BER_Sim
+    res = sim.load(str(tmp_path)).run(verbose=False)
+    for k, s in enumerate(("1.00", "2.00")):
+        assert res["sim_Nframes"][k] == 20000
+        assert _agree(res["sim_frame_errors"][k], 20000, ref[s]["frame_errors"], ref[s]["frames"]), (s, res)
+    # C++ harness
+    exe = os.path.join(root, "lut_ldpc_b200", "ber_sim")
+    if not os.path.exists(exe):
+        pytest.skip("ber_sim binary not built")
+    out = subprocess.run([exe, "-p", str(ini), "-b", str(tmp_path), "-s", "1"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, (out.stdout[-1000:], out.stderr[-1000:])
+    lines = [l for l in out.stdout.splitlines() if l.startswith("SNR = ")]
+    assert len(lines) == 2
+    for line, s in zip(lines, ("1.00", "2.00")):
+        frames = int(line.split("Simulated ")[1].split(" frames")[0])
+        fer = float(line.split("FER: ")[1])
+        assert frames == 20000 and _agree(round(fer * frames), frames, ref[s]["frame_errors"], ref[s]["frames"]), (s, line)
+    assert any(d.startswith("RES_N500_R0.5_maxIter30_zcw0_frames20000") for d in os.listdir(tmp_path / "results"))
