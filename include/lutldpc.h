@@ -87,6 +87,13 @@ const char* lutldpc_last_error(const lutldpc_decoder* h);
 int lutldpc_create(const lutldpc_desc* desc, lutldpc_decoder** out);
 int lutldpc_create_from_bundle(const char* bundle_path, lutldpc_decoder** out);
 void lutldpc_destroy(lutldpc_decoder* h);
+/* LDPC_Code_LUT::save_code (src/LDPC_Code_LUT.cpp:643-697): the decoder as the reference's own codec file (IT++ it_file,
+ * same variables in the same order), readable by the reference's load_code / Sim.codec_filename, lut_ldpc_vhdl and
+ * scripts/.  The generator is not stored (G_defined = false): a file to which LDPC_Generator_Systematic::save has
+ * appended carries IT++'s "Fileversion" 3 in place of the codec's 1 and the reference's load_code refuses it (:578-579).
+ * lutldpc_convert_codec: bundle or codec file in, codec file out; pure host code (no device needed). */
+int lutldpc_save_code(const lutldpc_decoder* h, const char* path);
+int lutldpc_convert_codec(const char* in_path, const char* out_it_path);
 int lutldpc_get_info(const lutldpc_decoder* h, lutldpc_info* info);
 
 /* LDPC_Code_LUT::set_exit_conditions(max_iters, psc, pisc), src/LDPC_Code_LUT.cpp:176-185.

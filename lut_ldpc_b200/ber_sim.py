@@ -64,6 +64,7 @@ class SimParams:
         self.results_dir = g("Sim", "results_dir", "results")
         self.custom_name = g("Sim", "custom_name", "")
         self.codec_filename = g("Sim", "codec_filename", "")
+        self.save_codec = int(float(g("Sim", "save_codec", 0)))
         self.zero_codeword = _flag(g("LDPC", "zero_codeword", "true"))
         self.parity_check_iter = _flag(g("LDPC", "parity_check_iter", "true"))
         self.max_iter = int(float(g("LUT", "max_iter", 30)))
@@ -159,10 +160,21 @@ class LDPC_BER_Sim_LUT:
                                            min_lut=p.min_lut)
             if not p.zero_codeword:
                 self.dec = self.dec.systematic()[0]
+            if self.rand_seed == p.save_codec and self.rank == 0:  # src/LDPC_BER_Sim.cpp:511-520
+                d = os.path.join(basedir, p.results_dir, self.gen_filename())
+                os.makedirs(d, exist_ok=True)
+                self.dec.save_code(os.path.join(d, "lut_codec.it"))
         self.dec.set_exit_conditions(self.p.max_iter, self.p.parity_check_iter, self.p.parity_check_iter)  # :500
         self.dec.set_initial_message_mode(INIT_QCHA if self.p.initial_message_mode == "from_quantized_channel_llrs"
                                           else INIT_CONT)
         return self
+
+    def gen_filename(self):
+        """LDPC_BER_Sim_LUT::gen_filename, src/LDPC_BER_Sim.cpp:553-568 (the rate as an ostream prints a double)"""
+        p = self.p
+        return "%s_N%d_R%s_maxIter%d_zcw%d_frames%d%s%s" % (p.results_prefix, self.dec.nvar, "%g" % self.dec.rate, p.max_iter,
+                                                           int(p.zero_codeword), p.Nframes, "_minLUT" if p.min_lut else "_LUT",
+                                                           p.custom_name)
 
     def _simulate(self, snr, n, first):
         if self._sim is not None:

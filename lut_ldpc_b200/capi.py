@@ -207,6 +207,8 @@ def load_library():
     L.lutldpc_create_systematic.argtypes = [vp, C.POINTER(vp), vp]
     L.lutldpc_decode_packed_device.argtypes = [vp, i32, vp, vp, vp]
     L.lutldpc_get_profile.argtypes = [vp, vp, vp, vp, vp]
+    L.lutldpc_save_code.argtypes = [vp, C.c_char_p]
+    L.lutldpc_convert_codec.argtypes = [C.c_char_p, C.c_char_p]
     L.lutldpc_bp_create.argtypes = [C.POINTER(_Graph), C.POINTER(_BpParams), i32, C.POINTER(vp), vp]
     L.lutldpc_bp_destroy.argtypes = [vp]
     L.lutldpc_bp_destroy.restype = None
@@ -297,6 +299,10 @@ class Decoder:
             raise LutLdpcError(rc, (self._L.lutldpc_last_error(self._h) or b"").decode())
 
     # ---- configuration (LDPC_Code_LUT::set_exit_conditions / set_initial_message_mode)
+    def save_code(self, path):
+        """LDPC_Code_LUT::save_code: the decoder as the reference's codec file (lut_codec.it)."""
+        self._ck(self._L.lutldpc_save_code(self._h, os.fsencode(path)))
+
     def set_exit_conditions(self, max_iters, psc=True, pisc=False):
         self._ck(self._L.lutldpc_set_exit_conditions(self._h, int(max_iters), int(psc), int(pisc)))
 

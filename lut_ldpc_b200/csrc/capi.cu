@@ -87,6 +87,8 @@ int lutldpc_create(const lutldpc_desc* d, lutldpc_decoder** out) {
     m.qb_Cha.assign(d->qb_Cha, d->qb_Cha + d->Nq_Cha - 1);
     if (d->n_qb_Msg) m.qb_Msg.assign(d->qb_Msg, d->qb_Msg + d->n_qb_Msg);
     if (!parse_tree_array(d->var_tree_string, d->var_tree_len, m.var_trees, err)) err = "var trees: " + err;
+    m.var_tree_text.assign(d->var_tree_string, d->var_tree_len);
+    if (d->chk_tree_string && d->chk_tree_len) m.chk_tree_text.assign(d->chk_tree_string, d->chk_tree_len);
   }
   if (err.empty() && d->chk_tree_string && d->chk_tree_len) {
     std::string e2;
@@ -215,6 +217,25 @@ int lutldpc_create_systematic(const lutldpc_decoder* src, lutldpc_decoder** out,
   if (rc != LUTLDPC_OK) return rc;
   (*out)->psc = src->psc; (*out)->pisc = src->pisc; (*out)->init_mode = src->init_mode;
   if (col_perm) memcpy(col_perm, r.col_perm.data(), sizeof(int32_t) * sm.nvar);
+  return LUTLDPC_OK;
+}
+
+int lutldpc_save_code(const lutldpc_decoder* h, const char* path) {
+  if (!h || !path) return LUTLDPC_ERR_ARG;
+  std::string err;
+  if (!save_it_codec_file(path, h->m, err)) {
+    const_cast<lutldpc_decoder*>(h)->err = err;
+    return LUTLDPC_ERR_STATE;
+  }
+  return LUTLDPC_OK;
+}
+
+int lutldpc_convert_codec(const char* in_path, const char* out_it_path) {
+  if (!in_path || !out_it_path) { g_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
+  DecoderModel m;
+  std::string err;
+  if (!load_decoder_file(in_path, m, err)) { g_create_error = err; return LUTLDPC_ERR_MODEL; }
+  if (!save_it_codec_file(out_it_path, m, err)) { g_create_error = err; return LUTLDPC_ERR_STATE; }
   return LUTLDPC_OK;
 }
 

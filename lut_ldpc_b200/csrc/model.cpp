@@ -115,8 +115,10 @@ bool load_bundle_file(const char* path, DecoderModel& m, std::string& err) {
     if (k == 0) {
       if (!parsed) { fclose(f); err = "bundle: var trees: " + perr; return false; }
       m.var_trees = std::move(ta);
-    } else if (parsed) {
-      m.chk_trees = std::move(ta);
+      m.var_tree_text.assign(txt.data(), (size_t)len);
+    } else {
+      if (parsed) m.chk_trees = std::move(ta);
+      m.chk_tree_text.assign(txt.data(), (size_t)len);
     }
   }
   if (r.ok && has_gen) {
@@ -252,6 +254,8 @@ bool load_it_codec_file(const char* path, DecoderModel& m, std::string& err) {
   }
   std::string perr;
   if (!parse_tree_array(vt.data(), vt.size(), m.var_trees, perr)) { err = "codec file: var trees: " + perr; return false; }
+  m.var_tree_text.assign(vt.begin(), vt.end());
+  m.chk_tree_text.assign(ct.begin(), ct.end());
   if (!ct.empty()) {
     TreeArray ta;
     if (parse_tree_array(ct.data(), ct.size(), ta, perr)) m.chk_trees = std::move(ta);
@@ -271,6 +275,70 @@ bool load_it_codec_file(const char* path, DecoderModel& m, std::string& err) {
     }
   }
   return finalize_model(m, err);
+}
+
+bool save_it_codec_file(const char* path, const DecoderModel& m, std::string& err) {
+  if (m.var_tree_text.empty()) { err = "save_code: the decoder holds no tree text"; return false; }
+  FILE* fp = fopen(path, "wb");
+  if (!fp) { err = std::string("save_code: cannot open ") + path; return false; }
+  bool ok = fwrite("IT++\x03", 1, 5, fp) == 5;
+  auto block = [&](const char* name, const char* type, const std::string& data) {
+    const uint64_t hdr = 24 + strlen(name) + 1 + strlen(type) + 1 + 1, db = data.size(), blk = hdr + db;
+    ok = ok && fwrite(&hdr, 8, 1, fp) == 1 && fwrite(&db, 8, 1, fp) == 1 && fwrite(&blk, 8, 1, fp) == 1;
+    ok = ok && fwrite(name, 1, strlen(name) + 1, fp) == strlen(name) + 1 && fwrite(type, 1, strlen(type) + 1, fp) == strlen(type) + 1;
+    ok = ok && fputc(0, fp) == 0;  // empty description
+    ok = ok && (data.empty() || fwrite(data.data(), 1, data.size(), fp) == data.size());
+  };
+  auto i32 = [&](const char* name, int32_t v) { block(name, "int32", std::string(reinterpret_cast<const char*>(&v), 4)); };
+  auto flag = [&](const char* name, bool v) { block(name, "bool", std::string(1, v ? '\1' : '\0')); };
+  auto counted = [](uint64_t n) { return std::string(reinterpret_cast<const char*>(&n), 8); };
+  auto ivec = [&](const char* name, const std::vector<int32_t>& v) {
+    std::string d = counted(v.size());
+    d.append(reinterpret_cast<const char*>(v.data()), 4 * v.size());
+    block(name, "ivec", d);
+  };
+  auto dvec = [&](const char* name, const std::vector<double>& v) {
+    std::string d = counted(v.size());
+    d.append(reinterpret_cast<const char*>(v.data()), 8 * v.size());
+    block(name, "dvec", d);
+  };
+  i32("Fileversion", 1);  // LUT_LDPC_binary_file_version, src/LDPC_Code_LUT.cpp:35
+  flag("H_defined", true);
+  flag("G_defined", false);
+  flag("LUTs_defined", true);
+  i32("nvar", m.nvar);
+  i32("nchk", m.nchk);
+  i32("nchk_lin_indep", m.nchk_lin_indep);
+  ivec("dv_vec", m.dv);
+  ivec("dc_vec", m.dc);
+  {  // chk_equ_idx: Array<ivec>, the sorted variable indices of every check (:531-535)
+    std::string d = counted((uint64_t)m.nchk);
+    for (int c = 0; c < m.nchk; ++c) {
+      const int a = m.cn_start[c], b = m.cn_start[c + 1];
+      d += counted((uint64_t)(b - a));
+      d.append(reinterpret_cast<const char*>(m.chk_equ_idx.data() + a), 4 * (size_t)(b - a));
+    }
+    block("chk_equ_idx", "ivecArray", d);
+  }
+  ivec("cn_msg_idx", m.cn_msg_idx);
+  i32("Nq_Cha", m.Nq_Cha);
+  ivec("Nq_Msg", m.Nq_Msg);
+  ivec("Nq_Cha_2_Nq_Msg_map", m.cha2msg);
+  dvec("qb_Cha", m.qb_Cha);
+  dvec("qb_Msg", m.qb_Msg);
+  {
+    std::string d = counted(m.reuse.size());
+    for (int32_t r : m.reuse) d.push_back(r ? '\1' : '\0');
+    block("reuse_vec", "bvec", d);
+  }
+  flag("minLUT", m.minLUT);
+  i32("output_verbosity", 0);
+  i32("max_iters", m.max_iters);
+  block("var_tree_string", "string", counted(m.var_tree_text.size()) + m.var_tree_text);
+  block("chk_tree_string", "string", counted(m.chk_tree_text.size()) + m.chk_tree_text);
+  ok = (fclose(fp) == 0) && ok;
+  if (!ok) err = std::string("save_code: write error on ") + path;
+  return ok;
 }
 
 // bundle ("LUTLDPC1", oracle/ref_driver.cpp) or the reference's codec file ("IT++"), by magic

@@ -38,6 +38,7 @@ struct DecoderModel {
   std::vector<int32_t> dv, dc, cn_msg_idx, Nq_Msg, reuse, cha2msg;
   std::vector<double> qb_Cha, qb_Msg;
   TreeArray var_trees, chk_trees;
+  std::string var_tree_text, chk_tree_text;  // the reference's text serialisation as it came in (written back by save)
   int gen_rows = 0, gen_cols = 0;
   std::vector<uint8_t> gen;  // dense parity part P, codeword = [u, P*u]
   // derived (set_trees / decoder_parameterization)
@@ -53,6 +54,10 @@ bool parse_tree_array(const char* txt, size_t len, TreeArray& out, std::string& 
 bool load_bundle_file(const char* path, DecoderModel& m, std::string& err);
 // the reference's codec file written by LDPC_Code_LUT::save_code (IT++ it_file, src/LDPC_Code_LUT.cpp:643-697)
 bool load_it_codec_file(const char* path, DecoderModel& m, std::string& err);
+// LDPC_Code_LUT::save_code (src/LDPC_Code_LUT.cpp:643-697): the same variables in the same order, as an IT++ it_file the
+// reference's load_code (and lut_ldpc_vhdl, scripts/) reads.  The generator is not written: a file to which
+// LDPC_Generator_Systematic::save has appended (it replaces "Fileversion" by IT++'s own, 3) is refused by load_code (:578-579).
+bool save_it_codec_file(const char* path, const DecoderModel& m, std::string& err);
 // either of the two, told apart by the file magic
 bool load_decoder_file(const char* path, DecoderModel& m, std::string& err);
 // fills the derived members and validates; false + err on unsupported/inconsistent input

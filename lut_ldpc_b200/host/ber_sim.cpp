@@ -306,6 +306,12 @@ int main(int argc, char** argv) {
          << "_zcw" << (int)zero_cw << "_frames" << Nframes;
     if (use_lut) name << (C[0]->is_min_lut() ? "_minLUT" : "_LUT");
     name << custom;
+    // a designed decoder is saved when the seed equals Sim.save_codec (src/LDPC_BER_Sim.cpp:59,511-520)
+    if (use_lut && codec.empty() && (int64_t)seed == (int64_t)ini.num("Sim.save_codec", 0)) {
+      mkdir(path(results_dir).c_str(), 0777);
+      mkdir((path(results_dir) + "/" + name.str()).c_str(), 0777);
+      C[0]->save_code(path(results_dir) + "/" + name.str() + "/lut_codec.it");
+    }
 
     // ---- run(), src/LDPC_BER_Sim.cpp:121-155
     auto t0 = std::chrono::steady_clock::now();

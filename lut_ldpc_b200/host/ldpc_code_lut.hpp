@@ -69,6 +69,9 @@ class LDPC_Code_LUT : public Channel_Code {
   }
   void set_initial_message_mode(initial_message_mode_t m) { ck(lutldpc_set_initial_message_mode(h_, (int)m), "set_initial_message_mode"); }
 
+  // src/LDPC_Code_LUT.cpp:643-697: the reference's own codec file (without the generator, see include/lutldpc.h)
+  void save_code(const std::string& filename) const { ck(lutldpc_save_code(h_, filename.c_str()), "save_code"); }
+
   // ---- Channel_Code
   void encode(const bvec& input, bvec& output) override {  // src/LDPC_Code_LUT.cpp:187-197
     if ((int)input.size() != info_.ninfo) throw std::runtime_error("LDPC_Code_LUT::encode(): input length must equal ninfo");

@@ -280,3 +280,35 @@ def test_stimuli_pairs_of_the_fused_step(L, tmp_path):
     assert set(bits) <= {"0", "1"}
     o1, _ = dec.decode_quantized(np.array([[int(x, 16) for x in labels]], np.uint8), np.array([[int(x, 16) for x in labels]], np.uint8))
     assert [str(b) for b in o1[0]] == bits
+
+
+def test_designed_decoder_is_saved_as_the_reference_codec_file(L, tmp_path):
+    """Sim.save_codec (src/LDPC_BER_Sim.cpp:59,511-520): the harness that designs its decoder from an alist leaves
+    results/<name>/lut_codec.it when the seed matches; the file is the reference's format (a handle created from it
+    decodes the reference's fixtures bit-exactly, and it equals the conversion of the golden bundle)."""
+    import pyoracle
+    from _alist import write_alist
+    from lut_ldpc_b200 import ber_sim as bs
+    (tmp_path / "codes").mkdir()
+    write_alist("c1b_reg36_n1000", str(tmp_path / "codes" / "reg36.alist"))
+    ini = tmp_path / "p.ini"
+    ini.write_text("[Sim]\nSNRdB = 3\nNframes = 2048\nsave_codec = 7\n[LDPC]\nparity_filename = reg36\n"
+                   "[LUT]\nmax_iter = %d\ndesign_thr = %s\nqbits_channel = %d\nqbits_message_uniform = %d\n"
+                   % _design_keys("c1b_reg36_n1000"))
+    sim = bs.LDPC_BER_Sim_LUT(bs.SimParams(str(ini)), rand_seed=7, chunk_frames=2048).load(str(tmp_path))
+    sim.run(verbose=False)
+    saved = tmp_path / "results" / sim.gen_filename() / "lut_codec.it"
+    assert saved.exists()
+    dec = L.Decoder(str(saved))
+    fx = pyoracle.read_fixture(_golden.fixture_path("c1b_reg36_n1000", "snr1.5"))
+    dec.set_exit_conditions(dec.max_iters, True, True)
+    bits, iters = dec.decode_quantized(fx["cha"], fx["msg"])
+    assert np.array_equal(iters, fx["ret"]) and np.array_equal(bits, fx["out"])
+    assert saved.read_bytes() == open(_golden.codec_path("c1b_reg36_n1000"), "rb").read()
+
+
+def _design_keys(cfg):
+    """(max_iter, design_thr, qbits_channel, qbits_message) of the reference design run recorded in the manifest"""
+    a = _golden.MANIFEST[cfg]["design"].split()
+    kv = {a[i]: a[i + 1] for i in range(len(a) - 1) if a[i].startswith("--")}
+    return int(kv["--max-iter"]), kv["--design-thr"], int(kv["--qcha"]), int(kv["--qmsg"])
