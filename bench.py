@@ -365,10 +365,10 @@ def run_b200(args):
 
     # ---- the BP comparison decoder of ber_sim's [BP] section on the same code and SNR (IT++ LDPC_Code::bp_decode,
     # int32 QLLR messages, [BP] defaults except max_iter = the LUT decoder's): Monte-Carlo step on the device
-    import _alist
     from lut_ldpc_b200 import capi as _capi
-    bp_graph = _alist.bundle_graph(cfg)
-    bp_graph["nchk_lin_indep"] = N - K  # same rate as the LUT decoder of this bundle
+    _b = _golden.read_bundle(_golden.bundle_path(cfg))  # the graph of the same code
+    bp_graph = dict(dv_vec=_b["dv_vec"], dc_vec=_b["dc_vec"], cn_msg_idx=_b["cn_msg_idx"],
+                    nchk_lin_indep=N - K)  # same rate as the LUT decoder of this bundle
     bpd = _capi.BpDecoder(bp_graph, max_iters=dec.max_iters)
     Fbp = min(F, 8192)
     bpd.simulate_snr(snr, Fbp, seed=5, batch_frames=Fbp)
