@@ -2,7 +2,9 @@
 """BER/FER curve of one golden decoder over an SNR grid with the multi-GPU Monte-Carlo harness (ber_sim.py: disjoint Philox
 frame ranges per rank, lutldpc_simulate_snr, NCCL all-reduce of the counters after every chunk, global stop rules as
 LDPC_BER_Sim::run / sim_snr_point).  Launch with torchrun (one rank per GPU) or plain python (one GPU).
-  ber_curves.py <cfg> <SNRdB vec, e.g. 0:.5:4> <Nframes> <Nfers> <ber_min> <fer_min> <chunk per GPU> <out.json>"""
+  ber_curves.py <cfg> <SNRdB vec, e.g. 0:.5:4> <Nframes> <Nfers> <ber_min> <fer_min> <chunk per GPU> <out.json> [bp [max_iter]]
+A trailing `bp` runs the BP comparison decoder of the [BP] section on the same code and the same noise (same seed and
+frame indices) instead of the LUT decoder."""
 import json
 import os
 import sys
@@ -32,10 +34,17 @@ def main():
                      initial_message_mode="from_quantized_channel_llrs" if man["init_mode"] == "qcha" else "from_continuous_input")
     sim = bs.LDPC_BER_Sim_LUT(p, rand_seed=2026, chunk_frames=chunk, dist=dist if world > 1 else None,
                               device="cuda" if world > 1 else None)
-    from lut_ldpc_b200.capi import Decoder, INIT_CONT, INIT_QCHA
-    sim.dec = Decoder(p.codec_filename)
-    sim.dec.set_exit_conditions(sim.dec.max_iters, True, True)
-    sim.dec.set_initial_message_mode(INIT_QCHA if man["init_mode"] == "qcha" else INIT_CONT)
+    from lut_ldpc_b200.capi import BpDecoder, Decoder, INIT_CONT, INIT_QCHA
+    use_bp = len(sys.argv) > 9 and sys.argv[9] == "bp"
+    if use_bp:
+        b = _golden.read_bundle(p.codec_filename)
+        sim.dec = BpDecoder(dict(dv_vec=b["dv_vec"], dc_vec=b["dc_vec"], cn_msg_idx=b["cn_msg_idx"],
+                                 nchk_lin_indep=b["nchk_lin_indep"]),
+                            max_iters=int(sys.argv[10]) if len(sys.argv) > 10 else b["max_iters"])
+    else:
+        sim.dec = Decoder(p.codec_filename)
+        sim.dec.set_exit_conditions(sim.dec.max_iters, True, True)
+        sim.dec.set_initial_message_mode(INIT_QCHA if man["init_mode"] == "qcha" else INIT_CONT)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -43,7 +52,7 @@ def main():
     r = sim.run(verbose=int(os.environ.get("RANK", 0)) == 0)
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
-    r.update(cfg=cfg, design=man["design"], world=world, wall_s=round(wall, 3), Nframes=nframes, Nfers=nfers, ber_min=ber_min,
+    r.update(cfg=cfg, decoder="bp (IT++ bp_decode, QLLR 12/300/7/28)" if use_bp else "lut", design=man["design"], world=world, wall_s=round(wall, 3), Nframes=nframes, Nfers=nfers, ber_min=ber_min,
              fer_min=fer_min, chunk_frames_per_gpu=chunk, allreduces=sim.n_allreduce,
              allreduce_s=round(sim.t_allreduce, 4), simulate_s=round(sim.t_simulate, 3),
              ninfo=sim.dec.ninfo, nvar=sim.dec.nvar,
