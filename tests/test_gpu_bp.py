@@ -205,3 +205,22 @@ def test_ber_sim_with_a_bp_section(capi, tmp_path):
         fer = float(line.split("FER: ")[1])
         assert frames == 20000 and _agree(round(fer * frames), frames, ref[s]["frame_errors"], ref[s]["frames"]), (s, line)
     assert any(d.startswith("RES_N500_R0.5_maxIter30_zcw0_frames20000") for d in os.listdir(tmp_path / "results"))
+
+
+def test_cpp_facade_one_frame_per_call(tmp_path):
+    """host/ldpc_code_bp.hpp: Channel_Code::decode(vec), bp_decode, encode -- one frame per call like the reference's
+    callers -- against a reference fixture"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "facade_check_bp")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-o", exe, os.path.join(root, "tests", "facade_check_bp.cpp"),
+                           "-I" + root, "-L" + os.path.join(root, "lut_ldpc_b200"), "-llutldpc_b200",
+                           "-Wl,-rpath," + os.path.join(root, "lut_ldpc_b200")])
+    alist = str(tmp_path / "reg36.alist")
+    _alist.write_alist("c1b_reg36_n1000", alist)
+    _bpgolden.fixture("c1b_default")  # unpacks into the cache
+    fix = os.path.join(_golden.CACHE, "bp_c1b_default.fix")
+    p = subprocess.run([exe, alist, fix], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, (p.stdout[-2000:], p.stderr[-2000:])
+    r = json.loads(p.stdout.strip().splitlines()[-1])
+    assert r["frames"] == 12 and r["mismatches"] == 0 and r["checked"] >= 3 * 12
