@@ -36,6 +36,7 @@ constexpr int kCnRegsMax = 32;  // check degrees up to this run out of registers
 struct Calc {
   int d1, d2, d3, qmax;  // Dint1..3, qllr_max = 2^(Dint4-1) - 1
   double scale, qmax_d;  // 2^Dint1, to_double(qllr_max)
+  int four, two;         // 4 and 2 as run-time values: multiplications by them stay on the FMA pipe (see bp_logexp)
 };
 
 // LLR_calc_unit::to_qllr, llr.h:266-279 (positive overflow returns QLLR_MAX, not qllr_max)
@@ -47,21 +48,36 @@ __device__ __forceinline__ int bp_to_qllr(double l, const Calc& c) {
 __device__ __forceinline__ int bp_clamp(int v, int qmax) { return max(-qmax, min(qmax, v)); }
 // qsum, llr.h:320-329
 __device__ __forceinline__ int bp_qsum(int a, int b, int qmax) { return bp_clamp(a + b, qmax); }
-// logexp, llr.h:282-298 (x >= 0): 0 beyond the table -- tab[d2] holds that 0, so the index is clamped, not tested
-__device__ __forceinline__ int bp_logexp(int x, const int* tab, const Calc& c) { return tab[min(x >> c.d3, c.d2)]; }
+// logexp, llr.h:282-298 (x >= 0): 0 beyond the table -- tab[d2] holds that 0, so the index is clamped, not tested.
+// tab is the table's shared-memory address; the byte address is formed with a multiply-add (FMA pipe) because the
+// integer ALU pipe is what bounds the check pass.
+__device__ __forceinline__ int bp_logexp(int x, uint32_t tab, const Calc& c) {
+  const int idx = min(x >> c.d3, c.d2);
+  uint32_t addr;
+  int v;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(addr) : "r"(idx), "r"(c.four), "r"(tab));
+  asm("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
 // Boxplus, llr.cpp:148-185: term1 + logexp(|a+b|) - logexp(|a-b|), saturated, with term1 = sign(a) sign(b) min(|a|,|b|)
 // (the reference's nested selects give 0 when a or b is 0, like the product).  {|a+b|, |a-b|} = {|a|+|b|, ||a|-|b||},
 // in this order when the signs agree and swapped when they differ, so the value is sign(a) sign(b) * r with
 // r = min + logexp(|a|+|b|) - logexp(max-min); the saturation is symmetric, so it commutes with the sign.  For a or b
-// = 0 both forms give logexp(max) - logexp(max) = 0.  Fewer operations on the integer ALU pipe, which bounds the pass.
-__device__ __forceinline__ int bp_boxplus(int a, int b, const int* tab, const Calc& c) {
+// = 0 both forms give logexp(max) - logexp(max) = 0.
+// FAST: a table is in use and qllr_max >= table[0]; then r >= min - table[0] >= -qllr_max and the lower saturation
+// cannot trigger.  The sign is applied by a multiplication (FMA pipe again).
+template <bool FAST>
+__device__ __forceinline__ int bp_boxplus(int a, int b, uint32_t tab, const Calc& c) {
   const int aa = abs(a), bb = abs(b);
   const int mn = min(aa, bb), mx = max(aa, bb);
   int r = mn;
-  if (c.d2 != 0) r += bp_logexp(aa + bb, tab, c) - bp_logexp(mx - mn, tab, c);
-  r = bp_clamp(r, c.qmax);
+  if (FAST || c.d2 != 0) r += bp_logexp(aa + bb, tab, c) - bp_logexp(mx - mn, tab, c);
+  r = FAST ? min(r, c.qmax) : bp_clamp(r, c.qmax);
   const int sg = (a ^ b) >> 31;  // 0 or -1
-  return (r ^ sg) - sg;
+  int sgn, res;
+  asm("mad.lo.s32 %0, %1, %2, 1;" : "=r"(sgn) : "r"(sg), "r"(c.two));
+  asm("mul.lo.s32 %0, %1, %2;" : "=r"(res) : "r"(r), "r"(sgn));
+  return res;
 }
 
 __device__ __forceinline__ bool slot_done(const uint32_t* donew, size_t s) { return (donew[s >> 5] >> (s & 31)) & 1u; }
@@ -115,7 +131,7 @@ __device__ __forceinline__ int32_t* bp_row(int32_t* col, uint32_t e, uint32_t S4
 // cls_edge = the edge ids of the class's checks, DC per check, back to back.  A block takes CPB checks: their
 // CPB * DC edge ids are staged in shared memory with one coalesced load, then every thread has all CPB * DC message
 // loads of its slot in flight before the first Boxplus -- the pass is bound by memory latency otherwise.
-template <int DC, int CPB>
+template <int DC, int CPB, bool FAST>
 __global__ void __launch_bounds__(kBpThreads) k_bp_cn_deg(const int32_t* __restrict__ cls_edge, int n_list, uint32_t S4,
                                                            int32_t* __restrict__ msg, const uint32_t* __restrict__ donew, Calc c,
                                                            const int32_t* __restrict__ table) {
@@ -126,6 +142,7 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_cn_deg(const int32_t* __restr
     s_idx[i] = t0 * DC + i < n_list * DC ? (uint32_t)cls_edge[(size_t)t0 * DC + i] : 0u;
   for (int i = threadIdx.x; i <= c.d2; i += kBpThreads) s_tab[i] = i < c.d2 ? table[i] : 0;
   __syncthreads();
+  const uint32_t tb = (uint32_t)__cvta_generic_to_shared(s_tab);
   const size_t s = (size_t)blockIdx.y * kBpThreads + threadIdx.x;
   if (slot_done(donew, s)) return;
   int32_t* col = msg + s;
@@ -139,27 +156,27 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_cn_deg(const int32_t* __restr
     if (t0 + q >= n_list) break;
     const uint32_t* e = s_idx + q * DC;
     if constexpr (DC == 6) {
-      const int m01 = bp_boxplus(m[q][0], m[q][1], s_tab, c), m23 = bp_boxplus(m[q][2], m[q][3], s_tab, c),
-                m45 = bp_boxplus(m[q][4], m[q][5], s_tab, c);
-      const int m03 = bp_boxplus(m01, m23, s_tab, c), m25 = bp_boxplus(m23, m45, s_tab, c),
-                m0145 = bp_boxplus(m01, m45, s_tab, c);
-      *bp_row(col, e[0], S4) = bp_boxplus(m[q][1], m25, s_tab, c);
-      *bp_row(col, e[1], S4) = bp_boxplus(m[q][0], m25, s_tab, c);
-      *bp_row(col, e[2], S4) = bp_boxplus(m0145, m[q][3], s_tab, c);
-      *bp_row(col, e[3], S4) = bp_boxplus(m0145, m[q][2], s_tab, c);
-      *bp_row(col, e[4], S4) = bp_boxplus(m03, m[q][5], s_tab, c);
-      *bp_row(col, e[5], S4) = bp_boxplus(m03, m[q][4], s_tab, c);
+      const int m01 = bp_boxplus<FAST>(m[q][0], m[q][1], tb, c), m23 = bp_boxplus<FAST>(m[q][2], m[q][3], tb, c),
+                m45 = bp_boxplus<FAST>(m[q][4], m[q][5], tb, c);
+      const int m03 = bp_boxplus<FAST>(m01, m23, tb, c), m25 = bp_boxplus<FAST>(m23, m45, tb, c),
+                m0145 = bp_boxplus<FAST>(m01, m45, tb, c);
+      *bp_row(col, e[0], S4) = bp_boxplus<FAST>(m[q][1], m25, tb, c);
+      *bp_row(col, e[1], S4) = bp_boxplus<FAST>(m[q][0], m25, tb, c);
+      *bp_row(col, e[2], S4) = bp_boxplus<FAST>(m0145, m[q][3], tb, c);
+      *bp_row(col, e[3], S4) = bp_boxplus<FAST>(m0145, m[q][2], tb, c);
+      *bp_row(col, e[4], S4) = bp_boxplus<FAST>(m03, m[q][5], tb, c);
+      *bp_row(col, e[5], S4) = bp_boxplus<FAST>(m03, m[q][4], tb, c);
     } else {
       int suf[DC];
       suf[DC - 1] = m[q][DC - 1];
 #pragma unroll
-      for (int k = DC - 2; k >= 1; --k) suf[k] = bp_boxplus(suf[k + 1], m[q][k], s_tab, c);
+      for (int k = DC - 2; k >= 1; --k) suf[k] = bp_boxplus<FAST>(suf[k + 1], m[q][k], tb, c);
       *bp_row(col, e[0], S4) = suf[1];
       int l = m[q][0];
 #pragma unroll
       for (int k = 1; k <= DC - 2; ++k) {
-        *bp_row(col, e[k], S4) = bp_boxplus(l, suf[k + 1], s_tab, c);
-        l = bp_boxplus(l, m[q][k], s_tab, c);
+        *bp_row(col, e[k], S4) = bp_boxplus<FAST>(l, suf[k + 1], tb, c);
+        l = bp_boxplus<FAST>(l, m[q][k], tb, c);
       }
       *bp_row(col, e[DC - 1], S4) = l;
     }
@@ -179,6 +196,7 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_cn_big(const int32_t* __restr
   const int T = blockDim.x;
   for (int i = threadIdx.x; i <= c.d2; i += T) s_tab[i] = i < c.d2 ? table[i] : 0;
   __syncthreads();
+  const uint32_t tb = (uint32_t)__cvta_generic_to_shared(s_tab);
   const size_t s = (size_t)blockIdx.y * T + threadIdx.x;
   if (slot_done(donew, s)) return;
   int32_t* col = msg + s;
@@ -189,28 +207,28 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_cn_big(const int32_t* __restr
     for (int k = 0; k < dc; ++k) s_m[k * T] = *bp_row(col, idx[k], S4);
     if (dc == 6) {
       const int m0 = s_m[0], m1 = s_m[T], m2 = s_m[2 * T], m3 = s_m[3 * T], m4 = s_m[4 * T], m5 = s_m[5 * T];
-      const int m01 = bp_boxplus(m0, m1, s_tab, c), m23 = bp_boxplus(m2, m3, s_tab, c), m45 = bp_boxplus(m4, m5, s_tab, c);
-      const int m03 = bp_boxplus(m01, m23, s_tab, c), m25 = bp_boxplus(m23, m45, s_tab, c),
-                m0145 = bp_boxplus(m01, m45, s_tab, c);
-      *bp_row(col, idx[0], S4) = bp_boxplus(m1, m25, s_tab, c);
-      *bp_row(col, idx[1], S4) = bp_boxplus(m0, m25, s_tab, c);
-      *bp_row(col, idx[2], S4) = bp_boxplus(m0145, m3, s_tab, c);
-      *bp_row(col, idx[3], S4) = bp_boxplus(m0145, m2, s_tab, c);
-      *bp_row(col, idx[4], S4) = bp_boxplus(m03, m5, s_tab, c);
-      *bp_row(col, idx[5], S4) = bp_boxplus(m03, m4, s_tab, c);
+      const int m01 = bp_boxplus<false>(m0, m1, tb, c), m23 = bp_boxplus<false>(m2, m3, tb, c), m45 = bp_boxplus<false>(m4, m5, tb, c);
+      const int m03 = bp_boxplus<false>(m01, m23, tb, c), m25 = bp_boxplus<false>(m23, m45, tb, c),
+                m0145 = bp_boxplus<false>(m01, m45, tb, c);
+      *bp_row(col, idx[0], S4) = bp_boxplus<false>(m1, m25, tb, c);
+      *bp_row(col, idx[1], S4) = bp_boxplus<false>(m0, m25, tb, c);
+      *bp_row(col, idx[2], S4) = bp_boxplus<false>(m0145, m3, tb, c);
+      *bp_row(col, idx[3], S4) = bp_boxplus<false>(m0145, m2, tb, c);
+      *bp_row(col, idx[4], S4) = bp_boxplus<false>(m03, m5, tb, c);
+      *bp_row(col, idx[5], S4) = bp_boxplus<false>(m03, m4, tb, c);
       continue;
     }
     int r = s_m[(dc - 1) * T];
     s_suf[(dc - 1) * T] = r;
     for (int k = dc - 2; k >= 1; --k) {
-      r = bp_boxplus(r, s_m[k * T], s_tab, c);
+      r = bp_boxplus<false>(r, s_m[k * T], tb, c);
       s_suf[k * T] = r;
     }
     *bp_row(col, idx[0], S4) = s_suf[T];
     int l = s_m[0];
     for (int k = 1; k <= dc - 2; ++k) {
-      *bp_row(col, idx[k], S4) = bp_boxplus(l, s_suf[(k + 1) * T], s_tab, c);
-      l = bp_boxplus(l, s_m[k * T], s_tab, c);
+      *bp_row(col, idx[k], S4) = bp_boxplus<false>(l, s_suf[(k + 1) * T], tb, c);
+      l = bp_boxplus<false>(l, s_m[k * T], tb, c);
     }
     *bp_row(col, idx[dc - 1], S4) = l;
   }
@@ -505,6 +523,7 @@ struct lutldpc_bp {
   lutldpc_bp_params par{};
   Calc calc{};
   bool repack_on = true;
+  bool fast_boxplus = false;  // a table is in use and qllr_max >= table[0] (see bp_boxplus)
   std::vector<int32_t> table;
   DevBuf<int32_t> d_vn_off, d_cn_off, d_cn_edge, d_cn_var, d_table, d_cn_list, d_cls_edge;
   struct CnClass { int dc, n, off, edge_off; };
@@ -572,8 +591,13 @@ template <int DC>
 void launch_cn_deg(lutldpc_bp* h, const lutldpc_bp::CnClass& cl, size_t S, int32_t* msg) {
   constexpr int CPB = DC <= 9 ? 4 : DC <= 16 ? 2 : 1;  // CPB * DC message registers per thread
   dim3 grid((cl.n + CPB - 1) / CPB, (unsigned)(S / kBpThreads));
-  k_bp_cn_deg<DC, CPB><<<grid, kBpThreads, ((size_t)h->calc.d2 + 1) * 4, h->stream>>>(h->d_cls_edge.p + cl.edge_off, cl.n, (uint32_t)(S * 4), msg,
-                                                                                   h->donew.p, h->calc, h->d_table.p);
+  const size_t smem = ((size_t)h->calc.d2 + 1) * 4;
+  if (h->fast_boxplus)
+    k_bp_cn_deg<DC, CPB, true><<<grid, kBpThreads, smem, h->stream>>>(h->d_cls_edge.p + cl.edge_off, cl.n, (uint32_t)(S * 4), msg,
+                                                                      h->donew.p, h->calc, h->d_table.p);
+  else
+    k_bp_cn_deg<DC, CPB, false><<<grid, kBpThreads, smem, h->stream>>>(h->d_cls_edge.p + cl.edge_off, cl.n, (uint32_t)(S * 4), msg,
+                                                                       h->donew.p, h->calc, h->d_table.p);
 }
 
 int launch_cn(lutldpc_bp* h, size_t S, int32_t* msg) {
@@ -929,6 +953,7 @@ int lutldpc_bp_create(const lutldpc_graph* gr, const lutldpc_bp_params* p, int w
   c.d1 = p->qllr_scale_res; c.d2 = p->qllr_table_size; c.d3 = p->qllr_spacing_res;
   c.qmax = (1 << (p->qllr_total_res - 1)) - 1;
   c.scale = (double)(1 << c.d1);
+  c.four = 4; c.two = 2;
   c.qmax_d = (double)c.qmax / (double)(1 << c.d1);
   h->table.assign(std::max(1, c.d2), 0);
   for (int i = 0; i < c.d2; ++i) {
@@ -936,6 +961,7 @@ int lutldpc_bp_create(const lutldpc_graph* gr, const lutldpc_bp_params* p, int w
     const double l = std::log(1 + std::exp(-x));
     h->table[i] = l > c.qmax_d ? kQllrMaxConst : l < -c.qmax_d ? -c.qmax : (int32_t)std::floor(0.5 + c.scale * l);
   }
+  h->fast_boxplus = c.d2 > 0 && c.qmax >= h->table[0];
   cudaError_t e = cudaSuccess;
   if (e == cudaSuccess) e = h->d_vn_off.upload(vn_off);
   if (e == cudaSuccess) e = h->d_cn_off.upload(cn_off);
