@@ -224,3 +224,56 @@ def test_cpp_facade_one_frame_per_call(tmp_path):
     assert p.returncode == 0, (p.stdout[-2000:], p.stderr[-2000:])
     r = json.loads(p.stdout.strip().splitlines()[-1])
     assert r["frames"] == 12 and r["mismatches"] == 0 and r["checked"] >= 3 * 12
+
+
+def _random_rows(rs, N, M, dcs):
+    """a random parity-check matrix: row c has dcs[c] distinct columns; every column is used at least once"""
+    rows = [sorted(rs.choice(N, size=d, replace=False).tolist()) for d in dcs]
+    used = set(v for r in rows for v in r)
+    for v in range(N):
+        if v not in used:
+            c = int(rs.randint(M))
+            rows[c] = sorted(set(rows[c]) | {v})
+    return rows
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_bp_random_graphs_and_llr_units_vs_oracle(capi, seed):
+    """random matrices (check degrees 2..40, variable degrees from 1) with random LLR_calc_unit parameters -- table
+    sizes from 0 (min-sum) up, coarse and fine spacings, total resolutions from 5 bits (saturation everywhere, the lower
+    clamp of Boxplus live) to 28 -- and random exit conditions: soft outputs and return values equal the oracle's"""
+    rs = np.random.RandomState(1000 + seed)
+    N, M = int(rs.randint(60, 400)), int(rs.randint(20, 120))
+    dcs = rs.choice([2, 3, 4, 5, 6, 7, 8, 9, 12, 17, 33, 40], size=M, p=[.1, .1, .1, .1, .15, .1, .1, .05, .05, .05, .05, .05])
+    dcs = np.minimum(dcs, N - 1)
+    g = _alist.graph_from_rows(N, _random_rows(rs, N, M, dcs))
+    d1 = int(rs.choice([2, 4, 8, 12]))
+    d4 = int(rs.choice([5, 8, 12, 16, 28]))
+    d4 = max(d4, d1 + 2) if rs.rand() < 0.7 else d4
+    par = pyoracle.BpParams(max_iter=int(rs.randint(1, 20)), psc=bool(rs.randint(2)), pisc=bool(rs.randint(2)),
+                            d1=d1, d2=int(rs.choice([0, 8, 64, 300])), d3=int(rs.randint(0, d1 + 1)), d4=d4)
+    dec = _dec(capi, g, par)
+    llr = rs.standard_normal((300, N)) * rs.choice([1.0, 4.0, 20.0]) + rs.choice([0.0, 2.0, 6.0])
+    qin = pyoracle.bp_to_qllr(llr, par.d1, par.d4)
+    want_out, want_ret = pyoracle.bp_decode(g["dv_vec"], g["dc_vec"], g["cn_msg_idx"], qin, par)
+    out, ret = dec.decode_qllr(qin)
+    assert np.array_equal(ret, want_ret), (seed, vars(par))
+    assert np.array_equal(out, want_out), (seed, vars(par))
+    bits, ret2 = dec.decode_llr(llr)
+    assert np.array_equal(ret2, want_ret) and np.array_equal(bits, (want_out < 0).astype(np.uint8))
+
+
+@pytest.mark.parametrize("d1,d2,d3,d4", [(12, 300, 7, 12), (12, 300, 7, 8), (12, 64, 9, 5), (6, 300, 0, 6)])
+def test_bp_resolutions_below_the_table_values(capi, d1, d2, d3, d4):
+    """qllr_max below logexp_table[0]: Boxplus saturates on both sides, and with Dint4 < Dint1 + 1 the table entries
+    themselves are to_qllr's overflow value QLLR_MAX (itpp/itpp/comm/llr.h:266-272).  Still the oracle's numbers."""
+    g = _bpgolden.graph("synth_mixed")
+    par = pyoracle.BpParams(max_iter=6, psc=True, pisc=False, d1=d1, d2=d2, d3=d3, d4=d4)
+    tab = pyoracle.bp_logexp_table(d1, d2, d3, d4)
+    assert tab[0] > (1 << (d4 - 1)) - 1
+    dec = _dec(capi, g, par)
+    llr = np.random.RandomState(d4).standard_normal((200, g["nvar"])) * 3 + 1
+    qin = pyoracle.bp_to_qllr(llr, d1, d4)
+    want_out, want_ret = pyoracle.bp_decode(g["dv_vec"], g["dc_vec"], g["cn_msg_idx"], qin, par)
+    out, ret = dec.decode_qllr(qin)
+    assert np.array_equal(ret, want_ret) and np.array_equal(out, want_out)
