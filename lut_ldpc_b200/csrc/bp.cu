@@ -16,6 +16,7 @@
 // saturation, and per node degree the same association of Boxplus / qsum operations.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -589,7 +590,10 @@ struct BatchIO {       // what a batch hands back
 
 template <int DC>
 void launch_cn_deg(lutldpc_bp* h, const lutldpc_bp::CnClass& cl, size_t S, int32_t* msg) {
-  constexpr int CPB = DC <= 9 ? 4 : DC <= 16 ? 2 : 1;  // CPB * DC message registers per thread
+  // two checks per block up to degree 16: 56 registers at degrees 7-8, i.e. 32 warps per SM with 14-16 loads each in
+  // flight (measured against 3 and 4 checks per block, which hold more loads per thread but 20 warps: 167 / 177 / 172 ms
+  // for the N=64800 step)
+  constexpr int CPB = DC <= 16 ? 2 : 1;
   dim3 grid((cl.n + CPB - 1) / CPB, (unsigned)(S / kBpThreads));
   const size_t smem = ((size_t)h->calc.d2 + 1) * 4;
   if (h->fast_boxplus)
