@@ -32,6 +32,8 @@ namespace {
 
 constexpr int kQllrMaxConst = INT32_MAX >> 4;  // QLLR_MAX, itpp/itpp/comm/llr.h:61
 constexpr int kBpThreads = 128;
+constexpr int kCnGroups = 4;   // groups of checks a block of the by-degree check kernel walks through
+constexpr int kVnGroups = 1;   // the same for the by-degree variable kernel (more than one group measured no gain)
 constexpr int kCnRegsMax = 32;  // check degrees up to this run out of registers, larger ones out of shared memory
 
 struct Calc {
@@ -137,16 +139,20 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_cn_deg(const int32_t* __restr
                                                            int32_t* __restrict__ msg, const uint32_t* __restrict__ donew, Calc c,
                                                            const int32_t* __restrict__ table) {
   extern __shared__ int s_tab[];
-  __shared__ uint32_t s_idx[CPB * DC];
-  const int t0 = blockIdx.x * CPB;
-  for (int i = threadIdx.x; i < CPB * DC; i += kBpThreads)
-    s_idx[i] = t0 * DC + i < n_list * DC ? (uint32_t)cls_edge[(size_t)t0 * DC + i] : 0u;
+  __shared__ uint32_t s_idx_all[kCnGroups * CPB * DC];
+  const int tb0 = blockIdx.x * (kCnGroups * CPB);
+  for (int i = threadIdx.x; i < kCnGroups * CPB * DC; i += kBpThreads)
+    s_idx_all[i] = tb0 * DC + i < n_list * DC ? (uint32_t)cls_edge[(size_t)tb0 * DC + i] : 0u;
   for (int i = threadIdx.x; i <= c.d2; i += kBpThreads) s_tab[i] = i < c.d2 ? table[i] : 0;
   __syncthreads();
   const uint32_t tb = (uint32_t)__cvta_generic_to_shared(s_tab);
   const size_t s = (size_t)blockIdx.y * kBpThreads + threadIdx.x;
   if (slot_done(donew, s)) return;
   int32_t* col = msg + s;
+  for (int g = 0; g < kCnGroups; ++g) {  // the table and the edge ids are staged once for kCnGroups groups of CPB checks
+  const int t0 = tb0 + g * CPB;
+  if (t0 >= n_list) break;
+  const uint32_t* s_idx = s_idx_all + g * CPB * DC;
   int m[CPB][DC];
 #pragma unroll
   for (int q = 0; q < CPB; ++q)
@@ -181,6 +187,7 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_cn_deg(const int32_t* __restr
       }
       *bp_row(col, e[DC - 1], S4) = l;
     }
+  }
   }
 }
 
@@ -245,12 +252,12 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_vn_deg(const int32_t* __restr
                                                            int32_t* __restrict__ msg, const int32_t* __restrict__ qin,
                                                            const uint32_t* __restrict__ donew, uint32_t* __restrict__ hardw,
                                                            int32_t* __restrict__ soft, int qmax) {
-  __shared__ int s_i[VPB], s_e0[VPB];
-  if (threadIdx.x < VPB) {
-    const int t = blockIdx.x * VPB + threadIdx.x;
+  __shared__ int s_i_all[kVnGroups * VPB], s_e0_all[kVnGroups * VPB];
+  if (threadIdx.x < kVnGroups * VPB) {
+    const int t = blockIdx.x * (kVnGroups * VPB) + threadIdx.x;
     const int i = t < n_list ? list[t] : -1;
-    s_i[threadIdx.x] = i;
-    s_e0[threadIdx.x] = i >= 0 ? vn_off[i] : 0;
+    s_i_all[threadIdx.x] = i;
+    s_e0_all[threadIdx.x] = i >= 0 ? vn_off[i] : 0;
   }
   __syncthreads();
   const size_t s = (size_t)blockIdx.y * kBpThreads + threadIdx.x;
@@ -259,6 +266,10 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_vn_deg(const int32_t* __restr
   if (dmask == 0xFFFFFFFFu) return;  // the whole warp has returned
   const uint32_t S32 = S4 >> 7;
   const bool lane0 = (threadIdx.x & 31) == 0;
+  for (int g = 0; g < kVnGroups; ++g) {  // the variable ids are staged once for kVnGroups groups of VPB variables
+  const int* s_i = s_i_all + g * VPB;
+  const int* s_e0 = s_e0_all + g * VPB;
+  if (s_i[0] < 0) break;
   int L[VPB], m[VPB][DV];
   uint32_t old[VPB];
 #pragma unroll
@@ -305,6 +316,7 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_vn_deg(const int32_t* __restr
     }
     const uint32_t bal = __ballot_sync(0xFFFFFFFFu, !done && out < 0);
     if (lane0) hardw[(size_t)i * S32 + (s >> 5)] = (old[v] & dmask) | (bal & ~dmask);
+  }
   }
 }
 
@@ -594,7 +606,7 @@ void launch_cn_deg(lutldpc_bp* h, const lutldpc_bp::CnClass& cl, size_t S, int32
   // flight (measured against 3 and 4 checks per block, which hold more loads per thread but 20 warps: 167 / 177 / 172 ms
   // for the N=64800 step)
   constexpr int CPB = DC <= 16 ? 2 : 1;
-  dim3 grid((cl.n + CPB - 1) / CPB, (unsigned)(S / kBpThreads));
+  dim3 grid((cl.n + kCnGroups * CPB - 1) / (kCnGroups * CPB), (unsigned)(S / kBpThreads));
   const size_t smem = ((size_t)h->calc.d2 + 1) * 4;
   if (h->fast_boxplus)
     k_bp_cn_deg<DC, CPB, true><<<grid, kBpThreads, smem, h->stream>>>(h->d_cls_edge.p + cl.edge_off, cl.n, (uint32_t)(S * 4), msg,
@@ -630,7 +642,7 @@ int launch_cn(lutldpc_bp* h, size_t S, int32_t* msg) {
 template <int DV>
 void launch_vn_deg(lutldpc_bp* h, const lutldpc_bp::CnClass& cl, size_t S, int32_t* msg, const int32_t* qin, int32_t* soft) {
   constexpr int VPB = DV <= 2 ? 8 : DV <= 4 ? 4 : DV <= 8 ? 2 : 1;  // VPB * DV message registers per thread
-  dim3 grid((cl.n + VPB - 1) / VPB, (unsigned)(S / kBpThreads));
+  dim3 grid((cl.n + kVnGroups * VPB - 1) / (kVnGroups * VPB), (unsigned)(S / kBpThreads));
   k_bp_vn_deg<DV, VPB><<<grid, kBpThreads, 0, h->stream>>>(h->d_vn_list.p + cl.off, cl.n, h->d_vn_off.p, (uint32_t)(S * 4), msg, qin,
                                                           h->donew.p, h->hardw.p, soft, h->calc.qmax);
 }
