@@ -312,6 +312,13 @@ typedef struct lutldpc_bp_params {
 } lutldpc_bp_params;
 int lutldpc_bp_create(const lutldpc_graph* g, const lutldpc_bp_params* p, int with_generator, lutldpc_bp** out,
                       int32_t* col_perm);
+/* bp_codec.it == IT++'s LDPC_Code::save_code / load_code file (itpp/itpp/comm/ldpc.cpp:1250-1322) with the block
+ * LDPC_Generator_Systematic::save appends (:1002-1009): what ber_sim saves for a [BP] run when the seed equals
+ * Sim.save_codec and loads through Sim.codec_filename + Sim.codec_type = BP (src/LDPC_BER_Sim.cpp:207-239).
+ * lutldpc_bp_convert_alist: alist in, codec file (no generator) out; pure host code. */
+int lutldpc_bp_create_from_file(const char* codec_path, const lutldpc_bp_params* p, lutldpc_bp** out);
+int lutldpc_bp_save_code(lutldpc_bp* h, const char* path);
+int lutldpc_bp_convert_alist(const char* alist_path, const char* out_it_path);
 void lutldpc_bp_destroy(lutldpc_bp* h);
 const char* lutldpc_bp_last_error(const lutldpc_bp* h);   /* h == NULL: error of the last failed lutldpc_bp_create */
 int lutldpc_bp_get_info(const lutldpc_bp* h, lutldpc_info* info);   /* nvar, nchk, nchk_lin_indep, ninfo, num_edges,

@@ -250,19 +250,36 @@ class LDPC_BER_Sim(LDPC_BER_Sim_LUT):
     def load(self, basedir="."):
         from .capi import BpDecoder, alist_graph
         p = self.p
-        if p.codec_filename:
-            raise RuntimeError("LDPC_BER_Sim::load(): stored bp_codec.it files are not supported, name the alist "
-                               "(LDPC.parity_filename)")
+        kw = dict(max_iters=p.bp_max_iter, psc=p.parity_check_iter, pisc=p.parity_check_iter,
+                  qllr_scale_res=p.qllr_scale_res, qllr_table_size=p.qllr_table_size,
+                  qllr_spacing_res=p.qllr_spacing_res, qllr_total_res=p.qllr_total_res)
+        if p.codec_filename:  # codes_path / codec_filename, src/LDPC_BER_Sim.cpp:219-239
+            path = os.path.join(basedir, p.codes_dir, p.codec_filename)
+            if os.path.isabs(p.codec_filename) or not os.path.exists(path):
+                path = p.codec_filename if os.path.isabs(p.codec_filename) else os.path.join(basedir, p.codec_filename)
+            if not os.path.exists(path):
+                raise RuntimeError("Codec file" + path + " does not exist!")
+            self.dec = BpDecoder.from_file(path, **kw)
+            if not p.zero_codeword and not self.dec.has_gen:
+                raise RuntimeError("LDPC_BER_Sim::load(): LDPC.zero_codeword = false needs a codec file with a generator")
+            return self
         if not p.parity_filename:
             raise RuntimeError("LDPC_BER_Sim::load(): LDPC.parity_filename is required")
         alist = os.path.join(basedir, p.codes_dir, p.parity_filename + ".alist")
         if not os.path.exists(alist):
             raise RuntimeError("Parity file" + alist + " does not exist!")  # :162-164
-        self.dec = BpDecoder(alist_graph(alist), max_iters=p.bp_max_iter, psc=p.parity_check_iter, pisc=p.parity_check_iter,
-                             qllr_scale_res=p.qllr_scale_res, qllr_table_size=p.qllr_table_size,
-                             qllr_spacing_res=p.qllr_spacing_res, qllr_total_res=p.qllr_total_res,
-                             with_generator=not p.zero_codeword)
+        self.dec = BpDecoder(alist_graph(alist), with_generator=not p.zero_codeword, **kw)
+        if self.rand_seed == p.save_codec and self.rank == 0:  # :207-216
+            d = os.path.join(basedir, p.results_dir, self.gen_filename())
+            os.makedirs(d, exist_ok=True)
+            self.dec.save_code(os.path.join(d, "bp_codec.it"))
         return self
+
+    def gen_filename(self):
+        """LDPC_BER_Sim::gen_filename, src/LDPC_BER_Sim.cpp:104-114"""
+        p = self.p
+        return "%s_N%d_R%s_maxIter%d_zcw%d_frames%d%s" % (p.results_prefix, self.dec.nvar, "%g" % self.dec.rate, p.bp_max_iter,
+                                                         int(p.zero_codeword), p.Nframes, p.custom_name)
 
 
 def make_sim(params, **kw):

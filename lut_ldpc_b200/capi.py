@@ -210,6 +210,9 @@ def load_library():
     L.lutldpc_save_code.argtypes = [vp, C.c_char_p]
     L.lutldpc_convert_codec.argtypes = [C.c_char_p, C.c_char_p]
     L.lutldpc_bp_create.argtypes = [C.POINTER(_Graph), C.POINTER(_BpParams), i32, C.POINTER(vp), vp]
+    L.lutldpc_bp_create_from_file.argtypes = [C.c_char_p, C.POINTER(_BpParams), C.POINTER(vp)]
+    L.lutldpc_bp_save_code.argtypes = [vp, C.c_char_p]
+    L.lutldpc_bp_convert_alist.argtypes = [C.c_char_p, C.c_char_p]
     L.lutldpc_bp_destroy.argtypes = [vp]
     L.lutldpc_bp_destroy.restype = None
     L.lutldpc_bp_last_error.restype = C.c_char_p
@@ -478,21 +481,26 @@ class BpDecoder:
     (itpp/itpp/comm/ldpc.cpp:1398-1622; src/LDPC_BER_Sim.cpp:74-78,197-201)."""
 
     def __init__(self, graph, max_iters=30, psc=True, pisc=None, qllr_scale_res=12, qllr_table_size=300,
-                 qllr_spacing_res=7, qllr_total_res=28, with_generator=False):
-        """graph: the dict of alist_graph().  pisc defaults to psc, as LDPC_BER_Sim::load passes parity_check_iter twice."""
+                 qllr_spacing_res=7, qllr_total_res=28, with_generator=False, codec_file=None):
+        """graph: the dict of alist_graph() (or None with codec_file = a bp_codec.it, see from_file).  pisc defaults to
+        psc, as LDPC_BER_Sim::load passes parity_check_iter twice."""
         self._L = load_library()
         pisc = psc if pisc is None else pisc
-        dv = np.ascontiguousarray(graph["dv_vec"], np.int32)
-        dc = np.ascontiguousarray(graph["dc_vec"], np.int32)
-        idx = np.ascontiguousarray(graph["cn_msg_idx"], np.int32)
-        i32p = C.POINTER(C.c_int32)
-        g = _Graph(int(dv.size), int(dc.size), int(idx.size), int(graph.get("nchk_lin_indep", -1)),
-                   dv.ctypes.data_as(i32p), dc.ctypes.data_as(i32p), idx.ctypes.data_as(i32p))
         par = _BpParams(int(max_iters), int(bool(psc)), int(bool(pisc)), int(qllr_scale_res), int(qllr_table_size),
                         int(qllr_spacing_res), int(qllr_total_res))
         h = C.c_void_p()
-        self.col_perm = np.empty(dv.size, np.int32)
-        rc = self._L.lutldpc_bp_create(C.byref(g), C.byref(par), int(bool(with_generator)), C.byref(h), _p(self.col_perm))
+        if codec_file is not None:
+            self.col_perm = None
+            rc = self._L.lutldpc_bp_create_from_file(os.fsencode(codec_file), C.byref(par), C.byref(h))
+        else:
+            dv = np.ascontiguousarray(graph["dv_vec"], np.int32)
+            dc = np.ascontiguousarray(graph["dc_vec"], np.int32)
+            idx = np.ascontiguousarray(graph["cn_msg_idx"], np.int32)
+            i32p = C.POINTER(C.c_int32)
+            g = _Graph(int(dv.size), int(dc.size), int(idx.size), int(graph.get("nchk_lin_indep", -1)),
+                       dv.ctypes.data_as(i32p), dc.ctypes.data_as(i32p), idx.ctypes.data_as(i32p))
+            self.col_perm = np.empty(dv.size, np.int32)
+            rc = self._L.lutldpc_bp_create(C.byref(g), C.byref(par), int(bool(with_generator)), C.byref(h), _p(self.col_perm))
         if rc != 0:
             raise LutLdpcError(rc, (self._L.lutldpc_bp_last_error(None) or b"").decode())
         self._h = h
@@ -500,6 +508,15 @@ class BpDecoder:
         self._ck(self._L.lutldpc_bp_get_info(self._h, C.byref(info)))
         self.nvar, self.nchk, self.ninfo, self.num_edges = info.nvar, info.nchk, info.ninfo, info.num_edges
         self.nchk_lin_indep, self.max_iters, self.has_gen, self.rate = info.nchk_lin_indep, info.max_iters, bool(info.has_gen), info.rate
+
+    @classmethod
+    def from_file(cls, codec_file, **kw):
+        """LDPC_Code(filename, G): IT++'s bp_codec.it (LDPC_Code::save_code, with the generator if it was saved)."""
+        return cls(None, codec_file=codec_file, **kw)
+
+    def save_code(self, path):
+        """LDPC_Code::save_code (+ LDPC_Generator_Systematic::save when the handle carries the generator)."""
+        self._ck(self._L.lutldpc_bp_save_code(self._h, os.fsencode(path)))
 
     def close(self):
         if getattr(self, "_h", None):
@@ -550,3 +567,11 @@ class BpDecoder:
         ms, nl, fi = C.c_double(), C.c_int64(), C.c_int64()
         self._ck(self._L.lutldpc_bp_last_call_stats(self._h, C.byref(ms), C.byref(nl), C.byref(fi)))
         return dict(device_ms=ms.value, kernel_launches=nl.value, frame_iterations=fi.value)
+
+
+def bp_convert_alist(alist_path, out_it_path):
+    """alist -> bp_codec.it as IT++'s LDPC_Code(H).save_code() writes it (host only)."""
+    L = load_library()
+    rc = L.lutldpc_bp_convert_alist(os.fsencode(alist_path), os.fsencode(out_it_path))
+    if rc != 0:
+        raise LutLdpcError(rc, (L.lutldpc_bp_last_error(None) or b"").decode())

@@ -884,6 +884,97 @@ int decode_host(lutldpc_bp* h, int n_frames, const T* in, uint8_t* out_bits, int
 
 extern "C" {
 
+// the argument checks of LLR_calc_unit and set_exit_conditions
+static int bp_check_params(const lutldpc_bp_params* p) {
+  // LLR_calc_unit::init_llr_bounds asserts d4 <= 8*sizeof(QLLR)-4 (llr.cpp:74-80)
+  if (p->qllr_total_res < 2 || p->qllr_total_res > 28 || p->qllr_scale_res < 0 || p->qllr_scale_res > 27 ||
+      p->qllr_table_size < 0 || p->qllr_table_size > 8192 || p->qllr_spacing_res < 0 || p->qllr_spacing_res > 30 ||
+      p->max_iters < 0) {
+    g_bp_create_error = "LLR_calc_unit::init_llr_bounds(): Resolution too large! (or a negative [BP] parameter)";
+    return LUTLDPC_ERR_ARG;
+  }
+  return LUTLDPC_OK;
+}
+
+// everything after the graph is in h->g: degree classes, LLR_calc_unit table, device copies
+static int bp_finish(lutldpc_bp* h) {
+  const FlatGraph& g = h->g;
+  std::vector<int32_t> vn_off(g.nvar + 1, 0), cn_off(g.nchk + 1, 0), edge_var(g.num_edges), cn_var(g.num_edges);
+  for (int i = 0; i < g.nvar; ++i) {
+    if (g.dv[i] < 1) { g_bp_create_error = "LDPC_Code::bp_decode(): sumX1(i)=0"; return LUTLDPC_ERR_MODEL; }
+    vn_off[i + 1] = vn_off[i] + g.dv[i];
+    h->max_dv = std::max(h->max_dv, (int)g.dv[i]);
+    for (int k = 0; k < g.dv[i]; ++k) edge_var[vn_off[i] + k] = i;
+  }
+  for (int j = 0; j < g.nchk; ++j) {
+    if (g.dc[j] < 2) { g_bp_create_error = g.dc[j] == 0 ? "LDPC_Code::bp_decode(): sumX2(j)=0" : "LDPC_Code::bp_decode(): sumX2(j)=1"; return LUTLDPC_ERR_MODEL; }
+    if (g.dc[j] > 200) { g_bp_create_error = "check node degrees >200 not supported in this version"; return LUTLDPC_ERR_MODEL; }
+    cn_off[j + 1] = cn_off[j] + g.dc[j];
+    h->max_dc = std::max(h->max_dc, (int)g.dc[j]);
+  }
+  for (int e = 0; e < g.num_edges; ++e) cn_var[e] = edge_var[g.cn_msg_idx[e]];
+  std::vector<int32_t> cn_list, cls_edge;  // checks by degree, ascending index within a degree; their edge ids
+  for (int d = 2; d <= h->max_dc; ++d) {
+    lutldpc_bp::CnClass cl{d, 0, (int)cn_list.size(), (int)cls_edge.size()};
+    for (int j = 0; j < g.nchk; ++j)
+      if (g.dc[j] == d) {
+        cn_list.push_back(j);
+        ++cl.n;
+        cls_edge.insert(cls_edge.end(), g.cn_msg_idx.begin() + cn_off[j], g.cn_msg_idx.begin() + cn_off[j + 1]);
+      }
+    if (cl.n) h->cn_classes.push_back(cl);
+  }
+  std::vector<int32_t> vn_list;
+  for (int d = 1; d <= h->max_dv; ++d) {
+    lutldpc_bp::CnClass cl{d, 0, (int)vn_list.size(), 0};
+    for (int i = 0; i < g.nvar; ++i)
+      if (g.dv[i] == d) { vn_list.push_back(i); ++cl.n; }
+    if (cl.n) h->vn_classes.push_back(cl);
+  }
+  // LLR_calc_unit (llr.cpp:66-92)
+  Calc& c = h->calc;
+  c.d1 = h->par.qllr_scale_res; c.d2 = h->par.qllr_table_size; c.d3 = h->par.qllr_spacing_res;
+  c.qmax = (1 << (h->par.qllr_total_res - 1)) - 1;
+  c.scale = (double)(1 << c.d1);
+  c.four = 4; c.two = 2;
+  c.qmax_d = (double)c.qmax / (double)(1 << c.d1);
+  h->table.assign(std::max(1, c.d2), 0);
+  for (int i = 0; i < c.d2; ++i) {
+    const double x = std::pow(2.0, (double)(c.d3 - c.d1)) * i;
+    const double l = std::log(1 + std::exp(-x));
+    h->table[i] = l > c.qmax_d ? kQllrMaxConst : l < -c.qmax_d ? -c.qmax : (int32_t)std::floor(0.5 + c.scale * l);
+  }
+  h->fast_boxplus = c.d2 > 0 && c.qmax >= h->table[0];
+  cudaError_t e = cudaSuccess;
+  if (e == cudaSuccess) e = h->d_vn_off.upload(vn_off);
+  if (e == cudaSuccess) e = h->d_cn_off.upload(cn_off);
+  if (e == cudaSuccess) e = h->d_cn_edge.upload(g.cn_msg_idx);
+  if (e == cudaSuccess) e = h->d_cn_var.upload(cn_var);
+  if (e == cudaSuccess) e = h->d_table.upload(h->table);
+  if (e == cudaSuccess) e = h->d_cn_list.upload(cn_list);
+  if (e == cudaSuccess) e = h->d_cls_edge.upload(cls_edge);
+  if (e == cudaSuccess) e = h->d_vn_list.upload(vn_list);
+  if (e == cudaSuccess && h->max_dc > kCnRegsMax)
+    e = cudaFuncSetAttribute(k_bp_cn_big, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(((size_t)c.d2 + 1) * 4 + (size_t)2 * h->max_dc * 64 * 4));
+  if (e != cudaSuccess) {
+    g_bp_create_error = std::string("device set-up: ") + cudaGetErrorString(e);
+    cudaGetLastError();
+    return LUTLDPC_ERR_CUDA;
+  }
+  return LUTLDPC_OK;
+}
+
+static lutldpc_bp* bp_new(const lutldpc_bp_params* p) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { g_bp_create_error = "no CUDA device: the BP decoder has no CPU path"; cudaGetLastError(); return nullptr; }
+  lutldpc_bp* h = new (std::nothrow) lutldpc_bp();
+  if (!h) { g_bp_create_error = "out of memory"; return nullptr; }
+  h->device = dev;
+  h->par = *p;
+  return h;
+}
+
 int lutldpc_bp_create(const lutldpc_graph* gr, const lutldpc_bp_params* p, int with_generator, lutldpc_bp** out,
                       int32_t* col_perm) {
   if (!gr || !p || !out) { g_bp_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
@@ -892,19 +983,10 @@ int lutldpc_bp_create(const lutldpc_graph* gr, const lutldpc_bp_params* p, int w
     g_bp_create_error = "empty graph";
     return LUTLDPC_ERR_ARG;
   }
-  // LLR_calc_unit::init_llr_bounds asserts d4 <= 8*sizeof(QLLR)-4 (llr.cpp:74-80)
-  if (p->qllr_total_res < 2 || p->qllr_total_res > 28 || p->qllr_scale_res < 0 || p->qllr_scale_res > 27 ||
-      p->qllr_table_size < 0 || p->qllr_table_size > 8192 || p->qllr_spacing_res < 0 || p->qllr_spacing_res > 30 ||
-      p->max_iters < 0) {
-    g_bp_create_error = "LLR_calc_unit::init_llr_bounds(): Resolution too large! (or a negative [BP] parameter)";
-    return LUTLDPC_ERR_ARG;
-  }
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) { g_bp_create_error = "no CUDA device: the BP decoder has no CPU path"; cudaGetLastError(); return LUTLDPC_ERR_CUDA; }
-  lutldpc_bp* h = new (std::nothrow) lutldpc_bp();
-  if (!h) { g_bp_create_error = "out of memory"; return LUTLDPC_ERR_ARG; }
-  h->device = dev;
-  h->par = *p;
+  int rc = bp_check_params(p);
+  if (rc) return rc;
+  lutldpc_bp* h = bp_new(p);
+  if (!h) return LUTLDPC_ERR_CUDA;
   std::vector<int32_t> dv(gr->dv_vec, gr->dv_vec + gr->nvar), dc(gr->dc_vec, gr->dc_vec + gr->nchk),
       idx(gr->cn_msg_idx, gr->cn_msg_idx + gr->num_edges);
   ParityRows H;
@@ -931,71 +1013,138 @@ int lutldpc_bp_create(const lutldpc_graph* gr, const lutldpc_bp_params* p, int w
     h->nchk_lin_indep = gr->nchk_lin_indep >= 0 ? gr->nchk_lin_indep : (gr->nvar < 50000 ? gf2_rank_host(H) : gr->nchk);
     if (col_perm) for (int i = 0; i < gr->nvar; ++i) col_perm[i] = i;
   }
-  const FlatGraph& g = h->g;
-  std::vector<int32_t> vn_off(g.nvar + 1, 0), cn_off(g.nchk + 1, 0), edge_var(g.num_edges), cn_var(g.num_edges);
-  for (int i = 0; i < g.nvar; ++i) {
-    if (g.dv[i] < 1) { g_bp_create_error = "LDPC_Code::bp_decode(): sumX1(i)=0"; delete h; return LUTLDPC_ERR_MODEL; }
+  if ((rc = bp_finish(h))) { delete h; return rc; }
+  *out = h;
+  return LUTLDPC_OK;
+}
+
+// the arrays LDPC_Code keeps for H (decoder_parameterization, itpp/itpp/comm/ldpc.cpp:1676-1745) from the flat graph
+static void bp_codec_arrays(const FlatGraph& g, int nchk_lin_indep, BpCodecFile& f) {
+  const int N = g.nvar, M = g.nchk;
+  int cmax = 0, vmax = 0;
+  for (int d : g.dv) cmax = std::max(cmax, d);
+  for (int d : g.dc) vmax = std::max(vmax, d);
+  std::vector<int32_t> vn_off(N + 1, 0), cn_off(M + 1, 0), edge_var(g.num_edges), edge_chk(g.num_edges), edge_pos(g.num_edges);
+  for (int i = 0; i < N; ++i) {
     vn_off[i + 1] = vn_off[i] + g.dv[i];
-    h->max_dv = std::max(h->max_dv, (int)g.dv[i]);
     for (int k = 0; k < g.dv[i]; ++k) edge_var[vn_off[i] + k] = i;
   }
-  for (int j = 0; j < g.nchk; ++j) {
-    if (g.dc[j] < 2) { g_bp_create_error = g.dc[j] == 0 ? "LDPC_Code::bp_decode(): sumX2(j)=0" : "LDPC_Code::bp_decode(): sumX2(j)=1"; delete h; return LUTLDPC_ERR_MODEL; }
-    if (g.dc[j] > 200) { g_bp_create_error = "check node degrees >200 not supported in this version"; delete h; return LUTLDPC_ERR_MODEL; }
+  for (int j = 0; j < M; ++j) {
     cn_off[j + 1] = cn_off[j] + g.dc[j];
-    h->max_dc = std::max(h->max_dc, (int)g.dc[j]);
+    for (int k = 0; k < g.dc[j]; ++k) {
+      edge_chk[g.cn_msg_idx[cn_off[j] + k]] = j;
+      edge_pos[g.cn_msg_idx[cn_off[j] + k]] = k;
+    }
   }
-  for (int e = 0; e < g.num_edges; ++e) cn_var[e] = edge_var[g.cn_msg_idx[e]];
-  std::vector<int32_t> cn_list, cls_edge;  // checks by degree, ascending index within a degree; their edge ids
-  for (int d = 2; d <= h->max_dc; ++d) {
-    lutldpc_bp::CnClass cl{d, 0, (int)cn_list.size(), (int)cls_edge.size()};
-    for (int j = 0; j < g.nchk; ++j)
-      if (g.dc[j] == d) {
-        cn_list.push_back(j);
-        ++cl.n;
-        cls_edge.insert(cls_edge.end(), g.cn_msg_idx.begin() + cn_off[j], g.cn_msg_idx.begin() + cn_off[j + 1]);
+  f.nvar = N; f.ncheck = M; f.ncheck_lin_indep = nchk_lin_indep;
+  f.sumX1.assign(g.dv.begin(), g.dv.end());
+  f.sumX2.assign(g.dc.begin(), g.dc.end());
+  f.C.assign((size_t)cmax * N, 0); f.iind.assign((size_t)N * cmax, 0);
+  f.V.assign((size_t)M * vmax, 0); f.jind.assign((size_t)M * vmax, 0);
+  for (int i = 0; i < N; ++i)
+    for (int k = 0; k < g.dv[i]; ++k) {
+      const int e = vn_off[i] + k;
+      f.C[(size_t)k + (size_t)cmax * i] = edge_chk[e];                       // :1696-1701
+      f.iind[(size_t)i + (size_t)k * N] = edge_chk[e] + edge_pos[e] * M;     // :1731-1741
+    }
+  for (int j = 0; j < M; ++j)
+    for (int k = 0; k < g.dc[j]; ++k) {
+      const int e = g.cn_msg_idx[cn_off[j] + k], v = edge_var[e];
+      f.V[(size_t)j + (size_t)M * k] = v;                                    // :1705-1710
+      f.jind[(size_t)j + (size_t)k * M] = v + (e - vn_off[v]) * N;           // :1714-1726
+    }
+}
+
+int lutldpc_bp_convert_alist(const char* alist_path, const char* out_it_path) {
+  if (!alist_path || !out_it_path) { g_bp_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
+  ParityRows H;
+  std::string err;
+  if (!load_alist_file(alist_path, H, err)) { g_bp_create_error = err; return LUTLDPC_ERR_MODEL; }
+  FlatGraph g;
+  flatten_graph(H, g);
+  BpCodecFile f;
+  bp_codec_arrays(g, H.nvar < 50000 ? gf2_rank_host(H) : H.nchk, f);  // LDPC_Parity::get_ncheck_lin_indep, ldpc.h:138-147
+  if (!save_bp_codec_file(out_it_path, f, err)) { g_bp_create_error = err; return LUTLDPC_ERR_STATE; }
+  return LUTLDPC_OK;
+}
+
+int lutldpc_bp_save_code(lutldpc_bp* h, const char* path) {
+  if (!h || !path) return LUTLDPC_ERR_ARG;
+  BpCodecFile f;
+  bp_codec_arrays(h->g, h->nchk_lin_indep, f);
+  if (h->d_P) {  // G: (nvar - ninfo) x ninfo, the first ceil(ninfo / 8) bytes of every bit-packed row
+    CKB(cudaSetDevice(h->device), "cudaSetDevice");
+    std::vector<uint32_t> P((size_t)h->gen_rows * h->P_wp);
+    CKB(cudaMemcpy(P.data(), h->d_P, P.size() * 4, cudaMemcpyDeviceToHost), "D2H generator");
+    const size_t nb = (size_t)(h->gen_cols + 7) / 8;
+    f.gen_rows = h->gen_rows; f.gen_cols = h->gen_cols;
+    f.gen_bytes.resize((size_t)h->gen_rows * nb);
+    for (int r = 0; r < h->gen_rows; ++r) memcpy(&f.gen_bytes[r * nb], &P[(size_t)r * h->P_wp], nb);
+  }
+  std::string err;
+  if (!save_bp_codec_file(path, f, err)) return h->fail(LUTLDPC_ERR_STATE, err);
+  return LUTLDPC_OK;
+}
+
+int lutldpc_bp_create_from_file(const char* codec_path, const lutldpc_bp_params* p, lutldpc_bp** out) {
+  if (!codec_path || !p || !out) { g_bp_create_error = "NULL argument"; return LUTLDPC_ERR_ARG; }
+  *out = nullptr;
+  int rc = bp_check_params(p);
+  if (rc) return rc;
+  BpCodecFile f;
+  std::string err;
+  if (!load_bp_codec_file(codec_path, f, err)) { g_bp_create_error = err; return LUTLDPC_ERR_MODEL; }
+  // The graph exactly as the file holds it: the k-th edge of variable i is the check C(k + cmax*i), position ip of check
+  // j is the variable V(j + ncheck*ip) and its edge jind(j + ncheck*ip) = v + k*nvar.  The orders are kept as stored
+  // -- after LDPC_Generator_Systematic has permuted the columns of H, the lists of the reference's sparse matrix are
+  // no longer sorted, and the order of a node's inputs is the order of its Boxplus / qsum operations.
+  FlatGraph fg;
+  fg.nvar = f.nvar; fg.nchk = f.ncheck;
+  fg.dv.assign(f.sumX1.begin(), f.sumX1.end());
+  fg.dc.assign(f.sumX2.begin(), f.sumX2.end());
+  const size_t vmax = f.V.size() / (size_t)f.ncheck, cmax = f.C.size() / (size_t)f.nvar;
+  std::vector<int64_t> vn_off(f.nvar + 1, 0);
+  for (int i = 0; i < f.nvar; ++i) {
+    if (f.sumX1[i] < 0 || (size_t)f.sumX1[i] > cmax) { g_bp_create_error = "bp codec file: sumX1 out of range"; return LUTLDPC_ERR_MODEL; }
+    vn_off[i + 1] = vn_off[i] + f.sumX1[i];
+  }
+  if (vn_off[f.nvar] <= 0 || vn_off[f.nvar] > (1 << 28) || f.jind.size() != f.V.size() || f.iind.size() != f.C.size()) {
+    g_bp_create_error = "bp codec file: inconsistent array sizes";
+    return LUTLDPC_ERR_MODEL;
+  }
+  fg.num_edges = (int)vn_off[f.nvar];
+  std::vector<uint8_t> seen(fg.num_edges, 0);
+  for (int j = 0; j < f.ncheck; ++j) {
+    if (f.sumX2[j] < 0 || (size_t)f.sumX2[j] > vmax) { g_bp_create_error = "bp codec file: sumX2 out of range"; return LUTLDPC_ERR_MODEL; }
+    for (int ip = 0; ip < f.sumX2[j]; ++ip) {
+      const size_t at = (size_t)j + (size_t)f.ncheck * ip;
+      const int64_t ji = f.jind[at];
+      const int64_t v = ji % f.nvar, k = ji / f.nvar;
+      if (ji < 0 || v != f.V[at] || k >= f.sumX1[v] || f.C[(size_t)k + cmax * (size_t)v] != j || seen[vn_off[v] + k]) {
+        g_bp_create_error = "bp codec file: C, V and jind do not describe one graph";
+        return LUTLDPC_ERR_MODEL;
       }
-    if (cl.n) h->cn_classes.push_back(cl);
+      seen[vn_off[v] + k] = 1;
+      fg.cn_msg_idx.push_back((int32_t)(vn_off[v] + k));
+    }
   }
-  std::vector<int32_t> vn_list;
-  for (int d = 1; d <= h->max_dv; ++d) {
-    lutldpc_bp::CnClass cl{d, 0, (int)vn_list.size(), 0};
-    for (int i = 0; i < g.nvar; ++i)
-      if (g.dv[i] == d) { vn_list.push_back(i); ++cl.n; }
-    if (cl.n) h->vn_classes.push_back(cl);
+  if ((int)fg.cn_msg_idx.size() != fg.num_edges) { g_bp_create_error = "bp codec file: row and column weights disagree"; return LUTLDPC_ERR_MODEL; }
+  lutldpc_bp* h = bp_new(p);
+  if (!h) return LUTLDPC_ERR_CUDA;
+  h->g = fg;
+  h->nchk_lin_indep = f.ncheck_lin_indep;
+  if (f.gen_rows > 0) {
+    if (f.gen_rows != f.ncheck_lin_indep) { g_bp_create_error = "bp codec file: generator shape does not match the code"; delete h; return LUTLDPC_ERR_MODEL; }
+    const int wp = (f.gen_cols + 31) / 32;
+    const size_t nb = (size_t)(f.gen_cols + 7) / 8;
+    std::vector<uint32_t> P((size_t)f.gen_rows * wp, 0u);
+    for (int r = 0; r < f.gen_rows; ++r) memcpy(&P[(size_t)r * wp], &f.gen_bytes[r * nb], nb);
+    cudaError_t e = cudaMalloc((void**)&h->d_P, P.size() * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_P, P.data(), P.size() * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { g_bp_create_error = std::string("generator upload: ") + cudaGetErrorString(e); cudaGetLastError(); delete h; return LUTLDPC_ERR_CUDA; }
+    h->P_wp = wp; h->gen_rows = f.gen_rows; h->gen_cols = f.gen_cols;
   }
-  // LLR_calc_unit (llr.cpp:66-92)
-  Calc& c = h->calc;
-  c.d1 = p->qllr_scale_res; c.d2 = p->qllr_table_size; c.d3 = p->qllr_spacing_res;
-  c.qmax = (1 << (p->qllr_total_res - 1)) - 1;
-  c.scale = (double)(1 << c.d1);
-  c.four = 4; c.two = 2;
-  c.qmax_d = (double)c.qmax / (double)(1 << c.d1);
-  h->table.assign(std::max(1, c.d2), 0);
-  for (int i = 0; i < c.d2; ++i) {
-    const double x = std::pow(2.0, (double)(c.d3 - c.d1)) * i;
-    const double l = std::log(1 + std::exp(-x));
-    h->table[i] = l > c.qmax_d ? kQllrMaxConst : l < -c.qmax_d ? -c.qmax : (int32_t)std::floor(0.5 + c.scale * l);
-  }
-  h->fast_boxplus = c.d2 > 0 && c.qmax >= h->table[0];
-  cudaError_t e = cudaSuccess;
-  if (e == cudaSuccess) e = h->d_vn_off.upload(vn_off);
-  if (e == cudaSuccess) e = h->d_cn_off.upload(cn_off);
-  if (e == cudaSuccess) e = h->d_cn_edge.upload(g.cn_msg_idx);
-  if (e == cudaSuccess) e = h->d_cn_var.upload(cn_var);
-  if (e == cudaSuccess) e = h->d_table.upload(h->table);
-  if (e == cudaSuccess) e = h->d_cn_list.upload(cn_list);
-  if (e == cudaSuccess) e = h->d_cls_edge.upload(cls_edge);
-  if (e == cudaSuccess) e = h->d_vn_list.upload(vn_list);
-  if (e == cudaSuccess && h->max_dc > kCnRegsMax)
-    e = cudaFuncSetAttribute(k_bp_cn_big, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)(((size_t)c.d2 + 1) * 4 + (size_t)2 * h->max_dc * 64 * 4));
-  if (e != cudaSuccess) {
-    g_bp_create_error = std::string("device set-up: ") + cudaGetErrorString(e);
-    cudaGetLastError();
-    delete h;
-    return LUTLDPC_ERR_CUDA;
-  }
+  if ((rc = bp_finish(h))) { delete h; return rc; }
   *out = h;
   return LUTLDPC_OK;
 }

@@ -341,6 +341,82 @@ bool save_it_codec_file(const char* path, const DecoderModel& m, std::string& er
   return ok;
 }
 
+bool load_bp_codec_file(const char* path, BpCodecFile& o, std::string& err) {
+  ItFile f;
+  if (!read_it_file(path, f, err)) return false;
+  int32_t ver = 0;
+  bool h_def = false, g_def = false;
+  if (!f.i32("Fileversion", ver) || ver != 3) { err = "LDPC_Code::load_code(): Unsupported file format"; return false; }  // ldpc.cpp:42,1258-1260
+  if (!f.flag("H_defined", h_def) || !h_def) { err = "bp codec file: no parity-check matrix stored"; return false; }
+  f.flag("G_defined", g_def);
+  o = BpCodecFile();
+  int32_t nvar = 0, nchk = 0, nli = 0;
+  bool ok = f.i32("nvar", nvar) && f.i32("ncheck", nchk) && f.i32("ncheck_lin_indep", nli) && f.arr("C", "ivec", 4, o.C) &&
+            f.arr("V", "ivec", 4, o.V) && f.arr("sumX1", "ivec", 4, o.sumX1) && f.arr("sumX2", "ivec", 4, o.sumX2) &&
+            f.arr("iind", "ivec", 4, o.iind) && f.arr("jind", "ivec", 4, o.jind);
+  if (!ok || nvar <= 0 || nchk <= 0 || (int)o.sumX1.size() != nvar || (int)o.sumX2.size() != nchk || o.V.size() % (size_t)nchk ||
+      o.C.size() % (size_t)nvar) {
+    err = "bp codec file: a variable of LDPC_Code::save_code is missing or has the wrong size";
+    return false;
+  }
+  o.nvar = nvar; o.ncheck = nchk; o.ncheck_lin_indep = nli;
+  if (g_def) {
+    const ItVar* g = f.find("G", "GF2mat");
+    uint64_t d[3] = {0, 0, 0};
+    if (g && g->n >= 24) memcpy(d, g->p, 24);
+    if (!g || d[0] == 0 || d[1] == 0 || d[2] != (d[1] + 7) / 8 || g->n != 24 + d[0] * d[2] || d[0] + d[1] != (uint64_t)nvar) {
+      err = "bp codec file: generator block missing or inconsistent";
+      return false;
+    }
+    o.gen_rows = (int)d[0]; o.gen_cols = (int)d[1];
+    o.gen_bytes.assign(g->p + 24, g->p + 24 + d[0] * d[2]);
+  }
+  return true;
+}
+
+bool save_bp_codec_file(const char* path, const BpCodecFile& m, std::string& err) {
+  FILE* fp = fopen(path, "wb");
+  if (!fp) { err = std::string("save_code: cannot open ") + path; return false; }
+  bool ok = fwrite("IT++\x03", 1, 5, fp) == 5;
+  auto block = [&](const char* name, const char* type, const std::string& data) {
+    const uint64_t hdr = 24 + strlen(name) + 1 + strlen(type) + 1 + 1, db = data.size(), blk = hdr + db;
+    ok = ok && fwrite(&hdr, 8, 1, fp) == 1 && fwrite(&db, 8, 1, fp) == 1 && fwrite(&blk, 8, 1, fp) == 1;
+    ok = ok && fwrite(name, 1, strlen(name) + 1, fp) == strlen(name) + 1 && fwrite(type, 1, strlen(type) + 1, fp) == strlen(type) + 1;
+    ok = ok && fputc(0, fp) == 0;
+    ok = ok && (data.empty() || fwrite(data.data(), 1, data.size(), fp) == data.size());
+  };
+  auto i32 = [&](const char* name, int32_t v) { block(name, "int32", std::string(reinterpret_cast<const char*>(&v), 4)); };
+  auto flag = [&](const char* name, bool v) { block(name, "bool", std::string(1, v ? '\1' : '\0')); };
+  auto counted = [](uint64_t n) { return std::string(reinterpret_cast<const char*>(&n), 8); };
+  auto ivec = [&](const char* name, const std::vector<int32_t>& v) {
+    std::string d = counted(v.size());
+    d.append(reinterpret_cast<const char*>(v.data()), 4 * v.size());
+    block(name, "ivec", d);
+  };
+  i32("Fileversion", 3);  // LDPC_binary_file_version, itpp/itpp/comm/ldpc.cpp:42
+  flag("H_defined", true);
+  flag("G_defined", m.gen_rows > 0);
+  i32("nvar", m.nvar);
+  i32("ncheck", m.ncheck);
+  i32("ncheck_lin_indep", m.ncheck_lin_indep);
+  ivec("C", m.C);
+  ivec("V", m.V);
+  ivec("sumX1", m.sumX1);
+  ivec("sumX2", m.sumX2);
+  ivec("iind", m.iind);
+  ivec("jind", m.jind);
+  if (m.gen_rows > 0) {  // LDPC_Generator_Systematic::save (:1002-1009); its "Fileversion" is the same 3 and stays in place
+    block("G_type", "string", counted(10) + "systematic");
+    const uint64_t d[3] = {(uint64_t)m.gen_rows, (uint64_t)m.gen_cols, (uint64_t)(m.gen_cols + 7) / 8};
+    std::string g(reinterpret_cast<const char*>(d), 24);
+    g.append(reinterpret_cast<const char*>(m.gen_bytes.data()), m.gen_bytes.size());
+    block("G", "GF2mat", g);
+  }
+  ok = (fclose(fp) == 0) && ok;
+  if (!ok) err = std::string("save_code: write error on ") + path;
+  return ok;
+}
+
 // bundle ("LUTLDPC1", oracle/ref_driver.cpp) or the reference's codec file ("IT++"), by magic
 bool load_decoder_file(const char* path, DecoderModel& m, std::string& err) {
   FILE* fp = fopen(path, "rb");

@@ -58,6 +58,17 @@ bool load_it_codec_file(const char* path, DecoderModel& m, std::string& err);
 // reference's load_code (and lut_ldpc_vhdl, scripts/) reads.  The generator is not written: a file to which
 // LDPC_Generator_Systematic::save has appended (it replaces "Fileversion" by IT++'s own, 3) is refused by load_code (:578-579).
 bool save_it_codec_file(const char* path, const DecoderModel& m, std::string& err);
+// IT++'s LDPC_Code::save_code / load_code file (itpp/itpp/comm/ldpc.cpp:1250-1322), the bp_codec.it of ber_sim's [BP]
+// path, with the block LDPC_Generator_Systematic::save appends (:1002-1009): the decoder parameterisation of H as
+// LDPC_Code holds it (:1676-1745) and the parity part G of the systematic generator, rows packed 8 columns per byte.
+struct BpCodecFile {
+  int nvar = 0, ncheck = 0, ncheck_lin_indep = 0;
+  std::vector<int32_t> C, V, sumX1, sumX2, iind, jind;
+  int gen_rows = 0, gen_cols = 0;        // 0: no generator stored
+  std::vector<uint8_t> gen_bytes;        // [gen_rows][(gen_cols + 7) / 8], bit (c & 7) of byte c >> 3 = column c
+};
+bool load_bp_codec_file(const char* path, BpCodecFile& f, std::string& err);
+bool save_bp_codec_file(const char* path, const BpCodecFile& f, std::string& err);
 // either of the two, told apart by the file magic
 bool load_decoder_file(const char* path, DecoderModel& m, std::string& err);
 // fills the derived members and validates; false + err on unsupported/inconsistent input

@@ -202,15 +202,27 @@ int main(int argc, char** argv) {
     if (use_bp) {
       // ---- LDPC_BER_Sim::load, src/LDPC_BER_Sim.cpp:157-244: LDPC_Parity(alist) [+ LDPC_Generator_Systematic] ->
       // LDPC_Code, exit conditions (max_iter, pci, pci) and the LLR_calc_unit of the [BP] section
-      if (!codec.empty()) throw std::runtime_error("LDPC_BER_Sim::load(): stored bp_codec.it files are not supported, name the alist");
-      const std::string alist = path(codes_dir + "/" + ini.get("LDPC.parity_filename", "") + ".alist");
-      struct stat sb;
-      if (stat(alist.c_str(), &sb) != 0) throw std::runtime_error("Parity file" + alist + " does not exist!");  // :162-164
       LLR_calc_unit lc((short)ini.num("BP.qllr_scale_res", 12), (short)ini.num("BP.qllr_table_size", 300),
                        (short)ini.num("BP.qllr_spacing_res", 7), (short)ini.num("BP.qllr_total_res", 28));
-      for (int g = 0; g < gpus; ++g) {
-        if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
-        Cbp[g].reset(new LDPC_Code(alist, !zero_cw, (int)ini.num("BP.max_iter", 30), pci, pci, lc));
+      const int bp_iter = (int)ini.num("BP.max_iter", 30);
+      struct stat sb;
+      if (!codec.empty()) {  // LDPC_Code(codec_path, G), src/LDPC_BER_Sim.cpp:219-239
+        std::string codec_file = path(codes_dir + "/" + codec);
+        if (codec[0] == '/' || stat(codec_file.c_str(), &sb) != 0) codec_file = path(codec);
+        if (stat(codec_file.c_str(), &sb) != 0) throw std::runtime_error("Codec file" + codec_file + " does not exist!");
+        for (int g = 0; g < gpus; ++g) {
+          if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
+          Cbp[g].reset(new LDPC_Code(codec_file, LDPC_Code::from_file_t(), bp_iter, pci, pci, lc));
+        }
+        if (!zero_cw && !Cbp[0]->has_generator())
+          throw std::runtime_error("LDPC.zero_codeword=false needs a codec file that carries the generator");
+      } else {
+        const std::string alist = path(codes_dir + "/" + ini.get("LDPC.parity_filename", "") + ".alist");
+        if (stat(alist.c_str(), &sb) != 0) throw std::runtime_error("Parity file" + alist + " does not exist!");  // :162-164
+        for (int g = 0; g < gpus; ++g) {
+          if (lutldpc_set_device(g) != LUTLDPC_OK) throw std::runtime_error("cudaSetDevice failed");
+          Cbp[g].reset(new LDPC_Code(alist, !zero_cw, bp_iter, pci, pci, lc));
+        }
       }
     } else if (!codec.empty()) {
       // codes_path / codec_filename (src/LDPC_BER_Sim.cpp:524), else relative to the base directory
@@ -306,6 +318,11 @@ int main(int argc, char** argv) {
          << "_zcw" << (int)zero_cw << "_frames" << Nframes;
     if (use_lut) name << (C[0]->is_min_lut() ? "_minLUT" : "_LUT");
     name << custom;
+    if (use_bp && codec.empty() && (int64_t)seed == (int64_t)ini.num("Sim.save_codec", 0)) {  // :207-216
+      mkdir(path(results_dir).c_str(), 0777);
+      mkdir((path(results_dir) + "/" + name.str()).c_str(), 0777);
+      Cbp[0]->save_code(path(results_dir) + "/" + name.str() + "/bp_codec.it");
+    }
     // a designed decoder is saved when the seed equals Sim.save_codec (src/LDPC_BER_Sim.cpp:59,511-520)
     if (use_lut && codec.empty() && (int64_t)seed == (int64_t)ini.num("Sim.save_codec", 0)) {
       mkdir(path(results_dir).c_str(), 0777);

@@ -41,6 +41,22 @@ class LDPC_Code : public Channel_Code {
     if (rc != LUTLDPC_OK) throw std::runtime_error(std::string("LDPC_Code::LDPC_Code(): ") + lutldpc_bp_last_error(nullptr));
     ck(lutldpc_bp_get_info(h_, &info_), "get_info");
   }
+  // LDPC_Code(const std::string& filename, LDPC_Generator* G) (ldpc.cpp:1217-1222): a stored bp_codec.it, with its
+  // generator if one was saved
+  struct from_file_t {};
+  LDPC_Code(const std::string& codec_filename, from_file_t, int max_iters = 50, bool syndr_check_each_iter = true,
+            bool syndr_check_at_start = false, const LLR_calc_unit& llrcalc = LLR_calc_unit())
+      : h_(nullptr) {
+    lutldpc_bp_params p;
+    p.max_iters = max_iters; p.psc = syndr_check_each_iter; p.pisc = syndr_check_at_start;
+    p.qllr_scale_res = llrcalc.Dint1; p.qllr_table_size = llrcalc.Dint2; p.qllr_spacing_res = llrcalc.Dint3;
+    p.qllr_total_res = llrcalc.Dint4;
+    if (lutldpc_bp_create_from_file(codec_filename.c_str(), &p, &h_) != LUTLDPC_OK)
+      throw std::runtime_error(std::string("LDPC_Code::load_code(): ") + lutldpc_bp_last_error(nullptr));
+    ck(lutldpc_bp_get_info(h_, &info_), "get_info");
+  }
+  // ldpc.cpp:1283-1322
+  void save_code(const std::string& filename) const { ck(lutldpc_bp_save_code(h_, filename.c_str()), "save_code"); }
   ~LDPC_Code() override { lutldpc_bp_destroy(h_); }
   LDPC_Code(const LDPC_Code&) = delete;
   LDPC_Code& operator=(const LDPC_Code&) = delete;

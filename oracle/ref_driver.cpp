@@ -386,8 +386,18 @@ static int cmd_results(const Args& a) {
 // LLR_calc_unit the .ini names.  bpfixture records, per frame, the channel LLRs, to_qllr of them, bp_decode's
 // soft output and its return value; bpsim is the frame loop of sim_snr_point around LDPC_Code::decode.
 static LDPC_Code* load_bp(const Args& a, const std::string& alist, LDPC_Parity** Hout) {
-  LDPC_Parity* H = new LDPC_Parity(alist, "alist");
-  LDPC_Code* C = new LDPC_Code(H);
+  LDPC_Parity* H = nullptr;
+  LDPC_Code* C;
+  if (alist.size() > 3 && alist.substr(alist.size() - 3) == ".it") {  // a stored bp_codec.it (LDPC_Code(filename, G))
+    it_ifile f(alist);
+    bool g_def = false;
+    f >> Name("G_defined") >> g_def;
+    f.close();
+    C = new LDPC_Code(alist, g_def ? new LDPC_Generator_Systematic() : nullptr);
+  } else {
+    H = new LDPC_Parity(alist, "alist");
+    C = new LDPC_Code(H);
+  }
   bool psc = a.num("psc", 1) != 0, pisc = a.num("pisc", a.num("psc", 1)) != 0;  // load(): (max_iter, pci, pci), :200
   C->set_exit_conditions((int)a.num("max-iter", 30), psc, pisc);
   C->set_llrcalc(LLR_calc_unit((short)a.num("d1", 12), (short)a.num("d2", 300), (short)a.num("d3", 7),
@@ -471,9 +481,55 @@ static int cmd_bpsim(const Args& a) {
   return 0;
 }
 
+// ---- bp_codec.it: what LDPC_BER_Sim::load saves / loads for the BP decoder (src/LDPC_BER_Sim.cpp:207-216,219-239):
+// IT++'s LDPC_Code::save_code / load_code (itpp/itpp/comm/ldpc.cpp:1250-1322) + LDPC_Generator_Systematic::save.
+//   bpcodec <alist> <out.it> [--gen 1] [--pairs file --n K]   H [and G] -> LDPC_Code -> save_code; with --pairs also
+//                                                             n (info, codeword) pairs of G->encode, one byte per bit
+//   bpreload <in.it> <out.it> [--pairs file --n K]            load_code (with its generator if present) -> save_code
+static void write_pairs(const Args& a, LDPC_Code& C) {
+  if (!a.has("pairs")) return;
+  std::ofstream os(a.get("pairs").c_str(), std::ios::binary);
+  int n = (int)a.num("n", 4), K = C.get_ninfo(), N = C.get_nvar();
+  put_i32(os, n); put_i32(os, K); put_i32(os, N);
+  RNG_reset((unsigned)a.num("seed", 1));
+  for (int f = 0; f < n; f++) {
+    bvec u = randb(K), cw = C.encode(u);
+    for (int i = 0; i < K; i++) os.put((char)(int)u(i));
+    for (int i = 0; i < N; i++) os.put((char)(int)cw(i));
+  }
+}
+static int cmd_bpcodec(const Args& a) {
+  if (a.pos.size() < 2) { fprintf(stderr, "bpcodec <code.alist> <out.it> [--gen 1]\n"); return 2; }
+  RNG_reset((unsigned)a.num("seed", 0));
+  LDPC_Parity* H = new LDPC_Parity(a.pos[0], "alist");
+  LDPC_Code* C;
+  if (a.num("gen", 0) != 0) {
+    LDPC_Generator_Systematic* G = new LDPC_Generator_Systematic(H);  // permutes the columns of *H
+    C = new LDPC_Code(H, G);
+  } else C = new LDPC_Code(H);
+  C->save_code(a.pos[1]);
+  if (a.num("gen", 0) != 0) write_pairs(a, *C);
+  printf("{\"cmd\":\"bpcodec\",\"nvar\":%d,\"ncheck\":%d,\"ninfo\":%d}\n", C->get_nvar(), C->get_ncheck(), C->get_ninfo());
+  return 0;
+}
+static int cmd_bpreload(const Args& a) {
+  if (a.pos.size() < 2) { fprintf(stderr, "bpreload <in.it> <out.it>\n"); return 2; }
+  it_ifile f(a.pos[0]);
+  bool g_def = false;
+  f >> Name("G_defined") >> g_def;
+  f.close();
+  LDPC_Generator_Systematic* G = g_def ? new LDPC_Generator_Systematic() : nullptr;
+  LDPC_Code C(a.pos[0], G);
+  C.save_code(a.pos[1]);
+  if (g_def) write_pairs(a, C);
+  printf("{\"cmd\":\"bpreload\",\"nvar\":%d,\"ncheck\":%d,\"ninfo\":%d,\"generator\":%d}\n", C.get_nvar(), C.get_ncheck(),
+         C.get_ninfo(), (int)g_def);
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 2) {
-    fprintf(stderr, "usage: lutldpc_ref design|bundle|fixture|sim|results|bpfixture|bpsim ...\n");
+    fprintf(stderr, "usage: lutldpc_ref design|bundle|fixture|sim|results|bpfixture|bpsim|bpcodec|bpreload ...\n");
     return 2;
   }
   std::string cmd = argv[1];
@@ -485,6 +541,8 @@ int main(int argc, char** argv) {
   if (cmd == "results") return cmd_results(a);
   if (cmd == "bpfixture") return cmd_bpfixture(a);
   if (cmd == "bpsim") return cmd_bpsim(a);
+  if (cmd == "bpcodec") return cmd_bpcodec(a);
+  if (cmd == "bpreload") return cmd_bpreload(a);
   fprintf(stderr, "unknown command %s\n", cmd.c_str());
   return 2;
 }

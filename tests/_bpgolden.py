@@ -27,8 +27,37 @@ def fixture(name):
     return pyoracle.read_bp_fixture(dst)
 
 
+def it_file_vars(raw):
+    """the int32 / ivec variables of an IT++ it_file (itpp/itpp/base/itfile.h:98-125) as numpy values"""
+    import struct
+    import numpy as np
+    out, off = {}, 5
+    while off + 24 <= len(raw):
+        hb, db, bb = struct.unpack("<3Q", raw[off:off + 24])
+        name, typ = raw[off + 24:off + hb].split(b"\0")[:2]
+        if typ == b"ivec":
+            out[name.decode()] = np.frombuffer(raw, "<i4", (db - 8) // 4, off + hb + 8).copy()
+        elif typ == b"int32":
+            out[name.decode()] = int(np.frombuffer(raw, "<i4", 1, off + hb)[0])
+        off += bb
+    return out
+
+
+def stored_codec(fname):
+    import lzma
+    return lzma.open(os.path.join(BP_DIR, fname + ".xz")).read()
+
+
 def graph(name):
     g = BP_MANIFEST[name]["graph"]
+    if g.startswith("file:"):  # a bp_codec.it: edges of variable v in the stored order, jind = v + k * nvar
+        import numpy as np
+        v = it_file_vars(stored_codec(g[5:]))
+        dv, dc, nvar, nchk = v["sumX1"], v["sumX2"], v["nvar"], v["ncheck"]
+        off = np.concatenate([[0], np.cumsum(dv)])
+        idx = [off[v["jind"][j + nchk * ip] % nvar] + v["jind"][j + nchk * ip] // nvar for j in range(nchk) for ip in range(dc[j])]
+        return dict(nvar=nvar, nchk=nchk, num_edges=int(dv.sum()), nchk_lin_indep=v["ncheck_lin_indep"], dv_vec=dv.astype(np.int32),
+                    dc_vec=dc.astype(np.int32), cn_msg_idx=np.array(idx, np.int32), codec_file=g[5:])
     if g.startswith("synth:"):
         return _alist.graph_from_rows(*_alist.synth_rows(g[6:]))
     return _alist.bundle_graph(g)

@@ -60,6 +60,33 @@ def main():
                 f.write(raw)
             manifest[name] = dict(graph=graph, args=opts, sha256=hashlib.sha256(raw).hexdigest(), bytes=len(raw))
             print(name, len(raw), os.path.getsize(os.path.join(OUT, name + ".fix.xz")))
+        # bp_codec.it as the reference writes it (LDPC_Code::save_code): hashes for the writer test, and one file with a
+        # generator (+ three (info, codeword) pairs of its encoder) for the reader test
+        codec = {}
+        for cfg in ("c1b_reg36_n1000", "c2_irr_n500", "c4_reg632_high", "c3_irr_n10000"):
+            alist = os.path.join(tmp, cfg + ".alist")
+            _alist.write_alist(cfg, alist)
+            out = os.path.join(tmp, cfg + ".bp_codec.it")
+            subprocess.check_call([REF, "bpcodec", alist, out], stdout=subprocess.DEVNULL)
+            codec[cfg] = hashlib.sha256(open(out, "rb").read()).hexdigest()
+        alist = os.path.join(tmp, "c2_irr_n500.alist")
+        out, pairs = os.path.join(tmp, "g.it"), os.path.join(OUT, "c2_gen.pairs.bin")
+        subprocess.check_call([REF, "bpcodec", alist, out, "--gen", "1", "--pairs", pairs, "--n", "3", "--seed", "21"],
+                              stdout=subprocess.DEVNULL)
+        raw = open(out, "rb").read()
+        with lzma.open(os.path.join(OUT, "c2_gen.bp_codec.it.xz"), "wb", preset=9 | lzma.PRESET_EXTREME) as f:
+            f.write(raw)
+        codec["c2_gen"] = hashlib.sha256(raw).hexdigest()
+        json.dump(codec, open(os.path.join(HERE, "bp_codec_sha256.json"), "w"), indent=1, sort_keys=True)
+        # frames through the decoder the reference builds from that file: after the generator's column permutation the
+        # lists of H are no longer sorted, and the order of a node's inputs is the order of its operations
+        name, opts = "c2_gen_stored_order", "--snr 1.2 --frames 10 --max-iter 30 --with-llr 0 --seed 15"
+        fix = os.path.join(tmp, name + ".fix")
+        subprocess.check_call([REF, "bpfixture", out, fix] + opts.split())
+        raw = open(fix, "rb").read()
+        with lzma.open(os.path.join(OUT, name + ".fix.xz"), "wb", preset=9 | lzma.PRESET_EXTREME) as f:
+            f.write(raw)
+        manifest[name] = dict(graph="file:c2_gen.bp_codec.it", args=opts, sha256=hashlib.sha256(raw).hexdigest(), bytes=len(raw))
     json.dump(manifest, open(os.path.join(HERE, "bp_manifest.json"), "w"), indent=1, sort_keys=True)
 
 

@@ -55,3 +55,23 @@ def test_convert_reports_errors(tmp_path):
     assert L.lutldpc_convert_codec(b"/nonexistent/file", os.fsencode(tmp_path / "x.it")) != 0
     assert b"cannot open" in L.lutldpc_last_error(None)
     assert L.lutldpc_convert_codec(os.fsencode(_golden.bundle_path("c2_irr_n500")), b"/nonexistent/dir/x.it") != 0
+
+
+# ---- bp_codec.it (IT++ LDPC_Code::save_code, the [BP] path's codec file)
+BP_SHA = __import__("json").load(open(os.path.join(_golden.GOLD, "bp_codec_sha256.json")))
+
+
+@pytest.mark.parametrize("cfg", sorted(k for k in BP_SHA if k != "c2_gen"))
+def test_bp_codec_file_equals_the_reference_written_one(cfg, tmp_path):
+    """alist -> bp_codec.it: C, V, sumX1, sumX2, iind, jind as LDPC_Code::decoder_parameterization lays them out; the file
+    has the hash of the one the reference wrote for the same matrix (tests/golden/make_bp_golden.py)"""
+    import hashlib
+    import _alist
+    alist, out = str(tmp_path / "h.alist"), str(tmp_path / "bp_codec.it")
+    _alist.write_alist(cfg, alist)
+    capi.bp_convert_alist(alist, out)
+    assert hashlib.sha256(open(out, "rb").read()).hexdigest() == BP_SHA[cfg]
+    if os.path.exists(REF):  # and the unmodified reference loads it and writes the same bytes again
+        back = str(tmp_path / "back.it")
+        subprocess.run([REF, "bpreload", out, back], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        assert open(back, "rb").read() == open(out, "rb").read()

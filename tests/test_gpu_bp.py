@@ -24,6 +24,13 @@ def capi():
 
 
 def _dec(capi, g, par, **kw):
+    if "codec_file" in g:  # a stored bp_codec.it: the graph in the order the file holds it
+        import tempfile
+        with tempfile.NamedTemporaryFile(suffix=".it") as f:
+            f.write(_bpgolden.stored_codec(g["codec_file"]))
+            f.flush()
+            return capi.BpDecoder.from_file(f.name, max_iters=par.max_iter, psc=par.psc, pisc=par.pisc, qllr_scale_res=par.d1,
+                                            qllr_table_size=par.d2, qllr_spacing_res=par.d3, qllr_total_res=par.d4)
     return capi.BpDecoder(g, max_iters=par.max_iter, psc=par.psc, pisc=par.pisc, qllr_scale_res=par.d1,
                           qllr_table_size=par.d2, qllr_spacing_res=par.d3, qllr_total_res=par.d4, **kw)
 
@@ -277,3 +284,87 @@ def test_bp_resolutions_below_the_table_values(capi, d1, d2, d3, d4):
     want_out, want_ret = pyoracle.bp_decode(g["dv_vec"], g["dc_vec"], g["cn_msg_idx"], qin, par)
     out, ret = dec.decode_qllr(qin)
     assert np.array_equal(ret, want_ret) and np.array_equal(out, want_out)
+
+
+def _unxz(name, tmp_path):
+    import lzma
+    dst = str(tmp_path / name)
+    open(dst, "wb").write(lzma.open(os.path.join(_bpgolden.BP_DIR, name + ".xz")).read())
+    return dst
+
+
+def _pairs(path):
+    raw = open(path, "rb").read()
+    n, K, N = np.frombuffer(raw, "<i4", 3)
+    a = np.frombuffer(raw, np.uint8, offset=12).reshape(n, K + N)
+    return a[:, :K].copy(), a[:, K:].copy()
+
+
+def test_bp_codec_file_with_generator_round_trip(capi, tmp_path):
+    """a bp_codec.it the reference wrote WITH its generator (random column order): the handle created from it encodes
+    like the reference's LDPC_Generator_Systematic::encode, decodes its codewords, and saves the same bytes again"""
+    src = _unxz("c2_gen.bp_codec.it", tmp_path)
+    dec = capi.BpDecoder.from_file(src, max_iters=30)
+    assert dec.has_gen and dec.nvar == 500 and dec.ninfo == 250
+    info, cw = _pairs(os.path.join(_bpgolden.BP_DIR, "c2_gen.pairs.bin"))
+    assert np.array_equal(dec.encode(info), cw)
+    bits, ret = dec.decode_llr((1.0 - 2.0 * cw) * 5.0)
+    assert np.array_equal(bits, cw) and (ret == 0).all()
+    out = str(tmp_path / "again.it")
+    dec.save_code(out)
+    assert open(out, "rb").read() == open(src, "rb").read()
+    c = dec.simulate_snr(2.0, 4096, seed=3, zero_codeword=False)
+    assert c.frames == 4096 and 0 < c.frame_errors < 400
+
+
+def test_bp_generator_built_here_is_accepted_by_the_reference(capi, tmp_path):
+    """alist -> generator on the device -> save_code: the unmodified reference loads the file (LDPC_Code(file, G)),
+    writes the same bytes back, and its encoder gives the codewords lutldpc_bp_encode gives"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref = os.path.join(root, "oracle", "_ref", "lutldpc_ref")
+    if not os.path.exists(ref):
+        pytest.skip("compiled reference not present")
+    dec = capi.BpDecoder(_alist.bundle_graph("c1b_reg36_n1000"), with_generator=True)
+    mine, back, pairs = str(tmp_path / "bp_codec.it"), str(tmp_path / "back.it"), str(tmp_path / "pairs.bin")
+    dec.save_code(mine)
+    subprocess.run([ref, "bpreload", mine, back, "--pairs", pairs, "--n", "4", "--seed", "5"], check=True,
+                   stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    assert open(back, "rb").read() == open(mine, "rb").read()
+    info, cw = _pairs(pairs)
+    assert np.array_equal(dec.encode(info), cw)
+    again = capi.BpDecoder.from_file(mine)
+    assert again.has_gen and np.array_equal(again.encode(info), cw)
+
+
+def test_bp_harness_saves_and_reloads_its_codec(capi, tmp_path):
+    """Sim.save_codec / Sim.codec_filename + codec_type = BP (src/LDPC_BER_Sim.cpp:207-239): a run leaves
+    results/<name>/bp_codec.it, a second run that loads it (no alist, no [BP] section needed to pick the decoder)
+    reproduces the first run's counters; the C++ binary does the same"""
+    import shutil
+    import subprocess
+    from lut_ldpc_b200 import ber_sim as bs
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    (tmp_path / "codes").mkdir()
+    _alist.write_alist("c2_irr_n500", str(tmp_path / "codes" / "irr500.alist"))
+    a = tmp_path / "a.ini"
+    a.write_text("[Sim]\nSNRdB = 2\nNframes = 8192\nNfers = 1000000\nfer_min = 0\nber_min = 0\nsave_codec = 3\n"
+                 "[LDPC]\nparity_filename = irr500\nzero_codeword = false\n[BP]\nmax_iter = 30\n")
+    sim = bs.make_sim(bs.SimParams(str(a)), rand_seed=3, chunk_frames=8192).load(str(tmp_path))
+    first = sim.run(verbose=False)
+    saved = tmp_path / "results" / sim.gen_filename() / "bp_codec.it"
+    assert saved.exists()
+    shutil.copy(saved, tmp_path / "codes" / "stored_bp.it")
+    b = tmp_path / "b.ini"
+    b.write_text("[Sim]\nSNRdB = 2\nNframes = 8192\nNfers = 1000000\nfer_min = 0\nber_min = 0\nsave_codec = -1\n"
+                 "codec_filename = stored_bp.it\ncodec_type = BP\n[LDPC]\nzero_codeword = false\n")
+    p = bs.SimParams(str(b))
+    assert p.has_bp_section and not p.has_lut_section
+    again = bs.make_sim(p, rand_seed=3, chunk_frames=8192).load(str(tmp_path)).run(verbose=False)
+    assert again == first and first["sim_frame_errors"][0] > 0
+    exe = os.path.join(root, "lut_ldpc_b200", "ber_sim")
+    if os.path.exists(exe):
+        out = subprocess.run([exe, "-p", str(b), "-b", str(tmp_path), "-s", "3"], capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, (out.stdout[-1000:], out.stderr[-1000:])
+        line = [l for l in out.stdout.splitlines() if l.startswith("SNR = ")][0]
+        assert int(line.split("Obtained ")[1].split(" data bit errors")[0]) == first["sim_data_bit_errors"][0]
