@@ -35,6 +35,7 @@ CASES = {
     "c2_coarse_table": ("c2_irr_n500", "--snr 1.5 --frames 8 --max-iter 40 --d1 8 --d2 64 --d3 4 --d4 12 --seed 8"),
     "c4_dc32": ("c4_reg632_high", "--snr 4.0 --frames 6 --max-iter 30 --seed 9 --with-llr 0"),
     "c3_n10000": ("c3_irr_n10000", "--snr 1.2 --frames 3 --max-iter 50 --with-llr 0 --seed 10"),
+    "c3_n10000_lowsnr": ("c3_irr_n10000", "--snr 0.85 --frames 3 --max-iter 50 --with-llr 0 --seed 16"),
     "c5_n64800": ("c5_n64800", "--snr 1.2 --frames 1 --max-iter 50 --with-llr 0 --seed 11"),
     "synth_mixed": ("synth:mixed", "--snr 2.0 --frames 10 --max-iter 20 --seed 12"),
     "synth_mixed_minsum": ("synth:mixed", "--snr 3.0 --frames 8 --max-iter 20 --d2 0 --seed 13 --with-llr 0"),
