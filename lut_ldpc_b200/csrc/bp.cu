@@ -352,16 +352,24 @@ __global__ void __launch_bounds__(kBpThreads) k_bp_vn_any(const int32_t* __restr
 }
 
 // syndrome_check(LLRout) (ldpc.cpp:1631-1652) for 32 slots at a time: XOR of the sign words of a check's variables
+constexpr int kSynChecks = 8;  // checks per thread: their parities are OR-ed before the one atomic
 __global__ void k_bp_syndrome(const int32_t* __restrict__ cn_off, const int32_t* __restrict__ cn_var, int M, int S32,
                               const uint32_t* __restrict__ hardw, const uint32_t* __restrict__ donew,
                               uint32_t* __restrict__ failw) {
   const int w = blockIdx.y * blockDim.x + threadIdx.x;
-  const int j = blockIdx.x * blockDim.y + threadIdx.y;
-  if (w >= S32 || j >= M) return;
+  const int j0 = (blockIdx.x * blockDim.y + threadIdx.y) * kSynChecks;
+  if (w >= S32 || j0 >= M) return;
   if (donew[w] == 0xFFFFFFFFu) return;
-  uint32_t x = 0;
-  for (int k = cn_off[j]; k < cn_off[j + 1]; ++k) x ^= hardw[(size_t)cn_var[k] * S32 + w];
-  if (x) atomicOr(&failw[w], x);
+  uint32_t fail = 0;
+  const int j1 = min(M, j0 + kSynChecks);
+  for (int j = j0; j < j1; ++j) {
+    uint32_t x = 0;
+    const int k1 = cn_off[j + 1];
+#pragma unroll 4
+    for (int k = cn_off[j]; k < k1; ++k) x ^= hardw[(size_t)cn_var[k] * S32 + w];
+    fail |= x;
+  }
+  if (fail) atomicOr(&failw[w], fail);
 }
 
 // slots whose syndrome is zero return `iter` (:1613-1616, or 0 from the initial check :1408-1411)
@@ -707,7 +715,7 @@ int run_batch(lutldpc_bp* h, int F, size_t S, const BatchIO& io) {
   ++h->launches;
 
   auto syndrome_and_mark = [&](int iter) -> int {
-    k_bp_syndrome<<<dim3((M + 3) / 4, (S32 + 31) / 32), dim3(32, 4), 0, st>>>(h->d_cn_off.p, h->d_cn_var.p, M, S32, h->hardw.p,
+    k_bp_syndrome<<<dim3((M + 4 * kSynChecks - 1) / (4 * kSynChecks), (S32 + 31) / 32), dim3(32, 4), 0, st>>>(h->d_cn_off.p, h->d_cn_var.p, M, S32, h->hardw.p,
                                                                               h->donew.p, h->failw.p);
     CKBL("bp syndrome");
     k_bp_mark<<<std::max(1, std::min(64, S32 / 128)), 128, 0, st>>>(iter, S32, h->failw.p, h->donew.p, h->fid.p, h->iters.p);
